@@ -1,0 +1,177 @@
+/*
+ * m3r_backends.h -- C ABI of the B200-native (sm_100a) MASt3R-SLAM dense backend.
+ *
+ * This is the drop-in boundary for the reference's native extension `mast3r_slam_backends`
+ * (reference: mast3r_slam/backend/src/gn.cpp:116-123 exports gauss_newton_points, gauss_newton_rays,
+ * gauss_newton_calib, iter_proj, refine_matches; declarations in mast3r_slam/backend/include/gn.h:11-117).
+ * The reference has no C ABI of its own -- its pybind function table is the operator API -- so each
+ * entry point below carries exactly the arguments of the corresponding pybind function, flattened to
+ * plain pointers + sizes (tensor layouts unchanged, see each comment).  The Python host side
+ * (mast3r_slam_ysh_b200/backends.py) re-creates the reference's torch-tensor signatures on top of it.
+ *
+ * Conventions
+ *   - every `const T*` / `T*` is a DEVICE pointer on the current CUDA device unless the name ends in _host;
+ *   - `stream` is a cudaStream_t passed as void* (NULL = legacy default stream); all work is enqueued on it and
+ *     NO entry point synchronises with the host (the reference blocks the host 3x per GN iteration,
+ *     gn_kernels.cu:1199-1222);
+ *   - return value: 0 on success, otherwise a negative M3R_ERR_* or a positive cudaError_t from a failed launch;
+ *     m3r_last_error_string() describes the last failure of the calling thread;
+ *   - numerical failure is NOT an error (reference: gn_kernels.cu:142-150): a non-SPD system yields dx = 0 and
+ *     leaves the poses untouched.
+ */
+#ifndef M3R_BACKENDS_H_
+#define M3R_BACKENDS_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define M3R_ABI_VERSION 1
+
+#if defined(__GNUC__)
+#define M3R_API __attribute__((visibility("default")))
+#else
+#define M3R_API
+#endif
+
+#define M3R_OK 0
+#define M3R_ERR_INVALID_ARGUMENT (-1)
+#define M3R_ERR_WORKSPACE_TOO_SMALL (-2)
+#define M3R_ERR_UNSUPPORTED (-3)
+
+/* residual kinds of the three Gauss-Newton entry points */
+#define M3R_GN_POINTS 0 /* gauss_newton_points (gn.h:22-31)  */
+#define M3R_GN_RAYS 1   /* gauss_newton_rays   (gn.h:45-55)  */
+#define M3R_GN_CALIB 2  /* gauss_newton_calib  (gn.h:74-87)  */
+
+/* robust kernels: the reference's CUDA kernels hard-code Huber k=1.345 (gn_kernels.cu:172-175); Tukey
+ * (nonlinear_optimizer.py:36-42, t=4.6851) is an opt-in extension named by BASELINE.json:north_star. */
+#define M3R_ROBUST_HUBER 0
+#define M3R_ROBUST_TUKEY 1
+
+M3R_API int m3r_abi_version(void);
+M3R_API const char* m3r_last_error_string(void);
+/* number of kernels this library launched from the calling process so far (bench.py's gpu_launches claim) */
+M3R_API uint64_t m3r_launch_count(void);
+
+/* ---------------------------------------------------------------------------------------------------------
+ * iter_proj  -- replaces iter_proj (gn.cpp:84-99 -> matching_kernels.cu:279-316, kernel :119-275)
+ *   rays_img_with_grad (b,h,w,9) f32, pts_3d_norm (b,n,3) f32, p_init (b,n,2) f32 [u,v]
+ *   -> p_new (b,n,2) f32, converged (b,n) bool(1 byte)
+ * ------------------------------------------------------------------------------------------------------- */
+M3R_API int m3r_iter_proj(const float* rays_img_with_grad, const float* pts_3d_norm, const float* p_init, float* p_new,
+                  uint8_t* converged, int b, int h, int w, int n, int max_iter, float lambda_init,
+                  float cost_thresh, void* stream);
+
+/* ---------------------------------------------------------------------------------------------------------
+ * refine_matches -- replaces refine_matches (gn.cpp:101-114 -> matching_kernels.cu:84-116, kernel :25-81)
+ *   D11 (b,h,w,fdim), D21 (b,n,fdim) fp16 (the dtype every reference caller uses, matching.py:80-81) or fp32;
+ *   p1 (b,n,2) int64 [u,v] -> p1_new (b,n,2) int64.  fp16 scores are rounded to fp16 after every multiply and
+ *   every add, exactly like c10::Half arithmetic in the reference kernel.
+ * ------------------------------------------------------------------------------------------------------- */
+M3R_API int m3r_refine_matches_f16(const uint16_t* D11, const uint16_t* D21, const int64_t* p1, int64_t* p1_new, int b,
+                           int h, int w, int n, int fdim, int radius, int dilation_max, void* stream);
+M3R_API int m3r_refine_matches_f32(const float* D11, const float* D21, const int64_t* p1, int64_t* p1_new, int b, int h,
+                           int w, int n, int fdim, int radius, int dilation_max, void* stream);
+
+/* ---------------------------------------------------------------------------------------------------------
+ * Gauss-Newton -- replaces gauss_newton_points / gauss_newton_rays / gauss_newton_calib
+ *   (gn.cpp:3-82 -> gn_kernels.cu:725-811, :1140-1228, :1546-1637)
+ *
+ *   Twc (num_kf,8) f32 [t, q_xyzw, s]  UPDATED IN PLACE (the primary output, gn_kernels.cu:1212-1215)
+ *   Xs (num_kf,num_pts,3) f32, Cs (num_kf,num_pts,1) f32
+ *   ii, jj (num_edges) int64 GLOBAL keyframe ids; the sorted unique ids index Twc/Xs/Cs (gn_kernels.cu:161-170)
+ *   idx_ii2jj (num_edges,num_pts) int64, valid_match (num_edges,num_pts,1) bool(1 byte), Q (num_edges,num_pts,1) f32
+ *   dx_out (num_kf-1,7) f32: last update (the reference returns it "for debugging", gn_kernels.cu:1227)
+ *   info_out (device, 4 x int32, may be NULL): [0] iterations executed, [1] 1 if stopped on ||dx|| < delta_thresh,
+ *            [2] number of iterations whose factorisation failed (dx = 0), [3] reserved
+ * The whole loop (Hessian assembly, reduction, fp64 Cholesky, retraction, convergence test) runs on the device
+ * without a host round trip; the first sorted keyframe is held fixed (num_fix = 1, gn_kernels.cu:1157).
+ * ------------------------------------------------------------------------------------------------------- */
+typedef struct m3r_gn_params {
+  int32_t kind;   /* M3R_GN_* */
+  int32_t robust; /* M3R_ROBUST_* (reference behaviour: HUBER) */
+  float sigma_a;  /* points: sigma_point | rays: sigma_ray   | calib: sigma_pixel */
+  float sigma_b;  /* points: unused      | rays: sigma_dist  | calib: sigma_depth */
+  float C_thresh;
+  float Q_thresh;
+  /* calib only (gn.h:74-87): intrinsics are read from K (3,3) f32 on the device; K may be NULL otherwise */
+  const float* K;
+  int32_t height, width, pixel_border;
+  float z_eps;
+  int32_t max_iter;
+  float delta_thresh;
+} m3r_gn_params;
+
+/* bytes of device scratch m3r_gauss_newton needs for a problem of this size (256-byte aligned buffer expected) */
+M3R_API size_t m3r_gn_workspace_bytes(int num_kf, int num_pts, int num_edges);
+
+M3R_API int m3r_gauss_newton(const m3r_gn_params* params, float* Twc, const float* Xs, const float* Cs, const int64_t* ii,
+                     const int64_t* jj, const int64_t* idx_ii2jj, const uint8_t* valid_match, const float* Q,
+                     int num_kf, int num_pts, int num_edges, float* dx_out, int32_t* info_out, void* workspace,
+                     size_t workspace_bytes, void* stream);
+
+/* ---------------------------------------------------------------------------------------------------------
+ * Step-wise Gauss-Newton for edge-sharded multi-GPU runs (BASELINE.json:north_star: "graph edges are split across
+ * GPUs and the block Hessian is all-reduced").  Each rank holds a slice of the edges and a replica of Twc/Xs/Cs:
+ *
+ *   m3r_gn_begin(...)               once per solve: index prep for the GLOBAL graph (all_ii/all_jj = every rank's
+ *                                   edges, so that keyframe numbering agrees), packing of this rank's edge slice
+ *   repeat max_iter times:
+ *     m3r_gn_accumulate(...)        Hessian blocks of the local edges -> local dense [H | b] (fp64)
+ *     <all-reduce m3r_gn_system_ptr()/m3r_gn_system_count() doubles over NCCL>
+ *     m3r_gn_solve_retract(...)     replicated fp64 Cholesky + retraction + convergence flag
+ *   m3r_gn_end(...)                 copies dx / info out
+ *
+ * m3r_gauss_newton == begin; max_iter x (accumulate; solve_retract); end on one GPU.
+ * ------------------------------------------------------------------------------------------------------- */
+M3R_API int m3r_gn_begin(const m3r_gn_params* params, const float* Twc, const float* Xs, const float* Cs,
+                 const int64_t* local_ii, const int64_t* local_jj, const int64_t* idx_ii2jj,
+                 const uint8_t* valid_match, const float* Q, int num_kf, int num_pts, int num_local_edges,
+                 const int64_t* all_ii, const int64_t* all_jj, int num_all_edges, void* workspace,
+                 size_t workspace_bytes, void* stream);
+M3R_API int m3r_gn_accumulate(const m3r_gn_params* params, const float* Twc, int num_kf, int num_pts, int num_local_edges,
+                      void* workspace, void* stream);
+M3R_API double* m3r_gn_system_ptr(void* workspace, int num_kf, int num_pts, int num_local_edges);
+M3R_API size_t m3r_gn_system_count(int num_kf);
+M3R_API int m3r_gn_solve_retract(const m3r_gn_params* params, float* Twc, int num_kf, int num_pts, int num_local_edges,
+                         void* workspace, void* stream);
+M3R_API int m3r_gn_end(int num_kf, int num_pts, int num_local_edges, float* dx_out, int32_t* info_out, void* workspace,
+               void* stream);
+
+/* ---------------------------------------------------------------------------------------------------------
+ * Diagnostics used by the parity tests: one evaluation of the per-edge kernel in the reference's output layout
+ *   Hs (4,num_edges,7,7) f32 = [H_ii, H_ij, H_ji, H_jj], gs (2,num_edges,7) f32 = [g_i, g_j]
+ *   (ray_align_kernel / calib_proj_kernel / point_align_kernel epilogue, gn_kernels.cu:1097-1137).
+ * ii_edge/jj_edge here index Twc/Xs directly (the reference's `ii_edge`, gn_kernels.cu:1162-1164).
+ * ------------------------------------------------------------------------------------------------------- */
+M3R_API int m3r_gn_edge_blocks(const m3r_gn_params* params, const float* Twc, const float* Xs, const float* Cs,
+                       const int64_t* ii_edge, const int64_t* jj_edge, const int64_t* idx_ii2jj,
+                       const uint8_t* valid_match, const float* Q, int num_kf, int num_pts, int num_edges, float* Hs,
+                       float* gs, void* workspace, size_t workspace_bytes, void* stream);
+
+/* pose_retr_kernel (gn_kernels.cu:415-453): poses (num_poses,8) in place, dx (num_poses-num_fix,7) */
+M3R_API int m3r_pose_retr(float* poses, const float* dx, int num_poses, int num_fix, void* stream);
+
+/* ---------------------------------------------------------------------------------------------------------
+ * Host-buffer convenience wrappers (end-to-end path: pageable/pinned HOST pointers in, results back on the host).
+ * They allocate device buffers, copy, run the device entry point on `stream`, copy back and synchronise.
+ * ------------------------------------------------------------------------------------------------------- */
+M3R_API int m3r_iter_proj_host(const float* rays_img_with_grad_host, const float* pts_3d_norm_host, const float* p_init_host,
+                       float* p_new_host, uint8_t* converged_host, int b, int h, int w, int n, int max_iter,
+                       float lambda_init, float cost_thresh);
+M3R_API int m3r_refine_matches_f16_host(const uint16_t* D11_host, const uint16_t* D21_host, const int64_t* p1_host,
+                                int64_t* p1_new_host, int b, int h, int w, int n, int fdim, int radius,
+                                int dilation_max);
+M3R_API int m3r_gauss_newton_host(const m3r_gn_params* params_with_host_K, float* Twc_host, const float* Xs_host,
+                          const float* Cs_host, const int64_t* ii_host, const int64_t* jj_host,
+                          const int64_t* idx_ii2jj_host, const uint8_t* valid_match_host, const float* Q_host,
+                          int num_kf, int num_pts, int num_edges, float* dx_out_host, int32_t* info_out_host);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* M3R_BACKENDS_H_ */

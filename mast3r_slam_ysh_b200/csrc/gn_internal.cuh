@@ -1,0 +1,73 @@
+// Internal layout + launcher prototypes shared by gn_hessian.cu / gn_solve.cu / gn_api.cu.
+#pragma once
+#include "m3r_common.cuh"
+
+namespace m3r {
+
+constexpr int kPoseDim = 7;          // sim(3) tangent (tau, omega, sigma)
+constexpr int kAcc = 35;             // 28 lower-triangle entries of S = sum w J J^T  +  7 entries of g = sum w e J
+constexpr int kAccStride = 36;       // padded stride of one tile's partial sums
+constexpr int kTilePix = 2048;       // pixels of one edge handled by one CTA of the Hessian kernel
+constexpr int kHessThreads = 256;
+constexpr int kBlk = 32;             // Cholesky block size
+constexpr int kBlockDoubles = 56;    // per-edge block: M (7x7 row-major) + v (7)
+
+// device-resident solver state (ints)
+enum StateSlot { kDone = 0, kIters = 1, kFailCount = 2, kFailNow = 3, kBadEdges = 4, kConverged = 5, kStateInts = 8 };
+
+// Edge record produced once per solve by the packing pre-pass (iteration-invariant part of the per-pixel work):
+//   idx >= 0 : index of the matched pixel in frame i, all pose-independent gates passed
+//              (valid_match & q > Q_thresh & c_i > C_thresh & c_j > C_thresh, gn_kernels.cu:953-957)
+//   idx <  0 : pixel contributes exactly zero (the reference multiplies it by a zero weight, :963-964)
+//   sq       : sqrtf(q)
+struct __align__(8) EdgeRec {
+  int idx;
+  float sq;
+};
+
+struct GnLayout {
+  int num_kf, num_pts, num_edges, n_free, n, ld, nblk, tiles;
+  size_t off_xc, off_rec, off_ie, off_je, off_io, off_jo, off_partial, off_blocks, off_inc_off, off_inc_list, off_sys,
+      off_lfac, off_dx, off_state, off_uniq_flag, off_all, off_K, total;
+};
+
+GnLayout gn_layout(int num_kf, int num_pts, int num_edges, int num_all_edges);
+
+struct GnWs {
+  GnLayout L;
+  char* base;
+  float4* xc() const { return (float4*)(base + L.off_xc); }
+  EdgeRec* rec() const { return (EdgeRec*)(base + L.off_rec); }
+  int* ie() const { return (int*)(base + L.off_ie); }
+  int* je() const { return (int*)(base + L.off_je); }
+  float* partial() const { return (float*)(base + L.off_partial); }
+  double* blocks() const { return (double*)(base + L.off_blocks); }
+  int* inc_off() const { return (int*)(base + L.off_inc_off); }
+  int* inc_list() const { return (int*)(base + L.off_inc_list); }
+  double* sys() const { return (double*)(base + L.off_sys); }
+  double* lfac() const { return (double*)(base + L.off_lfac); }
+  float* dx() const { return (float*)(base + L.off_dx); }
+  int* state() const { return (int*)(base + L.off_state); }
+  int* uniq_flag() const { return (int*)(base + L.off_uniq_flag); }
+  long long* all_ids() const { return (long long*)(base + L.off_all); }
+  float* Kdev() const { return (float*)(base + L.off_K); }
+};
+
+// gn_hessian.cu
+int launch_pack_points(const GnWs& ws, const float* Xs, const float* Cs, cudaStream_t st);
+int launch_pack_edges(const GnWs& ws, const m3r_gn_params& p, const float* Cs, const int64_t* idx, const uint8_t* valid,
+                      const float* Q, cudaStream_t st);
+int launch_hessian(const GnWs& ws, const m3r_gn_params& p, const float* Twc, cudaStream_t st);
+int launch_finalize_edges(const GnWs& ws, const float* Twc, cudaStream_t st);
+int launch_export_blocks(const GnWs& ws, float* Hs, float* gs, cudaStream_t st);
+
+// gn_solve.cu
+int launch_index_prep(const GnWs& ws, const int64_t* local_ii, const int64_t* local_jj, const int64_t* all_ii,
+                      const int64_t* all_jj, int num_all_edges, cudaStream_t st);
+int launch_direct_edge_index(const GnWs& ws, const int64_t* ii_edge, const int64_t* jj_edge, cudaStream_t st);
+int launch_assemble(const GnWs& ws, cudaStream_t st);
+int launch_cholesky(const GnWs& ws, cudaStream_t st);
+int launch_backsolve_retract(const GnWs& ws, float* Twc, float delta_thresh, cudaStream_t st);
+int launch_pose_retr(float* poses, const float* dx, int num_poses, int num_fix, cudaStream_t st);
+
+}  // namespace m3r

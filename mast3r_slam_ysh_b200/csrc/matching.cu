@@ -1,0 +1,355 @@
+// iter_proj and refine_matches for sm_100a.
+//
+// Replaces the reference's matching_kernels.cu (iter_proj_kernel :119-275, refine_matches_kernel :25-81) behind
+// the C ABI of include/m3r_backends.h.  Written from the behaviour documented in SURVEY.md section 8(a):
+//   * one thread per query point, flat 1-D grid over (batch x points) with a bounds guard (the reference uses
+//     16-thread blocks without a guard),
+//   * read-only (LDG.NC) loads so the ray image / descriptor map stay L1-resident across neighbouring queries,
+//   * `converged` kept in a register and stored once (the reference stores it every LM iteration),
+//   * fp16 scores use the non-contracting __hmul2_rn / __hadd_rn intrinsics: each product and each partial sum is
+//     rounded to fp16, which is bit-identical to the reference's c10::Half arithmetic (fp32 op + round to fp16)
+//     because a product of two fp16 values is exact in fp32 and fp32->fp16 double rounding of a two-term sum
+//     cannot change the result.
+#include <cuda_fp16.h>
+#include <float.h>
+
+#include "m3r_common.cuh"
+
+namespace m3r {
+
+// =================================================================================================== iter_proj
+// 9-channel bilinear sample; weights follow the reference's "opposite area" naming (matching_kernels.cu:161-170):
+//   w11 = du*dv multiplies pixel (v+1,u+1), w12 = (1-du)*dv -> (v+1,u), w21 = du*(1-dv) -> (v,u+1), w22 -> (v,u).
+struct BilerpW {
+  float w11, w12, w21, w22;
+  int off22;  // element offset of pixel (v11,u11) channel 0 inside the image
+};
+
+template <bool kMirrorFp64>
+__device__ __forceinline__ BilerpW bilerp_setup(float u, float v, int w) {
+  BilerpW B;
+  const int u11 = static_cast<int>(floorf(u));
+  const int v11 = static_cast<int>(floorf(v));
+  const float du = u - static_cast<float>(u11);
+  const float dv = v - static_cast<float>(v11);
+  B.w11 = du * dv;
+  if (kMirrorFp64) {
+    // the reference evaluates (1.0-du)*dv etc. in double and rounds once (matching_kernels.cu:162-164)
+    B.w12 = (float)((1.0 - (double)du) * (double)dv);
+    B.w21 = (float)((double)du * (1.0 - (double)dv));
+    B.w22 = (float)((1.0 - (double)du) * (1.0 - (double)dv));
+  } else {
+    const float cu = 1.0f - du, cv = 1.0f - dv;
+    B.w12 = cu * dv;
+    B.w21 = du * cv;
+    B.w22 = cu * cv;
+  }
+  B.off22 = (v11 * w + u11) * 9;
+  return B;
+}
+
+template <bool kMirrorFp64>
+__device__ __forceinline__ float inv_norm3(float x, float y, float z, float& nrm) {
+  nrm = sqrtf(x * x + y * y + z * z);
+  if (kMirrorFp64) return (float)(1.0 / (double)nrm);  // matching_kernels.cu:187
+  return 1.0f / nrm;
+}
+
+template <bool kMirrorFp64>
+__global__ void __launch_bounds__(128) iter_proj_kernel(const float* __restrict__ rays, const float* __restrict__ pts,
+                                                        const float* __restrict__ p_init, float* __restrict__ p_new,
+                                                        uint8_t* __restrict__ converged, long long total, int n, int h,
+                                                        int w, int max_iter, float lambda_init, float cost_thresh) {
+  const long long gid = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (gid >= total) return;
+  const int b = (int)(gid / n);
+  const float* __restrict__ img = rays + (size_t)b * h * w * 9;
+  const int row = w * 9;
+
+  const float2 p0 = __ldg(reinterpret_cast<const float2*>(p_init) + gid);
+  float u = fminf(fmaxf(p0.x, 1.0f), (float)(w - 2));
+  float v = fminf(fmaxf(p0.y, 1.0f), (float)(h - 2));
+  const float tx = __ldg(pts + gid * 3 + 0), ty = __ldg(pts + gid * 3 + 1), tz = __ldg(pts + gid * 3 + 2);
+
+  float lambda = lambda_init;
+  bool conv = false;
+  for (int it = 0; it < max_iter; it++) {
+    BilerpW B = bilerp_setup<kMirrorFp64>(u, v, w);
+    const float* r22 = img + B.off22;  // (v, u)
+    const float* r21 = r22 + 9;        // (v, u+1)
+    const float* r12 = r22 + row;      // (v+1, u)
+    const float* r11 = r12 + 9;        // (v+1, u+1)
+    float s[9];
+#pragma unroll
+    for (int j = 0; j < 9; j++)
+      s[j] = B.w11 * __ldg(r11 + j) + B.w12 * __ldg(r12 + j) + B.w21 * __ldg(r21 + j) + B.w22 * __ldg(r22 + j);
+    float nrm;
+    float inv = inv_norm3<kMirrorFp64>(s[0], s[1], s[2], nrm);
+    const float e0 = s[0] * inv - tx, e1 = s[1] * inv - ty, e2 = s[2] * inv - tz;
+    const float cost = e0 * e0 + e1 * e1 + e2 * e2;
+    float A00 = s[3] * s[3] + s[4] * s[4] + s[5] * s[5];
+    const float A01 = s[3] * s[6] + s[4] * s[7] + s[5] * s[8];
+    float A11 = s[6] * s[6] + s[7] * s[7] + s[8] * s[8];
+    const float b0 = -(e0 * s[3] + e1 * s[4] + e2 * s[5]);
+    const float b1 = -(e0 * s[6] + e1 * s[7] + e2 * s[8]);
+    A00 += lambda;
+    A11 += lambda;
+    const float det = A00 * A11 - A01 * A01;
+    const float det_inv = kMirrorFp64 ? (float)(1.0 / (double)det) : 1.0f / det;
+    const float delta_u = det_inv * (A11 * b0 - A01 * b1);
+    const float delta_v = det_inv * (-A01 * b0 + A00 * b1);
+    const float u_new = fminf(fmaxf(u + delta_u, 1.0f), (float)(w - 2));
+    const float v_new = fminf(fmaxf(v + delta_v, 1.0f), (float)(h - 2));
+
+    B = bilerp_setup<kMirrorFp64>(u_new, v_new, w);
+    r22 = img + B.off22;
+    r21 = r22 + 9;
+    r12 = r22 + row;
+    r11 = r12 + 9;
+    float t[3];
+#pragma unroll
+    for (int j = 0; j < 3; j++)
+      t[j] = B.w11 * __ldg(r11 + j) + B.w12 * __ldg(r12 + j) + B.w21 * __ldg(r21 + j) + B.w22 * __ldg(r22 + j);
+    inv = inv_norm3<kMirrorFp64>(t[0], t[1], t[2], nrm);
+    const float f0 = t[0] * inv - tx, f1 = t[1] * inv - ty, f2 = t[2] * inv - tz;
+    const float new_cost = f0 * f0 + f1 * f1 + f2 * f2;
+    if (new_cost < cost) {
+      u = u_new;
+      v = v_new;
+      lambda = kMirrorFp64 ? (float)((double)lambda * 0.1) : lambda * 0.1f;
+      conv = new_cost < cost_thresh;
+    } else {
+      lambda = kMirrorFp64 ? (float)((double)lambda * 10.0) : lambda * 10.0f;
+      conv = cost < cost_thresh;
+    }
+  }
+  reinterpret_cast<float2*>(p_new)[gid] = make_float2(u, v);
+  converged[gid] = conv ? 1 : 0;
+}
+
+// ============================================================================================== refine_matches
+// fp16, compile-time descriptor length (multiple of 8 halves = 16 bytes so rows are uint4-aligned).
+template <int FDIM>
+__global__ void __launch_bounds__(128) refine_matches_f16_kernel(const uint4* __restrict__ D11,
+                                                                 const uint4* __restrict__ D21,
+                                                                 const longlong2* __restrict__ p1,
+                                                                 longlong2* __restrict__ p1_new, long long total,
+                                                                 int n, int h, int w, int radius, int dilation_max) {
+  constexpr int NV = FDIM / 8;  // uint4 per descriptor
+  const long long gid = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (gid >= total) return;
+  const int b = (int)(gid / n);
+  const longlong2 p = p1[gid];
+  // coordinates far outside any image can never produce an in-image candidate: result == input
+  const long long lim = 1LL << 29;
+  if (p.x < -lim || p.x > lim || p.y < -lim || p.y > lim) {
+    p1_new[gid] = p;
+    return;
+  }
+  __half2 q[NV * 4];
+#pragma unroll
+  for (int i = 0; i < NV; i++) {
+    const uint4 t = __ldg(D21 + gid * NV + i);
+    q[4 * i + 0] = *reinterpret_cast<const __half2*>(&t.x);
+    q[4 * i + 1] = *reinterpret_cast<const __half2*>(&t.y);
+    q[4 * i + 2] = *reinterpret_cast<const __half2*>(&t.z);
+    q[4 * i + 3] = *reinterpret_cast<const __half2*>(&t.w);
+  }
+  const uint4* __restrict__ img = D11 + (size_t)b * h * w * NV;
+  int u0 = (int)p.x, v0 = (int)p.y;
+  int u_new = u0, v_new = v0;
+  float max_score = 0.0f;  // cuda::std::numeric_limits<c10::Half>::min() == Half() == +0 (matching_kernels.cu:47)
+  for (int d = dilation_max; d > 0; d--) {
+    const int rd = radius * d;
+    const int diam = 2 * rd + 1;
+    for (int i = 0; i < diam; i += d) {
+      const int u = u0 - rd + i;
+      if (u < 0 || u >= w) continue;
+      for (int j = 0; j < diam; j += d) {
+        const int v = v0 - rd + j;
+        if (v < 0 || v >= h) continue;
+        const uint4* c = img + ((size_t)v * w + u) * NV;
+        __half score = __ushort_as_half(0);
+#pragma unroll
+        for (int k = 0; k < NV; k++) {
+          const uint4 t = __ldg(c + k);
+          const __half2 a0 = *reinterpret_cast<const __half2*>(&t.x);
+          const __half2 a1 = *reinterpret_cast<const __half2*>(&t.y);
+          const __half2 a2 = *reinterpret_cast<const __half2*>(&t.z);
+          const __half2 a3 = *reinterpret_cast<const __half2*>(&t.w);
+          __half2 pr;
+          pr = __hmul2_rn(q[4 * k + 0], a0);
+          score = __hadd_rn(score, __low2half(pr));
+          score = __hadd_rn(score, __high2half(pr));
+          pr = __hmul2_rn(q[4 * k + 1], a1);
+          score = __hadd_rn(score, __low2half(pr));
+          score = __hadd_rn(score, __high2half(pr));
+          pr = __hmul2_rn(q[4 * k + 2], a2);
+          score = __hadd_rn(score, __low2half(pr));
+          score = __hadd_rn(score, __high2half(pr));
+          pr = __hmul2_rn(q[4 * k + 3], a3);
+          score = __hadd_rn(score, __low2half(pr));
+          score = __hadd_rn(score, __high2half(pr));
+        }
+        const float s = __half2float(score);
+        if (s > max_score) {
+          max_score = s;
+          u_new = u;
+          v_new = v;
+        }
+      }
+    }
+    u0 = u_new;
+    v0 = v_new;
+  }
+  p1_new[gid] = make_longlong2((long long)u_new, (long long)v_new);
+}
+
+// generic descriptor length (any fdim), scalar loads; T = __half (rounded like c10::Half) or float
+template <typename T>
+struct ScoreOps;
+template <>
+struct ScoreOps<__half> {
+  __device__ static __forceinline__ __half zero() { return __ushort_as_half(0); }
+  __device__ static __forceinline__ __half mac(__half s, __half a, __half b) {
+    return __hadd_rn(s, __hmul_rn(a, b));
+  }
+  __device__ static __forceinline__ float to_float(__half s) { return __half2float(s); }
+  __device__ static __forceinline__ float init_max() { return 0.0f; }
+};
+template <>
+struct ScoreOps<float> {
+  __device__ static __forceinline__ float zero() { return 0.0f; }
+  __device__ static __forceinline__ float mac(float s, float a, float b) { return s + a * b; }
+  __device__ static __forceinline__ float to_float(float s) { return s; }
+  __device__ static __forceinline__ float init_max() { return FLT_MIN; }  // numeric_limits<float>::min()
+};
+
+template <typename T>
+__global__ void __launch_bounds__(128) refine_matches_generic_kernel(const T* __restrict__ D11,
+                                                                     const T* __restrict__ D21,
+                                                                     const longlong2* __restrict__ p1,
+                                                                     longlong2* __restrict__ p1_new, long long total,
+                                                                     int n, int h, int w, int fdim, int radius,
+                                                                     int dilation_max) {
+  const long long gid = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (gid >= total) return;
+  const int b = (int)(gid / n);
+  const longlong2 p = p1[gid];
+  const long long lim = 1LL << 29;
+  if (p.x < -lim || p.x > lim || p.y < -lim || p.y > lim) {
+    p1_new[gid] = p;
+    return;
+  }
+  const T* __restrict__ qd = D21 + (size_t)gid * fdim;
+  const T* __restrict__ img = D11 + (size_t)b * h * w * fdim;
+  int u0 = (int)p.x, v0 = (int)p.y;
+  int u_new = u0, v_new = v0;
+  float max_score = ScoreOps<T>::init_max();
+  for (int d = dilation_max; d > 0; d--) {
+    const int rd = radius * d;
+    const int diam = 2 * rd + 1;
+    for (int i = 0; i < diam; i += d) {
+      const int u = u0 - rd + i;
+      if (u < 0 || u >= w) continue;
+      for (int j = 0; j < diam; j += d) {
+        const int v = v0 - rd + j;
+        if (v < 0 || v >= h) continue;
+        const T* c = img + ((size_t)v * w + u) * fdim;
+        T score = ScoreOps<T>::zero();
+        for (int k = 0; k < fdim; k++) score = ScoreOps<T>::mac(score, __ldg(qd + k), __ldg(c + k));
+        const float s = ScoreOps<T>::to_float(score);
+        if (s > max_score) {
+          max_score = s;
+          u_new = u;
+          v_new = v;
+        }
+      }
+    }
+    u0 = u_new;
+    v0 = v_new;
+  }
+  p1_new[gid] = make_longlong2((long long)u_new, (long long)v_new);
+}
+
+}  // namespace m3r
+
+// ======================================================================================================= C ABI
+using namespace m3r;
+
+extern "C" int m3r_iter_proj(const float* rays_img_with_grad, const float* pts_3d_norm, const float* p_init,
+                             float* p_new, uint8_t* converged, int b, int h, int w, int n, int max_iter,
+                             float lambda_init, float cost_thresh, void* stream) {
+  M3R_REQUIRE(b >= 0 && n >= 0 && h >= 0 && w >= 0 && max_iter >= 0, "iter_proj: negative size");
+  const long long total = (long long)b * n;
+  if (total == 0) return M3R_OK;
+  M3R_REQUIRE(rays_img_with_grad && pts_3d_norm && p_init && p_new && converged, "iter_proj: null pointer");
+  M3R_REQUIRE(h >= 3 && w >= 3, "iter_proj: image must be at least 3x3 (got %dx%d)", h, w);
+  M3R_REQUIRE((long long)h * w * 9 < (1LL << 31), "iter_proj: image too large for 32-bit offsets");
+  M3R_REQUIRE(((uintptr_t)p_init & 7) == 0 && ((uintptr_t)p_new & 7) == 0, "iter_proj: p_init/p_new must be 8-byte aligned");
+  cudaStream_t st = (cudaStream_t)stream;
+  const int threads = 128;
+  const unsigned blocks = (unsigned)ceil_div_ll(total, threads);
+  iter_proj_kernel<true><<<blocks, threads, 0, st>>>(rays_img_with_grad, pts_3d_norm, p_init, p_new, converged, total,
+                                                     n, h, w, max_iter, lambda_init, cost_thresh);
+  M3R_LAUNCH_CHECK();
+  return M3R_OK;
+}
+
+template <typename T>
+static int launch_refine_generic(const T* D11, const T* D21, const int64_t* p1, int64_t* p1_new, long long total, int n,
+                                 int h, int w, int fdim, int radius, int dilation_max, cudaStream_t st) {
+  const int threads = 128;
+  const unsigned blocks = (unsigned)ceil_div_ll(total, threads);
+  refine_matches_generic_kernel<T><<<blocks, threads, 0, st>>>(D11, D21, (const longlong2*)p1, (longlong2*)p1_new, total,
+                                                               n, h, w, fdim, radius, dilation_max);
+  M3R_LAUNCH_CHECK();
+  return M3R_OK;
+}
+
+static int refine_check(const void* D11, const void* D21, const void* p1, const void* p1_new, int b, int h, int w,
+                        int n, int fdim, int radius, int dilation_max) {
+  M3R_REQUIRE(b >= 0 && n >= 0 && h >= 0 && w >= 0 && fdim >= 0, "refine_matches: negative size");
+  if ((long long)b * n == 0) return 1;
+  M3R_REQUIRE(D11 && D21 && p1 && p1_new, "refine_matches: null pointer");
+  M3R_REQUIRE(radius >= 0 && dilation_max >= 0, "refine_matches: radius/dilation must be >= 0");
+  M3R_REQUIRE(((uintptr_t)p1 & 15) == 0 && ((uintptr_t)p1_new & 15) == 0, "refine_matches: p1/p1_new must be 16-byte aligned");
+  M3R_REQUIRE((long long)radius * dilation_max < (1 << 20), "refine_matches: window too large");
+  return 0;
+}
+
+extern "C" int m3r_refine_matches_f16(const uint16_t* D11, const uint16_t* D21, const int64_t* p1, int64_t* p1_new,
+                                      int b, int h, int w, int n, int fdim, int radius, int dilation_max,
+                                      void* stream) {
+  int c = refine_check(D11, D21, p1, p1_new, b, h, w, n, fdim, radius, dilation_max);
+  if (c != 0) return c < 0 ? c : M3R_OK;
+  cudaStream_t st = (cudaStream_t)stream;
+  const long long total = (long long)b * n;
+  const bool aligned = (((uintptr_t)D11 | (uintptr_t)D21) & 15) == 0;
+  if (fdim == 24 && aligned) {
+    const int threads = 128;
+    const unsigned blocks = (unsigned)ceil_div_ll(total, threads);
+    refine_matches_f16_kernel<24><<<blocks, threads, 0, st>>>((const uint4*)D11, (const uint4*)D21, (const longlong2*)p1,
+                                                              (longlong2*)p1_new, total, n, h, w, radius, dilation_max);
+    M3R_LAUNCH_CHECK();
+    return M3R_OK;
+  }
+  if (fdim == 16 && aligned) {
+    const int threads = 128;
+    const unsigned blocks = (unsigned)ceil_div_ll(total, threads);
+    refine_matches_f16_kernel<16><<<blocks, threads, 0, st>>>((const uint4*)D11, (const uint4*)D21, (const longlong2*)p1,
+                                                              (longlong2*)p1_new, total, n, h, w, radius, dilation_max);
+    M3R_LAUNCH_CHECK();
+    return M3R_OK;
+  }
+  return launch_refine_generic<__half>((const __half*)D11, (const __half*)D21, p1, p1_new, total, n, h, w, fdim, radius,
+                                       dilation_max, st);
+}
+
+extern "C" int m3r_refine_matches_f32(const float* D11, const float* D21, const int64_t* p1, int64_t* p1_new, int b,
+                                      int h, int w, int n, int fdim, int radius, int dilation_max, void* stream) {
+  int c = refine_check(D11, D21, p1, p1_new, b, h, w, n, fdim, radius, dilation_max);
+  if (c != 0) return c < 0 ? c : M3R_OK;
+  return launch_refine_generic<float>(D11, D21, p1, p1_new, (long long)b * n, n, h, w, fdim, radius, dilation_max,
+                                      (cudaStream_t)stream);
+}
