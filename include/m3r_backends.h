@@ -153,6 +153,11 @@ M3R_API int m3r_gn_edge_blocks(const m3r_gn_params* params, const float* Twc, co
                        const uint8_t* valid_match, const float* Q, int num_kf, int num_pts, int num_edges, float* Hs,
                        float* gs, void* workspace, size_t workspace_bytes, void* stream);
 
+/* Profiling hook: after m3r_gn_begin, launches ONLY the per-pixel Hessian kernel of the local edges (the dominant
+ * kernel; bench.py brackets it with CUDA events for the roofline figure).  Results land in the workspace. */
+M3R_API int m3r_gn_hessian_pass(const m3r_gn_params* params, const float* Twc, int num_kf, int num_pts, int num_local_edges,
+                        void* workspace, void* stream);
+
 /* pose_retr_kernel (gn_kernels.cu:415-453): poses (num_poses,8) in place, dx (num_poses-num_fix,7) */
 M3R_API int m3r_pose_retr(float* poses, const float* dx, int num_poses, int num_fix, void* stream);
 

@@ -170,16 +170,15 @@ extern "C" int m3r_abi_version(void) { return M3R_ABI_VERSION; }
 extern "C" const char* m3r_last_error_string(void) { return m3r::g_err; }
 extern "C" uint64_t m3r_launch_count(void) { return m3r::g_launches.load(std::memory_order_relaxed); }
 
-extern "C" size_t m3r_gn_workspace_bytes(int num_kf, int num_pts, int num_edges) {
-  if (num_kf < 0 || num_pts < 0 || num_edges < 0) return 0;
-  // the "all edges" scratch is sized for up to 8x the local edge count (8 ranks) or 4096 ids, whichever is larger
-  const long long ea = (long long)num_edges * 8 > 4096 ? (long long)num_edges * 8 : 4096;
-  return gn_layout(num_kf, num_pts, num_edges, (int)ea).total;
+// the "all ranks' edges" scratch is sized for up to 16x the local edge count (uneven 8-way splits) or 4096 ids
+static int max_all_edges(int num_edges) {
+  const long long ea = (long long)num_edges * 16 + 64 > 4096 ? (long long)num_edges * 16 + 64 : 4096;
+  return (int)ea;
 }
 
-static int max_all_edges(int num_edges) {
-  const long long ea = (long long)num_edges * 8 > 4096 ? (long long)num_edges * 8 : 4096;
-  return (int)ea;
+extern "C" size_t m3r_gn_workspace_bytes(int num_kf, int num_pts, int num_edges) {
+  if (num_kf < 0 || num_pts < 0 || num_edges < 0) return 0;
+  return gn_layout(num_kf, num_pts, num_edges, max_all_edges(num_edges)).total;
 }
 
 extern "C" int m3r_gn_begin(const m3r_gn_params* params, const float* Twc, const float* Xs, const float* Cs,
@@ -213,6 +212,17 @@ extern "C" int m3r_gn_accumulate(const m3r_gn_params* params, const float* Twc, 
       M3R_OK)
     return rc;
   return gn_accumulate_impl(ws, params, Twc, (cudaStream_t)stream);
+}
+
+extern "C" int m3r_gn_hessian_pass(const m3r_gn_params* params, const float* Twc, int num_kf, int num_pts,
+                                   int num_local_edges, void* workspace, void* stream) {
+  int rc;
+  if ((rc = check_params(params)) != M3R_OK) return rc;
+  GnWs ws;
+  if ((rc = bind_ws(&ws, num_kf, num_pts, num_local_edges, max_all_edges(num_local_edges), workspace, (size_t)-1)) !=
+      M3R_OK)
+    return rc;
+  return launch_hessian(ws, *params, Twc, (cudaStream_t)stream);
 }
 
 extern "C" double* m3r_gn_system_ptr(void* workspace, int num_kf, int num_pts, int num_local_edges) {

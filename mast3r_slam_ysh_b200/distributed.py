@@ -1,0 +1,136 @@
+"""Multi-GPU drivers (one process per GPU, torch.distributed): edge-sharded Gauss-Newton and pair-sharded matching.
+
+The reference has no multi-GPU path (no NCCL/distributed call anywhere); this is the sharding
+BASELINE.json:north_star defines: "graph edges are split across GPUs and the block Hessian is all-reduced, and batched
+keyframe-pair matching ... is split by pair".
+
+GN: every rank holds a replica of Twc/Xs/Cs and a contiguous slice of the directed edges.  Per iteration each rank
+assembles its partial dense [H | b] in fp64 (m3r_gn_accumulate), ONE all-reduce sums it over NVLink, and every rank
+runs the same deterministic fp64 Cholesky + retraction (m3r_gn_solve_retract), so pose replicas stay bit-identical
+without a broadcast.  The convergence flag lives on the device (a pure function of the replicated dx), so no rank ever
+synchronises with its host inside the loop.
+"""
+import ctypes as C
+
+import torch
+import torch.distributed as dist
+
+from . import _lib
+
+
+# ------------------------------------------------------------------------------------------------ partitioning (host)
+def partition_edges(num_graph_edges, world_size):
+    """Contiguous, balanced split of the UNDIRECTED graph edges; returns [(lo, hi)] per rank.  Both directions of a
+    graph edge go to the same rank so the two keyframes' point tiles are shared in its L2."""
+    base, rem = divmod(num_graph_edges, world_size)
+    out, lo = [], 0
+    for r in range(world_size):
+        hi = lo + base + (1 if r < rem else 0)
+        out.append((lo, hi))
+        lo = hi
+    return out
+
+
+def directed_slice(num_graph_edges, lo, hi):
+    """Indices into the two-way edge arrays of prep_two_way_edges (global_opt.py:104-110: [forward..., backward...])
+    that belong to undirected edges lo..hi-1."""
+    fwd = torch.arange(lo, hi)
+    return torch.cat((fwd, fwd + num_graph_edges))
+
+
+def partition_pairs(num_pairs, world_size):
+    return partition_edges(num_pairs, world_size)
+
+
+def allreduce_system(sys_tensor, group=None):
+    """The one collective of a GN iteration: sum of the partial [H | b] buffers (fp64)."""
+    if dist.is_available() and dist.is_initialized() and dist.get_world_size(group) > 1:
+        dist.all_reduce(sys_tensor, op=dist.ReduceOp.SUM, group=group)
+    return sys_tensor
+
+
+# ------------------------------------------------------------------------------------------------ sharded GN (device)
+class ShardedGaussNewton:
+    """Step-wise GN over the C ABI (m3r_gn_begin / accumulate / solve_retract / end)."""
+
+    def __init__(self, params, Twc, Xs, Cs, local_ii, local_jj, idx_ii2jj, valid_match, Q, all_ii, all_jj, group=None):
+        self.lib = _lib.load()
+        self.params = params
+        self.group = group
+        self.Twc = Twc
+        self.dev = Twc.device
+        self.num_kf, self.num_pts = Xs.shape[0], Xs.shape[1]
+        self.E = local_ii.shape[0]
+        self.keep = (Xs, Cs, local_ii, local_jj, idx_ii2jj, valid_match, Q, all_ii, all_jj)
+        self.wsb = self.lib.m3r_gn_workspace_bytes(self.num_kf, self.num_pts, self.E)
+        self.ws = torch.empty(self.wsb + 256, dtype=torch.uint8, device=self.dev)
+        self.ws_ptr = self.ws.data_ptr() + ((-self.ws.data_ptr()) % 256)
+        st = self._stream()
+        p = lambda t: C.c_void_p(t.data_ptr()) if t.numel() > 0 else C.c_void_p(0)
+        with torch.cuda.device(self.dev):
+            rc = self.lib.m3r_gn_begin(C.byref(params), p(Twc), p(Xs), p(Cs), p(local_ii), p(local_jj), p(idx_ii2jj),
+                                       p(valid_match), p(Q), self.num_kf, self.num_pts, self.E, p(all_ii), p(all_jj),
+                                       all_ii.shape[0], C.c_void_p(self.ws_ptr), self.wsb, st)
+        _lib.check(rc, "gn_begin")
+        # torch view of the [H | b] region of the workspace for the collective
+        cnt = self.lib.m3r_gn_system_count(self.num_kf)
+        sys_ptr = self.lib.m3r_gn_system_ptr(C.c_void_p(self.ws_ptr), self.num_kf, self.num_pts, self.E)
+        off = sys_ptr - self.ws.data_ptr()
+        self.sys = self.ws[off:off + 8 * cnt].view(torch.float64)
+
+    def _stream(self):
+        return C.c_void_p(torch.cuda.current_stream(self.dev).cuda_stream)
+
+    def hessian_pass(self):
+        with torch.cuda.device(self.dev):
+            rc = self.lib.m3r_gn_hessian_pass(C.byref(self.params), C.c_void_p(self.Twc.data_ptr()), self.num_kf,
+                                              self.num_pts, self.E, C.c_void_p(self.ws_ptr), self._stream())
+        _lib.check(rc, "gn_hessian_pass")
+
+    def iterate(self):
+        with torch.cuda.device(self.dev):
+            rc = self.lib.m3r_gn_accumulate(C.byref(self.params), C.c_void_p(self.Twc.data_ptr()), self.num_kf,
+                                            self.num_pts, self.E, C.c_void_p(self.ws_ptr), self._stream())
+            _lib.check(rc, "gn_accumulate")
+            allreduce_system(self.sys, self.group)
+            rc = self.lib.m3r_gn_solve_retract(C.byref(self.params), C.c_void_p(self.Twc.data_ptr()), self.num_kf,
+                                               self.num_pts, self.E, C.c_void_p(self.ws_ptr), self._stream())
+            _lib.check(rc, "gn_solve_retract")
+
+    def finish(self):
+        dx = torch.zeros((max(self.num_kf - 1, 0), 7), dtype=torch.float32, device=self.dev)
+        info = torch.zeros(4, dtype=torch.int32, device=self.dev)
+        with torch.cuda.device(self.dev):
+            rc = self.lib.m3r_gn_end(self.num_kf, self.num_pts, self.E, C.c_void_p(dx.data_ptr()) if dx.numel() else None,
+                                     C.c_void_p(info.data_ptr()), C.c_void_p(self.ws_ptr), self._stream())
+        _lib.check(rc, "gn_end")
+        return dx, info
+
+
+def gauss_newton_rays_sharded(Twc, Xs, Cs, local_ii, local_jj, idx_ii2jj, valid_match, Q, all_ii, all_jj, sigma_ray,
+                              sigma_dist, C_thresh, Q_thresh, max_iter, delta_thresh, group=None):
+    """gauss_newton_rays (gn.cpp:28-52) with the directed edges sharded over the ranks of `group`.
+    local_* are this rank's edges, all_ii/all_jj the concatenation over ranks (keyframe numbering must agree)."""
+    params = _lib.GnParams(_lib.M3R_GN_RAYS, _lib.M3R_ROBUST_HUBER, float(sigma_ray), float(sigma_dist), float(C_thresh),
+                           float(Q_thresh), None, 0, 0, 0, 0.0, int(max_iter), float(delta_thresh))
+    s = ShardedGaussNewton(params, Twc, Xs, Cs, local_ii, local_jj, idx_ii2jj, valid_match, Q, all_ii, all_jj, group)
+    for _ in range(int(max_iter)):
+        s.iterate()
+    dx, info = s.finish()
+    return [dx], info
+
+
+# ------------------------------------------------------------------------------------------------ sharded matching
+def match_pairs_sharded(rays_img_with_grad, pts_3d_norm, p_init, D11, D21, matching_cfg, group=None, gather=False):
+    """iter_proj + refine_matches on THIS rank's pairs (split by pair, no data-path collective).  With gather=True the
+    per-rank results are all-gathered (equal pair counts per rank required)."""
+    from . import backends as be
+    p, conv = be.iter_proj(rays_img_with_grad, pts_3d_norm, p_init, matching_cfg["max_iter"],
+                           matching_cfg["lambda_init"], matching_cfg["convergence_thresh"])
+    (p1,) = be.refine_matches(D11, D21, p.long(), matching_cfg["radius"], matching_cfg["dilation_max"])
+    if gather and dist.is_initialized() and dist.get_world_size(group) > 1:
+        ws = dist.get_world_size(group)
+        outs = [torch.empty_like(p1) for _ in range(ws)]
+        dist.all_gather(outs, p1, group=group)
+        p1 = torch.cat(outs, 0)
+    return p1, conv

@@ -1,0 +1,267 @@
+"""GPU parity tests (run with -m gpu on the B200 box).  Every call goes through the C ABI (libm3r_backends_b200.so)
+via the host mirror in mast3r_slam_ysh_b200/backends.py and is compared with (a) the committed outputs of the
+reference's own CUDA kernels (tests/golden), (b) the CPU oracle on seeded inputs, (c) size-independent properties at
+BASELINE.json's full 512x384 size."""
+import numpy as np
+import pytest
+import torch
+
+from conftest import load_golden
+from test_oracle_golden import LO, MT, _run_gn
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda:0"
+
+
+def t(x, dtype=None):
+    x = torch.from_numpy(np.ascontiguousarray(x)).to(DEV)
+    return x if dtype is None else x.to(dtype)
+
+
+# ---------------------------------------------------------------------------------------------- matching vs golden
+@pytest.mark.parametrize("name", ["match_a", "match_b"])
+def test_iter_proj_vs_reference_cuda(be, name):
+    g = load_golden(name)
+    p_new, conv = be.iter_proj(t(g["rays"]), t(g["pts"]), t(g["p_init"]), MT["max_iter"], MT["lambda_init"],
+                               MT["convergence_thresh"])
+    err = (p_new.cpu().numpy() - g["p_new"])
+    assert np.abs(err).max() <= 1e-3  # north_star: within 1e-3 px of the reference backend
+    assert np.array_equal(conv.cpu().numpy(), g["converged"].astype(bool))
+    assert conv.dtype == torch.bool and p_new.dtype == torch.float32
+
+
+@pytest.mark.parametrize("name", ["match_a", "match_b"])
+def test_refine_matches_bit_exact_vs_reference_cuda(be, name):
+    g = load_golden(name)
+    D11, D21 = t(g["D11"].view(np.float16)), t(g["D21"].view(np.float16))
+    (p1n,) = be.refine_matches(D11, D21, t(g["p1"]), MT["radius"], MT["dilation_max"])
+    assert np.array_equal(p1n.cpu().numpy(), g["p1_new"])
+    (p1nb,) = be.refine_matches(D11, D21, t(g["p1_b"]), 2, 3)
+    assert np.array_equal(p1nb.cpu().numpy(), g["p1_new_b"])
+
+
+def test_refine_matches_generic_fdim_and_f32(be, orc):
+    rng = np.random.default_rng(3)
+    b, h, w = 2, 19, 23
+    for fdim in (8, 16, 20, 24):
+        D11 = rng.standard_normal((b, h, w, fdim)).astype(np.float16)
+        D21 = rng.standard_normal((b, h * w, fdim)).astype(np.float16)
+        p1 = np.stack([rng.integers(-3, w + 3, (b, h * w)), rng.integers(-3, h + 3, (b, h * w))], -1).astype(np.int64)
+        (got,) = be.refine_matches(t(D11), t(D21), t(p1), 3, 5)
+        (want,) = orc.refine_matches(D11, D21, p1, 3, 5)
+        assert np.array_equal(got.cpu().numpy(), want), fdim
+    D11 = rng.standard_normal((b, h, w, 12)).astype(np.float32)
+    D21 = rng.standard_normal((b, h * w, 12)).astype(np.float32)
+    p1 = np.stack([rng.integers(0, w, (b, h * w)), rng.integers(0, h, (b, h * w))], -1).astype(np.int64)
+    (got,) = be.refine_matches(t(D11), t(D21), t(p1), 2, 2)
+    (want,) = orc.refine_matches(D11, D21, p1, 2, 2)
+    assert (got.cpu().numpy() != want).any(-1).mean() < 1e-3  # fp32 scores: ties only through FMA contraction
+
+
+def test_refine_matches_edge_cases(be):
+    # non-positive scores never win (max_score starts at +0): all-zero descriptors keep p1; far-out p1 unchanged
+    D11 = torch.zeros(1, 8, 8, 24, dtype=torch.float16, device=DEV)
+    D21 = torch.zeros(1, 64, 24, dtype=torch.float16, device=DEV)
+    p1 = torch.randint(0, 8, (1, 64, 2), device=DEV)
+    p1[0, 0] = torch.tensor([10 ** 12, -5])
+    (out,) = be.refine_matches(D11, D21, p1, 3, 5)
+    assert torch.equal(out, p1)
+    (out,) = be.refine_matches(D11[:, :, :, :], D21[:, :0], p1[:, :0], 3, 5)  # empty query set
+    assert out.shape == (1, 0, 2)
+    (out,) = be.refine_matches(D11, D21, p1, 0, 5)  # radius 0: window is the centre only
+    assert torch.equal(out, p1)
+
+
+def test_iter_proj_edge_cases(be):
+    rays = torch.nn.functional.normalize(torch.randn(1, 6, 7, 9, device=DEV), dim=-1).contiguous()
+    pts = torch.nn.functional.normalize(torch.randn(1, 5, 3, device=DEV), dim=-1)
+    p0 = torch.tensor([[[-50.0, 2.0], [100.0, 100.0], [3.2, 2.7], [0.0, 0.0], [5.0, 4.0]]], device=DEV)
+    p_new, conv = be.iter_proj(rays, pts, p0, 0, 1e-8, 1e-6)  # max_iter = 0: clamped init, never converged
+    want = torch.stack((p0[..., 0].clamp(1, 5), p0[..., 1].clamp(1, 4)), -1)
+    assert torch.equal(p_new, want) and not conv.any()
+    p_new, conv = be.iter_proj(rays, pts[:, :0], p0[:, :0], 10, 1e-8, 1e-6)
+    assert p_new.shape == (1, 0, 2) and conv.shape == (1, 0)
+    p_new, _ = be.iter_proj(rays, pts, p0, 10, 1e-8, 1e-6)
+    assert (p_new[..., 0] >= 1).all() and (p_new[..., 0] <= 5).all() and (p_new[..., 1] >= 1).all() and (p_new[..., 1] <= 4).all()
+
+
+def test_matching_vs_oracle_seeded(be, orc):
+    from mast3r_slam_ysh_b200 import synthetic as syn
+    m = syn.make_match_problem(3, 60, 83, seed=77, yaw_step_deg=7.0, warm_start=True)
+    rays, pts, p0 = m["rays_img_with_grad"], m["pts_3d_norm"], m["p_init"]
+    p_new, conv = be.iter_proj(rays.to(DEV), pts.to(DEV), p0.to(DEV), 10, 1e-8, 1e-6)
+    p_o, c_o = orc.iter_proj(rays.numpy(), pts.numpy(), p0.numpy(), 10, 1e-8, 1e-6)
+    err = np.abs(p_new.cpu().numpy() - p_o).max(-1)
+    assert (err <= 1e-3).mean() >= 0.995  # the oracle is unfused CPU arithmetic; see test_oracle_golden.py
+    p1 = p_new.long()
+    D11, D21 = m["D11"].half(), m["D21"].view(3, -1, 24).half()
+    (got,) = be.refine_matches(D11.to(DEV), D21.to(DEV), p1, 3, 5)
+    (want,) = orc.refine_matches(D11.numpy(), D21.numpy(), p1.cpu().numpy(), 3, 5)
+    assert np.array_equal(got.cpu().numpy(), want)
+
+
+# ---------------------------------------------------------------------------------------------- Gauss-Newton
+class _Be:
+    """adapter so _run_gn can drive the torch API with the numpy fixtures"""
+
+    def __init__(self, be):
+        self.be = be
+
+    def _wrap(self, fn):
+        def call(T, *args, **kw):
+            targs = [t(a) if isinstance(a, np.ndarray) else a for a in args]
+            self.T = t(T)
+            out = fn(self.T, *targs, **kw)
+            torch.cuda.synchronize()
+            T[...] = self.T.cpu().numpy()
+            return [o.cpu().numpy() for o in out], None
+        return call
+
+    def __getattr__(self, name):
+        return self._wrap(getattr(self.be, name))
+
+
+@pytest.mark.parametrize("kind", ["rays", "calib", "points"])
+def test_gauss_newton_vs_reference_cuda(be, kind):
+    g = load_golden("gn_" + kind)
+    T = g["Twc"].copy()
+    (dx1,), _ = _run_gn(_Be(be), kind, g, T, 1)
+    rel = np.linalg.norm(dx1 - g["dx1"]) / np.linalg.norm(g["dx1"])
+    assert rel <= 1e-4, rel  # north_star: GN pose updates within 1e-4 relative
+    assert np.linalg.norm(T - g["T1"]) / np.linalg.norm(g["T1"]) <= 1e-5
+    T = g["Twc"].copy()
+    _run_gn(_Be(be), kind, g, T, 5)
+    assert np.linalg.norm(T - g["T5"]) / np.linalg.norm(g["T5"]) <= 1e-4
+    assert np.array_equal(T[0], g["Twc"][0])
+
+
+@pytest.mark.parametrize("kind", ["rays", "calib", "points"])
+def test_edge_blocks_vs_oracle_fp64(be, orc, kind):
+    g = load_golden("gn_" + kind)
+    uniq, ie, je = orc.index_prep(g["ii"], g["jj"])
+    idx = g["idx"].astype(np.int64)
+    kw = dict(rays=dict(sigma_ray=LO["sigma_ray"], sigma_dist=LO["sigma_dist"]),
+              points=dict(sigma_point=LO["sigma_point"]),
+              calib=dict(sigma_pixel=LO["sigma_pixel"], sigma_depth=LO["sigma_depth"], height=int(g["h"]),
+                         width=int(g["w"]), pixel_border=LO["pixel_border"], z_eps=LO["depth_eps"]))[kind]
+    okind = dict(rays=orc.KIND_RAYS, calib=orc.KIND_CALIB, points=orc.KIND_POINTS)[kind]
+    okw = dict(kw, K=g["K"]) if kind == "calib" else kw
+    for robust, rname in ((0, "huber"), (1, "tukey")):
+        Hs_o, gs_o = orc.gn_edge_blocks(okind, g["Twc"], g["Xs"], g["Cs"], ie, je, idx, g["valid"], g["Q"], LO["C_conf"],
+                                        LO["Q_conf"], robust=robust, **okw)
+        gkw = dict(kw, K=t(g["K"])) if kind == "calib" else kw
+        Hs, gs = be.gn_edge_blocks(kind, t(g["Twc"]), t(g["Xs"]), t(g["Cs"]), t(ie), t(je), t(idx), t(g["valid"]),
+                                   t(g["Q"]), LO["C_conf"], LO["Q_conf"], robust=rname, **gkw)
+        assert np.linalg.norm(Hs.cpu().numpy() - Hs_o) / np.linalg.norm(Hs_o) <= 2e-5, (kind, rname)
+        assert np.linalg.norm(gs.cpu().numpy() - gs_o) / np.linalg.norm(gs_o) <= 2e-5, (kind, rname)
+        # structure of the reference's output: H_ii = H_jj = -H_ij = -H_ji, g_i = -g_j (gn_kernels.cu:1000)
+        assert torch.equal(Hs[0], Hs[3]) and torch.equal(Hs[1], -Hs[0]) and torch.equal(gs[0], -gs[1])
+
+
+def test_gn_failure_and_degenerate_inputs(be):
+    g = load_golden("gn_rays")
+    idx = t(g["idx"].astype(np.int64))
+    args = lambda valid: (t(g["Xs"]), t(g["Cs"]), t(g["ii"]), t(g["jj"]), idx, valid, t(g["Q"]), LO["sigma_ray"],
+                          LO["sigma_dist"], LO["C_conf"], LO["Q_conf"])
+    # all matches invalid -> H = 0 -> factorisation fails -> dx = 0, poses untouched, loop stops (gn_kernels.cu:147-150)
+    T = t(g["Twc"])
+    (dx,), info = be.gauss_newton_rays(T, *args(torch.zeros_like(t(g["valid"]))), 4, 1e-8, return_info=True)
+    info = info.cpu().numpy()
+    assert not dx.any() and torch.equal(T, t(g["Twc"]))
+    assert info[0] == 1 and info[1] == 1 and info[2] == 1
+    # max_iter = 0: nothing happens
+    T = t(g["Twc"])
+    (dx,) = be.gauss_newton_rays(T, *args(t(g["valid"])), 0, 1e-8)
+    assert not dx.any() and torch.equal(T, t(g["Twc"]))
+    # huge delta threshold: exactly one iteration is applied, then the loop stops
+    T1, T2 = t(g["Twc"]), t(g["Twc"])
+    (_,), info = be.gauss_newton_rays(T1, *args(t(g["valid"])), 7, 1e9, return_info=True)
+    be.gauss_newton_rays(T2, *args(t(g["valid"])), 1, 1e-8)
+    assert info.cpu().numpy()[0] == 1 and torch.equal(T1, T2)
+    # deterministic: same inputs, same bits
+    T3 = t(g["Twc"])
+    be.gauss_newton_rays(T3, *args(t(g["valid"])), 1, 1e-8)
+    assert torch.equal(T2, T3)
+    # zero edges
+    T = t(g["Twc"])
+    e0 = torch.zeros(0, dtype=torch.int64, device=DEV)
+    (dx,) = be.gauss_newton_rays(T, t(g["Xs"]), t(g["Cs"]), e0, e0, idx[:0], t(g["valid"])[:0], t(g["Q"])[:0],
+                                 LO["sigma_ray"], LO["sigma_dist"], 0.0, 1.5, 3, 1e-8)
+    assert not dx.any() and torch.equal(T, t(g["Twc"]))
+
+
+def test_gn_medium_graph_vs_oracle(be, orc):
+    """37 keyframes -> system dimension 252 (8 Cholesky panels incl. a partial one), ragged pixel count."""
+    from mast3r_slam_ysh_b200 import synthetic as syn
+    nkf, h, w = 37, 21, 29
+    g = syn.make_gn_problem(nkf, h, w, syn.ring_edges(nkf, 3), seed=9, yaw_step_deg=6.0)
+    args = [g[k] for k in ("Xs", "Cs", "ii", "jj", "idx_ii2jj", "valid_match", "Q")]
+    P = (LO["sigma_ray"], LO["sigma_dist"], LO["C_conf"], LO["Q_conf"])
+    T_o = g["Twc"].numpy().copy()
+    (dx_o,), _ = orc.gauss_newton_rays(T_o, *[a.numpy() for a in args], *P, 2, 1e-8)
+    T = g["Twc"].to(DEV)
+    (dx,) = be.gauss_newton_rays(T, *[a.to(DEV) for a in args], *P, 2, 1e-8)
+    assert np.linalg.norm(T.cpu().numpy() - T_o) / np.linalg.norm(T_o) <= 1e-5
+    assert np.linalg.norm(dx.cpu().numpy() - dx_o) / np.linalg.norm(dx_o) <= 2e-3  # 2nd-iteration dx is tiny
+
+
+def test_pose_retr_vs_oracle(be, orc):
+    g = torch.Generator().manual_seed(5)
+    poses = torch.randn(9, 8, generator=g)
+    poses[:, 3:7] = torch.nn.functional.normalize(poses[:, 3:7], dim=-1)
+    poses[:, 7] = poses[:, 7].abs() + 0.5
+    dx = 0.1 * torch.randn(8, 7, generator=g)
+    dx[0, 3:] = 0          # theta = 0, sigma = 0
+    dx[1, 3:6] = 1e-8      # small-angle branch (gn_kernels.cu:306, 352, 361)
+    dx[2, 6] = 1e-9        # small-sigma branch
+    dx[3, 3:6] = 0
+    dx[4] = 0
+    want = orc.pose_retr(poses.numpy(), dx.numpy())
+    got = be.pose_retr(poses.to(DEV).clone(), dx.to(DEV))
+    assert np.allclose(got.cpu().numpy(), want, rtol=2e-6, atol=2e-7)
+    assert np.array_equal(got.cpu().numpy()[0], poses.numpy()[0])
+
+
+# ---------------------------------------------------------------------------------------------- full-size properties
+def test_full_size_properties(be):
+    """512x384 (BASELINE.json): properties that do not need the oracle."""
+    from mast3r_slam_ysh_b200 import synthetic as syn
+    h, w = 384, 512
+    m = syn.make_match_problem(1, h, w, seed=1235, device=DEV)
+    rays, pts, p0 = m["rays_img_with_grad"], m["pts_3d_norm"], m["p_init"]
+    p_new, conv = be.iter_proj(rays, pts, p0, 10, 1e-8, 1e-6)
+    assert (p_new[..., 0] >= 1).all() and (p_new[..., 0] <= w - 2).all() and (p_new[..., 1] >= 1).all() and (p_new[..., 1] <= h - 2).all()
+    # converged points really point along the target ray: bilinear ray at p_new matches pts within sqrt(cost_thresh)
+    u, v = p_new[0, :, 0], p_new[0, :, 1]
+    u0, v0 = u.floor().long(), v.floor().long()
+    du, dv = (u - u0)[:, None], (v - v0)[:, None]
+    img = rays[0, :, :, :3]
+    r = (1 - du) * (1 - dv) * img[v0, u0] + du * (1 - dv) * img[v0, u0 + 1] + (1 - du) * dv * img[v0 + 1, u0] + du * dv * img[v0 + 1, u0 + 1]
+    r = torch.nn.functional.normalize(r, dim=-1)
+    cost = ((r - pts[0]) ** 2).sum(-1)
+    assert (cost[conv[0]] < 1.5e-6).all() and conv.float().mean() > 0.05
+    # iter_proj restarted from its own converged answer stays put (fixed point)
+    p2, _ = be.iter_proj(rays, pts, p_new, 10, 1e-8, 1e-6)
+    assert ((p2 - p_new).abs().amax(-1)[conv] < 2e-2).all()
+    # refine_matches: output inside the image, within the reachable window, and never lowers the (fp32) score
+    p1 = p_new.long()
+    D11, D21 = m["D11"].half(), m["D21"].view(1, h * w, -1).half()
+    (q,) = be.refine_matches(D11, D21, p1, 3, 5)
+    assert (q[..., 0] >= 0).all() and (q[..., 0] < w).all() and (q[..., 1] >= 0).all() and (q[..., 1] < h).all()
+    assert ((q - p1).abs().amax(-1) <= 3 * (5 + 4 + 3 + 2 + 1)).all()
+    s_old = (D11[0, p1[0, :, 1], p1[0, :, 0]].float() * D21[0].float()).sum(-1)
+    s_new = (D11[0, q[0, :, 1], q[0, :, 0]].float() * D21[0].float()).sum(-1)
+    assert (s_new >= s_old - 2e-2).all()
+    # GN on a 6-keyframe full-size graph: converges towards the ground truth, gauge keyframe fixed, deterministic
+    g = syn.make_gn_problem(6, h, w, syn.ring_edges(6, 2, wrap=False), seed=1236, device=DEV, yaw_step_deg=10.0)
+    args = [g[k] for k in ("Xs", "Cs", "ii", "jj", "idx_ii2jj", "valid_match", "Q")]
+    P = (LO["sigma_ray"], LO["sigma_dist"], LO["C_conf"], LO["Q_conf"], 10, 1e-8)
+    T = g["Twc"].clone()
+    (dx,), info = be.gauss_newton_rays(T, *args, *P, return_info=True)
+    assert torch.equal(T[0], g["Twc"][0])
+    e0 = (g["Twc"] - g["Twc_gt"]).abs().max().item()
+    e1 = (T - g["Twc_gt"]).abs().max().item()
+    assert e1 < 0.05 * e0 and info.cpu().numpy()[2] == 0
+    T2 = g["Twc"].clone()
+    be.gauss_newton_rays(T2, *args, *P)
+    assert torch.equal(T, T2)
