@@ -1,0 +1,383 @@
+#!/usr/bin/env python
+"""bench.py -- GN solve ms/iter (+ iter_proj / refine_matches Mpix/s) at 512x384 on N B200s.
+
+Contract (one JSON line on rank 0):
+  metric  gn_solve_ms_per_iter: one "step" = one gauss_newton_rays solve (max_iter = 10 GN iterations: Hessian
+          assembly + reduction + fp64 Cholesky + retraction + convergence flag) of BASELINE.json configs[2]
+          (32 keyframes per GPU, 8 edges/kf -> 512 directed edges per GPU, dense 512x384 points), value = step time /
+          iterations executed.  N > 1: weak scaling -- 32*N keyframes, 512*N directed edges sharded by edge, one
+          NCCL all-reduce of the dense fp64 [H | b] per iteration, replicated Cholesky (at N = 8 this is the
+          256-keyframe graph of configs[4]).
+  e2e     same metric through the reference-facing Python call with pinned HOST buffers: H2D of every input and D2H of
+          the poses/dx inside the timed region.
+  roofline  the per-pixel Hessian kernel timed alone with CUDA events; algorithmic bytes = 45 B per pixel per directed
+          edge against MEASURED_PEAKS.json hbm_gbs.
+  cpu_baseline  the CPU oracle port (oracle/m3r_oracle.c, OpenMP) on a bounded sample of the same workload.
+  --impl reference  times that CPU port as the reference arm (the reference's GN kernels are CUDA-only; its CPU code
+          for this math is the tracker solve, reported as extra.cpu_tracker).
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+H, W = 384, 512
+N_PIX = H * W
+KF_PER_GPU, SPAN, GN_ITERS = 32, 8, 10
+ALGO_BYTES_PER_PIXEL_EDGE = 45  # valid 1 + idx 8 + X_j 12 + X_i 12 + Q 4 + C_i 4 + C_j 4
+ITER_PROJ_BYTES_PER_QUERY = 65  # 36 ray image + 12 target + 8 init + 8 out + 1 flag
+
+
+def measured_peak():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        return float(json.load(open(p))["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+class ClockSampler(threading.Thread):
+    Q = "clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown," \
+        "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+
+    def __init__(self, index=0):
+        super().__init__(daemon=True)
+        self.index, self.rows, self.stop_flag = index, [], False
+
+    def run(self):
+        while not self.stop_flag:
+            try:
+                out = subprocess.run(["nvidia-smi", f"--id={self.index}", f"--query-gpu={self.Q}",
+                                      "--format=csv,noheader,nounits"], capture_output=True, text=True, timeout=5).stdout
+                self.rows.append([x.strip() for x in out.strip().split(",")])
+            except Exception:
+                pass
+            time.sleep(0.1)
+
+    def summary(self):
+        self.stop_flag = True
+        sm = sorted(int(r[0]) for r in self.rows if len(r) >= 6 and r[0].isdigit())
+        mx = [int(r[1]) for r in self.rows if len(r) >= 6 and r[1].isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = [n for k, n in enumerate(names) if any(len(r) >= 6 and r[2 + k].lower().startswith("active") for r in self.rows)]
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None, "reasons": reasons,
+                "samples": len(sm)}
+
+
+def gn_params():
+    from mast3r_slam_ysh_b200 import synthetic as syn
+    lo = syn.LOCAL_OPT
+    return (lo["sigma_ray"], lo["sigma_dist"], lo["C_conf"], lo["Q_conf"], GN_ITERS, lo["delta_norm"])
+
+
+# ====================================================================================================== reference arm
+def cpu_gn_sample(target_seconds=12.0, device="cpu"):
+    """Times the CPU oracle port on a bounded sample of configs[2]: S of the 512 directed edges, ONE GN iteration of
+    edge-block evaluation (the O(E*N) part), scaled to 512 edges, plus the dense solve of the 217-dim system."""
+    import numpy as np
+    from mast3r_slam_ysh_b200 import synthetic as syn
+    from oracle import oracle as orc
+    lo = syn.LOCAL_OPT
+    cores = orc.num_threads()
+    nkf = KF_PER_GPU
+    edges = syn.ring_edges(nkf, SPAN)
+    S = max(cores, 8)
+    g = syn.make_gn_problem(nkf, H, W, edges, seed=1236, device=device, directed_subset=__import__("torch").arange(S))
+    a = [g[k].cpu().numpy() for k in ("Twc", "Xs", "Cs")]
+    ie, je = g["ii"].cpu().numpy(), g["jj"].cpu().numpy()
+    rest = [g[k].cpu().numpy() for k in ("idx_ii2jj", "valid_match", "Q")]
+
+    def one(n_edges):
+        t = time.perf_counter()
+        orc.gn_edge_blocks(orc.KIND_RAYS, *a, ie[:n_edges], je[:n_edges], rest[0][:n_edges], rest[1][:n_edges],
+                           rest[2][:n_edges], lo["C_conf"], lo["Q_conf"], accum=1, sigma_ray=lo["sigma_ray"],
+                           sigma_dist=lo["sigma_dist"])
+        return time.perf_counter() - t
+    one(cores)  # warm
+    t_s = one(S)
+    E_full = 2 * len(edges[0])
+    # dense solve part on a random SPD 217-dim system (same code path as the oracle's per-iteration solve)
+    rng = np.random.default_rng(0)
+    Hs = np.zeros((4, nkf - 1, 7, 7), np.float32)
+    Mb = rng.standard_normal((nkf - 1, 7, 7)).astype(np.float32)
+    Hs[0] = Mb @ Mb.transpose(0, 2, 1) + 7 * np.eye(7, dtype=np.float32)
+    gs = rng.standard_normal((2, nkf - 1, 7)).astype(np.float32)
+    io = np.arange(nkf - 1)
+    t = time.perf_counter()
+    orc.gn_solve(Hs, gs, io, io - 10 ** 6, nkf - 1)
+    t_solve = time.perf_counter() - t
+    ms_iter = (t_s * E_full / S + t_solve) * 1e3
+    return dict(value=ms_iter, unit="ms/iter", cores=cores, kind="port",
+                sample=f"{S} of {E_full} directed edges x {N_PIX} px, 1 GN iteration of oracle/m3r_oracle.c "
+                       f"(fp32 reference-order accumulation, OpenMP), scaled x{E_full / S:.0f}, + dense fp64 solve"), t_s
+
+
+def cpu_tracker_baseline(threads=None):
+    """configs[0]: pure-torch tracker solve (oracle/tracker_torch.py) on one synthetic 512x384 pair, host cores."""
+    import torch
+    from mast3r_slam_ysh_b200 import synthetic as syn
+    from oracle import tracker_torch as tt
+    if threads:
+        torch.set_num_threads(threads)
+    g = syn.make_gn_problem(2, H, W, ([0], [1]), seed=1234, yaw_step_deg=8.0)
+    idx = g["idx_ii2jj"][0]
+    valid = g["valid_match"][0].float() * (g["Q"][0] > 1.5).float()
+    Xf, Xk, Qk = g["Xs"][1], g["Xs"][0][idx], g["Q"][0]
+    ts, its = [], 0
+    for rep in range(4):
+        t = time.perf_counter()
+        _, _, its = tt.opt_pose_ray_dist_sim3(Xf, Xk, tt.Sim3(g["Twc"][1:2].clone()), tt.Sim3(g["Twc"][0:1].clone()), Qk, valid)
+        if rep:
+            ts.append((time.perf_counter() - t) / its)
+    ts.sort()
+    return dict(ms_per_iter=ts[len(ts) // 2] * 1e3, iters=its, threads=torch.get_num_threads(),
+                what="tracker.opt_pose_ray_dist_sim3 port, 1 pair 512x384, torch CPU")
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    vals = []
+    base = None
+    for s in range(args.warmup + args.steps):
+        base, _ = cpu_gn_sample()
+        if s >= args.warmup:
+            vals.append(base["value"])
+    v = sum(vals) / len(vals)
+    base["value"] = v
+    line = dict(impl="reference", metric="gn_solve_ms_per_iter", value=v, unit="ms/iter", n_gpus=args.gpus,
+                steps=args.steps, warmup=args.warmup, ms_per_step=v * GN_ITERS, higher_is_better=False, scaling="weak",
+                vs_baseline=None, dtype="f32 (fp64 solve)", data="synthetic",
+                config=workload_config(args.gpus), cpu_baseline=base,
+                e2e=dict(value=v, unit="ms/iter", h2d_bytes_per_step=0, d2h_bytes_per_step=0), gpu_launches=0,
+                extra=dict(cpu_tracker=cpu_tracker_baseline()))
+    print(json.dumps(line), flush=True)
+
+
+def workload_config(n):
+    return dict(workload="FactorGraph.solve_GN_rays: %d keyframes, 8 edges/kf -> %d directed edges, dense 512x384 points, "
+                         "max_iter 10 (BASELINE.json configs[2]%s)" % (KF_PER_GPU * n, 2 * KF_PER_GPU * SPAN * n,
+                                                                      "" if n == 1 else ", weak-scaled; N=8 == configs[4] size"),
+                keyframes=KF_PER_GPU * n, directed_edges=2 * KF_PER_GPU * SPAN * n, pixels=N_PIX, gn_iters=GN_ITERS,
+                parallelism="edge-sharded x%d, all-reduce [H|b] fp64, replicated Cholesky" % n,
+                l2_policy="inputs (>1.3 GB per GPU) exceed the 126 MB L2; no explicit flush")
+
+
+# ====================================================================================================== our arm (GPU)
+def run_ours(args):
+    import torch
+    import torch.distributed as dist
+    from mast3r_slam_ysh_b200 import _lib, backends as be, distributed as md, synthetic as syn
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device -- the B200 backend has no CPU fallback")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    lib = _lib.load()
+    P = gn_params()
+    nkf = KF_PER_GPU * world
+    edges = syn.ring_edges(nkf, SPAN)
+    n_graph = len(edges[0])
+    lo_e, hi_e = md.partition_edges(n_graph, world)[rank]
+    sel = md.directed_slice(n_graph, lo_e, hi_e)
+    g = syn.make_gn_problem(nkf, H, W, edges, seed=1236, device=dev, directed_subset=sel if world > 1 else None)
+    Xs, Cs, ii, jj, idx, vm, Q = (g[k] for k in ("Xs", "Cs", "ii", "jj", "idx_ii2jj", "valid_match", "Q"))
+    T0 = g["Twc"].clone()
+    T = T0.clone()
+    E_local, E_total = int(ii.numel()), 2 * n_graph
+    torch.cuda.synchronize()
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    info_keep = {}
+
+    def step():
+        T.copy_(T0)
+        if world == 1:
+            (dx,), info = be.gauss_newton_rays(T, Xs, Cs, ii, jj, idx, vm, Q, *P, return_info=True)
+        else:
+            (dx,), info = md.gauss_newton_rays_sharded(T, Xs, Cs, ii, jj, idx, vm, Q, g["all_ii"], g["all_jj"], *P)
+        info_keep["info"] = info
+        return dx
+
+    for _ in range(args.warmup):
+        step()
+    barrier()
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    l0 = lib.m3r_launch_count()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    ev0.record()
+    for _ in range(args.steps):
+        step()
+    ev1.record()
+    barrier()
+    launches = int(lib.m3r_launch_count() - l0)
+    total_ms = torch.tensor([ev0.elapsed_time(ev1)], device=dev, dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(total_ms, op=dist.ReduceOp.MAX)
+    total_ms = float(total_ms.item())
+    iters = int(info_keep["info"].cpu()[0])
+    ms_per_step = total_ms / args.steps
+    value = ms_per_step / max(iters, 1)
+
+    # ---- dominant kernel alone: per-pixel Hessian kernel over this rank's edges, CUDA events on the launch stream
+    params = _lib.GnParams(_lib.M3R_GN_RAYS, _lib.M3R_ROBUST_HUBER, P[0], P[1], P[2], P[3], None, 0, 0, 0, 0.0, GN_ITERS, P[5])
+    sh = md.ShardedGaussNewton(params, T0.clone(), Xs, Cs, ii, jj, idx, vm, Q, g["all_ii"], g["all_jj"])
+    for _ in range(3):
+        sh.hessian_pass()
+    torch.cuda.synchronize()
+    reps = 20
+    k0, k1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    k0.record()
+    for _ in range(reps):
+        sh.hessian_pass()
+    k1.record()
+    torch.cuda.synchronize()
+    hess_ms = k0.elapsed_time(k1) / reps
+    clocks = sampler.summary() if rank == 0 else None
+    peak, peak_src = measured_peak()
+    algo_bytes = ALGO_BYTES_PER_PIXEL_EDGE * N_PIX * E_local
+    achieved = algo_bytes / (hess_ms * 1e-3) / 1e9
+    del sh
+
+    # ---- e2e: pinned host buffers -> device -> solve -> poses/dx back to the host, every step
+    host_in = [x.cpu().pin_memory() for x in (T0, Xs, Cs, ii, jj, idx, vm, Q)]
+    h2d = sum(x.numel() * x.element_size() for x in host_in)
+    out_T = torch.empty_like(host_in[0]).pin_memory()
+    out_dx = torch.empty((nkf - 1, 7), dtype=torch.float32).pin_memory()
+    d2h = out_T.numel() * 4 + out_dx.numel() * 4
+    if world > 1:
+        all_ii_h, all_jj_h = g["all_ii"].cpu().pin_memory(), g["all_jj"].cpu().pin_memory()
+        h2d += 2 * all_ii_h.numel() * 8
+    del Xs, Cs, idx, vm, Q
+    torch.cuda.empty_cache()
+
+    def e2e_step():
+        d = [x.to(dev, non_blocking=True) for x in host_in]
+        if world == 1:
+            (dx,) = be.gauss_newton_rays(*d, *P)
+        else:
+            (dx,), _ = md.gauss_newton_rays_sharded(*d, all_ii_h.to(dev, non_blocking=True),
+                                                    all_jj_h.to(dev, non_blocking=True), *P)
+        out_T.copy_(d[0], non_blocking=True)
+        out_dx.copy_(dx, non_blocking=True)
+        torch.cuda.current_stream().synchronize()
+
+    for _ in range(2):
+        e2e_step()
+    barrier()
+    t0 = time.perf_counter()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    e2e_steps = max(2, min(args.steps, 5))
+    for _ in range(e2e_steps):
+        e2e_step()
+    e1.record()
+    barrier()
+    e2e_ms = torch.tensor([e0.elapsed_time(e1)], device=dev, dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(e2e_ms, op=dist.ReduceOp.MAX)
+    e2e_val = float(e2e_ms.item()) / e2e_steps / max(iters, 1)
+    del host_in
+    torch.cuda.empty_cache()
+
+    extra = {}
+    if rank == 0:
+        extra = matching_extra(be, syn, dev, torch)
+        extra["hessian_kernel_ms"] = hess_ms
+        extra["solve_other_ms_per_iter"] = value - hess_ms
+        extra["iterations_executed"] = iters
+        cpu_base = cpu_gn_sample(device=dev)[0] if world == 1 else None
+        line = dict(metric="gn_solve_ms_per_iter", value=value, unit="ms/iter", n_gpus=world, steps=args.steps,
+                    warmup=args.warmup, ms_per_step=ms_per_step, higher_is_better=False, scaling="weak", vs_baseline=None,
+                    dtype="f32 (fp64 reduction + Cholesky)", data="synthetic", config=workload_config(world),
+                    clocks=clocks, gpu_launches=launches,
+                    e2e=dict(value=e2e_val, unit="ms/iter", h2d_bytes_per_step=int(h2d), d2h_bytes_per_step=int(d2h)),
+                    roofline=dict(bound="hbm", achieved=achieved, peak=peak, unit="GB/s", frac=achieved / peak,
+                                  traffic=ncu_traffic(), kernel="hessian_kernel<RAYS,HUBER>", peak_source=peak_src,
+                                  algorithmic_bytes_per_launch=algo_bytes, launch_ms=hess_ms,
+                                  note="algorithmic bytes = 45 B x pixels x directed edges of the reference's input layout"),
+                    extra=extra)
+        if cpu_base is not None:
+            line["cpu_baseline"] = cpu_base
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def ncu_traffic():
+    """dram bytes per launch of the dominant kernel from the committed ncu capture (profiles/), else null."""
+    p = os.path.join(ROOT, "profiles", "hessian_dram_bytes_per_launch.json")
+    if os.path.exists(p):
+        try:
+            return json.load(open(p))["dram_bytes_per_launch"]
+        except Exception:
+            return None
+    return None
+
+
+def matching_extra(be, syn, dev, torch):
+    """BASELINE.json's second metric: iter_proj (+ refine_matches) Mpix/s at 512x384, configs[1] (b=1) and b=8."""
+    mt = syn.MATCHING
+    out = {}
+    for b in (1, 8):
+        m = syn.make_match_problem(b, H, W, seed=1235, device=dev)
+        rays, pts, p0 = m["rays_img_with_grad"], m["pts_3d_norm"], m["p_init"]
+        D11, D21 = m["D11"].half(), m["D21"].view(b, N_PIX, -1).half()
+        fn_ip = lambda: be.iter_proj(rays, pts, p0, mt["max_iter"], mt["lambda_init"], mt["convergence_thresh"])
+        p1 = fn_ip()[0].long()
+        fn_rf = lambda: be.refine_matches(D11, D21, p1, mt["radius"], mt["dilation_max"])
+        res = {}
+        for name, fn in (("iter_proj", fn_ip), ("refine_matches", fn_rf)):
+            for _ in range(3):
+                fn()
+            torch.cuda.synchronize()
+            a, c = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            reps = 20
+            a.record()
+            for _ in range(reps):
+                fn()
+            c.record()
+            torch.cuda.synchronize()
+            ms = a.elapsed_time(c) / reps
+            res[name + "_ms"] = ms
+            res[name + "_mpix_s"] = b * N_PIX / (ms * 1e-3) / 1e6
+        peak, _ = measured_peak()
+        res["iter_proj_hbm_frac"] = ITER_PROJ_BYTES_PER_QUERY * b * N_PIX / (res["iter_proj_ms"] * 1e-3) / 1e9 / peak
+        out[f"matching_b{b}"] = res
+        del m, rays, pts, p0, D11, D21
+    return out
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    args = ap.parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -191,12 +191,14 @@ def loop_closure_edges(num_kf, n_loop=3, seed=0):
 
 
 def make_gn_problem(num_kf, h, w, edges, seed=1236, device="cpu", calib=False, pose_noise=(0.02, 0.02, 0.01),
-                    kf_ids=None, yaw_step_deg=None, point_noise=0.005):
+                    kf_ids=None, yaw_step_deg=None, point_noise=0.005, directed_subset=None):
     """Inputs of gauss_newton_rays/calib/points exactly as FactorGraph hands them over (global_opt.py:121-155).
 
     Returns dict with Twc (num_kf,8) f32 [perturbed], Twc_gt, Xs (num_kf,N,3), Cs (num_kf,N,1), ii, jj (E) int64
     [global kf ids], idx_ii2jj (E,N) int64, valid_match (E,N,1) bool, Q (E,N,1) f32, K (3,3) f32.
     E = 2 * len(edges) (both directions, prep_two_way_edges global_opt.py:104-110).
+    directed_subset (1-D LongTensor of indices into the two-way edge list) restricts ii/jj/idx/valid/Q to one rank's
+    shard; all_ii/all_jj always hold the whole graph.
     """
     N = h * w
     g = torch.Generator().manual_seed(seed)
@@ -213,6 +215,9 @@ def make_gn_problem(num_kf, h, w, edges, seed=1236, device="cpu", calib=False, p
     e_i, e_j = edges
     ii = torch.tensor(list(e_i) + list(e_j), dtype=torch.int64)
     jj = torch.tensor(list(e_j) + list(e_i), dtype=torch.int64)
+    all_ii, all_jj = ii, jj
+    if directed_subset is not None:
+        ii, jj = ii[directed_subset], jj[directed_subset]
     E = ii.numel()
     idx = torch.zeros(E, N, dtype=torch.int64, device=device)
     valid = torch.zeros(E, N, 1, dtype=torch.bool, device=device)
@@ -241,10 +246,11 @@ def make_gn_problem(num_kf, h, w, edges, seed=1236, device="cpu", calib=False, p
     T_init = sim3_mul(sim3_exp_small(xi), T_gt)
     if kf_ids is not None:  # non-contiguous global keyframe ids exercise the unique/searchsorted prep
         ids = torch.tensor(kf_ids, dtype=torch.int64)
-        ii, jj = ids[ii], ids[jj]
+        ii, jj, all_ii, all_jj = ids[ii], ids[jj], ids[all_ii], ids[all_jj]
     return dict(Twc=T_init.float().to(device).contiguous(), Twc_gt=T_gt.float().to(device), Xs=Xs.float().contiguous(),
                 Cs=Cs.float().contiguous(), ii=ii.to(device), jj=jj.to(device), idx_ii2jj=idx.contiguous(),
-                valid_match=valid.contiguous(), Q=Q.float().contiguous(), K=Kd.float().contiguous(), h=h, w=w)
+                valid_match=valid.contiguous(), Q=Q.float().contiguous(), K=Kd.float().contiguous(), h=h, w=w,
+                all_ii=all_ii.to(device), all_jj=all_jj.to(device))
 
 
 # ----------------------------------------------------------------------------------------------- matching pairs

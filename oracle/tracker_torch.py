@@ -1,0 +1,152 @@
+"""TEST/BASELINE INFRASTRUCTURE ONLY -- the reference's CPU path for BASELINE.json configs[0].
+
+Pure-torch restatement of FrameTracker.opt_pose_ray_dist_sim3 + solve (reference: mast3r_slam/tracker.py:173-214,
+:156-171) with geometry.act_Sim3 / point_to_ray_dist (geometry.py:17-52), nonlinear_optimizer.huber /
+check_convergence (nonlinear_optimizer.py:5-33).  The reference imports `lietorch` for Sim(3) objects; lietorch is an
+un-pinned, un-vendored pip dependency (pyproject.toml:15) absent from this image, so `Sim3` below is a minimal
+stand-in with the same `.data` layout [t(3), q_xyzw(4), s(1)] and the operations the tracker uses (act, inv, *, retr =
+Exp(xi) o T with tangent order tau, omega, sigma -- consistent with gn_kernels.cu:392-413).  Results at that boundary
+are therefore "parity unpinned" by the reference; this file is a REPORTED CPU BASELINE, not a parity oracle.
+"""
+import math
+
+import torch
+
+TRACKING = dict(max_iters=50, rel_error=1e-3, delta_norm=1e-3, huber=1.345, sigma_ray=0.003, sigma_dist=10.0)
+
+
+def _qmul(a, b):
+    ax, ay, az, aw = a.unbind(-1)
+    bx, by, bz, bw = b.unbind(-1)
+    return torch.stack((aw * bx + ax * bw + ay * bz - az * by, aw * by - ax * bz + ay * bw + az * bx,
+                        aw * bz + ax * by - ay * bx + az * bw, aw * bw - ax * bx - ay * by - az * bz), -1)
+
+
+def _qrot(q, X):
+    qv = q[..., :3].expand_as(X)
+    uv = 2.0 * torch.cross(qv, X, dim=-1)
+    return X + q[..., 3:4] * uv + torch.cross(qv, uv, dim=-1)
+
+
+class Sim3:
+    def __init__(self, data):
+        self.data = data  # (...,8)
+
+    def act(self, X):
+        return self.data[..., 7:8] * _qrot(self.data[..., 3:7], X) + self.data[..., 0:3]
+
+    def inv(self):
+        d = self.data
+        qi = torch.cat((-d[..., 3:6], d[..., 6:7]), -1)
+        si = 1.0 / d[..., 7:8]
+        return Sim3(torch.cat((-si * _qrot(qi, d[..., 0:3]), qi, si), -1))
+
+    def __mul__(self, o):
+        a, b = self.data, o.data
+        t = a[..., 7:8] * _qrot(a[..., 3:7], b[..., 0:3]) + a[..., 0:3]
+        return Sim3(torch.cat((t, _qmul(a[..., 3:7], b[..., 3:7]), a[..., 7:8] * b[..., 7:8]), -1))
+
+    @staticmethod
+    def exp(xi):
+        tau, phi, sigma = xi[..., 0:3], xi[..., 3:6], xi[..., 6]
+        out = []
+        for k in range(xi.shape[0]):  # tiny (one pose): scalar branches as in expSim3 (gn_kernels.cu:323-390)
+            ph, sg, ta = phi[k], float(sigma[k]), tau[k]
+            th2 = float((ph * ph).sum())
+            th = math.sqrt(th2)
+            sc = math.exp(sg)
+            if th2 < 1e-6:
+                imag, real = 0.5 - th2 / 48.0 + th2 * th2 / 3840.0, 1.0 - th2 / 8.0 + th2 * th2 / 384.0
+            else:
+                imag, real = math.sin(0.5 * th) / th, math.cos(0.5 * th)
+            if abs(sg) < 1e-6:
+                Cc = 1.0
+                A, B = (0.5, 1.0 / 6.0) if th < 1e-6 else ((1 - math.cos(th)) / th2, (th - math.sin(th)) / (th2 * th))
+            else:
+                Cc = (sc - 1.0) / sg
+                if th < 1e-6:
+                    A = ((sg - 1) * sc + 1) / (sg * sg)
+                    B = (sc * 0.5 * sg * sg + sc - 1 - sg * sc) / (sg ** 3)
+                else:
+                    a, b, c = sc * math.sin(th), sc * math.cos(th), th2 + sg * sg
+                    A = (a * sg + (1 - b) * th) / (th * c)
+                    B = (Cc - ((b - 1) * sg + a * th) / c) / th2
+            cr = torch.linalg.cross(ph, ta)
+            t = Cc * ta + A * cr + B * torch.linalg.cross(ph, cr)
+            out.append(torch.cat((t, imag * ph, torch.tensor([real], dtype=xi.dtype), torch.tensor([sc], dtype=xi.dtype))))
+        return Sim3(torch.stack(out))
+
+    def retr(self, xi):
+        return Sim3.exp(xi) * self
+
+
+def skew_sym(x):
+    b = x.shape[:-1]
+    x, y, z = x.unbind(dim=-1)
+    o = torch.zeros_like(x)
+    return torch.stack([o, -z, y, z, o, -x, -y, x, o], dim=-1).view(*b, 3, 3)
+
+
+def point_to_ray_dist(X, jacobian=False):  # geometry.py:17-34
+    b = X.shape[:-1]
+    d = torch.linalg.norm(X, dim=-1, keepdim=True)
+    d_inv = 1.0 / d
+    r = d_inv * X
+    rd = torch.cat((r, d), dim=-1)
+    if not jacobian:
+        return rd
+    d_inv_2 = d_inv ** 2
+    I = torch.eye(3, device=X.device, dtype=X.dtype).repeat(*b, 1, 1)
+    dr_dX = d_inv.unsqueeze(-1) * (I - d_inv_2.unsqueeze(-1) * (X.unsqueeze(-1) @ X.unsqueeze(-2)))
+    return rd, torch.cat((dr_dX, r.unsqueeze(-2)), dim=-2)
+
+
+def act_Sim3(X, pC, jacobian=False):  # geometry.py:45-52
+    pW = X.act(pC)
+    if not jacobian:
+        return pW
+    dpC_dt = torch.eye(3, device=pW.device).repeat(*pW.shape[:-1], 1, 1)
+    return pW, torch.cat([dpC_dt, -skew_sym(pW), pW.reshape(*pW.shape[:-1], -1, 1)], dim=-1)
+
+
+def huber(r, k=1.345):  # nonlinear_optimizer.py:28-33
+    unit = torch.ones((1), dtype=r.dtype, device=r.device)
+    r_abs = torch.abs(r)
+    return torch.where(r_abs < k, unit, k / r_abs)
+
+
+def solve(sqrt_info, r, J, cfg):  # tracker.py:156-171
+    whitened_r = sqrt_info * r
+    robust_sqrt_info = sqrt_info * torch.sqrt(huber(whitened_r, k=cfg["huber"]))
+    mdim = J.shape[-1]
+    A = (robust_sqrt_info[..., None] * J).view(-1, mdim)
+    b = (robust_sqrt_info * r).view(-1, 1)
+    H = A.T @ A
+    g = -A.T @ b
+    cost = 0.5 * (b.T @ b).item()
+    L = torch.linalg.cholesky(H, upper=False)
+    return torch.cholesky_solve(g, L, upper=False).view(1, -1), cost
+
+
+def opt_pose_ray_dist_sim3(Xf, Xk, T_WCf, T_WCk, Qk, valid, cfg=TRACKING, max_iters=None):
+    """tracker.py:173-214.  Returns (T_WCf, T_CkCf, iterations executed)."""
+    sqrt_info_ray = 1 / cfg["sigma_ray"] * valid * torch.sqrt(Qk)
+    sqrt_info_dist = 1 / cfg["sigma_dist"] * valid * torch.sqrt(Qk)
+    sqrt_info = torch.cat((sqrt_info_ray.repeat(1, 3), sqrt_info_dist), dim=1)
+    T_CkCf = T_WCk.inv() * T_WCf
+    rd_k = point_to_ray_dist(Xk, jacobian=False)
+    old_cost = float("inf")
+    iters = 0
+    for step in range(max_iters or cfg["max_iters"]):
+        Xf_Ck, dXf_Ck_dT = act_Sim3(T_CkCf, Xf, jacobian=True)
+        rd_f_Ck, drd_dX = point_to_ray_dist(Xf_Ck, jacobian=True)
+        r = rd_k - rd_f_Ck
+        J = -drd_dX @ dXf_Ck_dT
+        tau, new_cost = solve(sqrt_info, r, J, cfg)
+        T_CkCf = T_CkCf.retr(tau)
+        iters += 1
+        rel_dec = math.fabs((old_cost - new_cost) / old_cost) if old_cost != float("inf") else float("inf")
+        if rel_dec < cfg["rel_error"] or torch.linalg.norm(tau) < cfg["delta_norm"]:
+            break
+        old_cost = new_cost
+    return T_WCk * T_CkCf, T_CkCf, iters
