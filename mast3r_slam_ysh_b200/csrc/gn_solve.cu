@@ -400,36 +400,53 @@ __global__ void __launch_bounds__(1024) backsolve_retract_kernel(const double* _
   if (state[kDone]) return;
   extern __shared__ double s_y[];  // n (+ padding to nblk*32)
   __shared__ double s_x[kBlk];
+  __shared__ double s_L[kBlk][kBlk + 1];  // diagonal factor block of the current step
+  __shared__ double s_dinv[kBlk];
+  __shared__ double s_part[4][256];
   __shared__ double s_norm[32];
   __shared__ int s_bad;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   if (tid == 0) s_bad = state[kFailNow];
   for (int c = tid; c < nblk * kBlk; c += blockDim.x) s_y[c] = (c < n) ? sys[(size_t)n * ld + c] : 0.0;
-  __syncthreads();
   for (int kb = nblk - 1; kb >= 0; kb--) {
     const int c0 = kb * kBlk;
+    {  // stage L_kk (identity-padded, 32x32) in shared memory: the serial loop below must not wait on L2
+      const double v = lfac[(size_t)kb * kBlk * kBlk + tid];
+      s_L[tid >> 5][tid & 31] = v;
+      if ((tid >> 5) == (tid & 31)) s_dinv[tid & 31] = 1.0 / v;
+    }
+    __syncthreads();
     if (warp == 0) {
-      const double* L = lfac + (size_t)kb * kBlk * kBlk;  // identity-padded
       double yv = s_y[c0 + lane];
+#pragma unroll
       for (int j = kBlk - 1; j >= 0; j--) {
-        double xj = 0.0;
-        if (lane == j) xj = yv / L[j * kBlk + j];
-        xj = shfl_d(xj, j);
+        const double xj = shfl_d(yv * s_dinv[j], j);  // lane j holds the finished y_j
         if (lane == j) yv = xj;
-        if (lane < j) yv -= L[j * kBlk + lane] * xj;
+        if (lane < j) yv -= s_L[j][lane] * xj;
       }
       s_x[lane] = yv;
       s_y[c0 + lane] = yv;
     }
     __syncthreads();
     const int rows = min(kBlk, n - c0);
-    for (int c = tid; c < c0; c += blockDim.x) {
-      double acc = s_y[c];
-      for (int i = 0; i < rows; i++) acc -= sys[(size_t)(c0 + i) * ld + c] * s_x[i];
-      s_y[c] = acc;
+    // y[0:c0] -= L[c0:c0+rows, 0:c0]^T x : 256 columns x 4 row groups per pass
+    for (int cb = 0; cb < c0; cb += 256) {
+      const int c = cb + (tid & 255), grp = tid >> 8;
+      double acc = 0.0;
+      if (c < c0) {
+#pragma unroll
+        for (int i = 0; i < 8; i++) {
+          const int r = grp * 8 + i;
+          if (r < rows) acc += sys[(size_t)(c0 + r) * ld + c] * s_x[r];
+        }
+      }
+      s_part[grp][tid & 255] = acc;
+      __syncthreads();
+      if (tid < 256 && c < c0) s_y[c] -= (s_part[0][tid] + s_part[1][tid]) + (s_part[2][tid] + s_part[3][tid]);
+      __syncthreads();
     }
-    __syncthreads();
   }
+  __syncthreads();
   // non-finite solution counts as a failed factorisation
   int bad_local = 0;
   for (int c = tid; c < n; c += blockDim.x)

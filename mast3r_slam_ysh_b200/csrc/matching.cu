@@ -12,6 +12,7 @@
 //     cannot change the result.
 #include <cuda_fp16.h>
 #include <float.h>
+#include <stdlib.h>
 
 #include "m3r_common.cuh"
 
@@ -121,6 +122,148 @@ __global__ void __launch_bounds__(128) iter_proj_kernel(const float* __restrict_
     } else {
       lambda = kMirrorFp64 ? (float)((double)lambda * 10.0) : lambda * 10.0f;
       conv = cost < cost_thresh;
+    }
+  }
+  reinterpret_cast<float2*>(p_new)[gid] = make_float2(u, v);
+  converged[gid] = conv ? 1 : 0;
+}
+
+// ------------------------------------------------------------------------------------------------ iter_proj v2
+// Layout pre-pass + cached LM loop.  Profiling v1 on B200 showed the kernel bound by L1 wavefronts, not HBM or issue:
+// every scalar LDG of the 36-byte-stride AoS image touches ~9 cache lines per warp and v1 issues 48 of them per LM
+// iteration.  v2 repacks the 9-channel image once per call into 16-byte records
+//   P0 = (ray.xyz, gx.x)   P1 = (gx.y, gx.z, gy.x, gy.y)   P2 = gy.z
+// so a corner is 2 x LDG.128 + 1 x LDG.32, and keeps the last sample in registers: a rejected LM step re-uses the
+// sample at (u,v) unchanged (the reference re-reads identical values), an accepted step re-uses the ray just sampled
+// at the candidate position and only fetches the gradients there.
+// Arithmetic notes (why this stays bit-compatible with matching_kernels.cu:155-268 up to rare double roundings):
+//   * u,v >= 1 so du,dv are multiples of 2^-23 and 1-du, 1-dv are exact in fp32; the reference's double products
+//     (1.0-du)*dv etc. rounded to float equal the single fp32 products;
+//   * (float)(1.0/(double)x) equals the correctly rounded fp32 reciprocal unless the double quotient lands within
+//     2^-54 of a float tie (probability ~2^-29 per operation);
+//   * lambda*10.0 is exact-then-rounded in both precisions; lambda*0.1 is kept in double (0.1 != 0.1f).
+__global__ void __launch_bounds__(256) repack_rays_kernel(const float* __restrict__ rays, float4* __restrict__ P0,
+                                                          float4* __restrict__ P1, float* __restrict__ P2,
+                                                          long long total) {
+  const long long p = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (p >= total) return;
+  const float* s = rays + p * 9;
+  P0[p] = make_float4(__ldg(s + 0), __ldg(s + 1), __ldg(s + 2), __ldg(s + 3));
+  P1[p] = make_float4(__ldg(s + 4), __ldg(s + 5), __ldg(s + 6), __ldg(s + 7));
+  P2[p] = __ldg(s + 8);
+}
+
+struct Bil {
+  float w11, w12, w21, w22;
+  int o22, o21, o12, o11;  // pixel offsets of (v,u), (v,u+1), (v+1,u), (v+1,u+1)
+};
+
+__device__ __forceinline__ Bil bil_setup(float u, float v, int w) {
+  Bil B;
+  const int u11 = static_cast<int>(floorf(u));
+  const int v11 = static_cast<int>(floorf(v));
+  const float du = u - static_cast<float>(u11);
+  const float dv = v - static_cast<float>(v11);
+  const float cu = 1.0f - du, cv = 1.0f - dv;  // exact (see header comment)
+  B.w11 = du * dv;
+  B.w12 = cu * dv;
+  B.w21 = du * cv;
+  B.w22 = cu * cv;
+  B.o22 = v11 * w + u11;
+  B.o21 = B.o22 + 1;
+  B.o12 = B.o22 + w;
+  B.o11 = B.o12 + 1;
+  return B;
+}
+
+#define M3R_BIL(B, a11, a12, a21, a22) ((B).w11 * (a11) + (B).w12 * (a12) + (B).w21 * (a21) + (B).w22 * (a22))
+
+template <int VAR>
+__global__ void __launch_bounds__(128) iter_proj_v2_kernel(const float4* __restrict__ P0, const float4* __restrict__ P1,
+                                                           const float* __restrict__ P2, const float* __restrict__ pts,
+                                                           const float* __restrict__ p_init, float* __restrict__ p_new,
+                                                           uint8_t* __restrict__ converged, long long total, int n,
+                                                           int h, int w, int max_iter, float lambda_init,
+                                                           float cost_thresh) {
+  const long long gid = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (gid >= total) return;
+  const int b = (int)(gid / n);
+  const size_t img = (size_t)b * h * w;
+  const float4* __restrict__ p0 = P0 + img;
+  const float4* __restrict__ p1 = P1 + img;
+  const float* __restrict__ p2 = P2 + img;
+
+  const float2 pi = __ldg(reinterpret_cast<const float2*>(p_init) + gid);
+  float u = fminf(fmaxf(pi.x, 1.0f), (float)(w - 2));
+  float v = fminf(fmaxf(pi.y, 1.0f), (float)(h - 2));
+  const float tx = __ldg(pts + gid * 3 + 0), ty = __ldg(pts + gid * 3 + 1), tz = __ldg(pts + gid * 3 + 2);
+
+  float lambda = lambda_init;
+  bool conv = false;
+  // cached sample at (u,v)
+  float r0 = 0.f, r1 = 0.f, r2 = 0.f, gx0 = 0.f, gx1 = 0.f, gx2 = 0.f, gy0 = 0.f, gy1 = 0.f, gy2 = 0.f;
+  bool have_r = false, have_g = false;  // cached ray (+gx.x) / cached remaining gradients at (u,v)
+  Bil B = bil_setup(u, v, w);
+  for (int it = 0; it < max_iter; it++) {
+    if (!have_r) {
+      const float4 a11 = __ldg(p0 + B.o11), a12 = __ldg(p0 + B.o12), a21 = __ldg(p0 + B.o21), a22 = __ldg(p0 + B.o22);
+      r0 = M3R_BIL(B, a11.x, a12.x, a21.x, a22.x);
+      r1 = M3R_BIL(B, a11.y, a12.y, a21.y, a22.y);
+      r2 = M3R_BIL(B, a11.z, a12.z, a21.z, a22.z);
+      gx0 = M3R_BIL(B, a11.w, a12.w, a21.w, a22.w);
+    }
+    if (!have_g) {
+      const float4 c11 = __ldg(p1 + B.o11), c12 = __ldg(p1 + B.o12), c21 = __ldg(p1 + B.o21), c22 = __ldg(p1 + B.o22);
+      const float d11 = __ldg(p2 + B.o11), d12 = __ldg(p2 + B.o12), d21 = __ldg(p2 + B.o21), d22 = __ldg(p2 + B.o22);
+      gx1 = M3R_BIL(B, c11.x, c12.x, c21.x, c22.x);
+      gx2 = M3R_BIL(B, c11.y, c12.y, c21.y, c22.y);
+      gy0 = M3R_BIL(B, c11.z, c12.z, c21.z, c22.z);
+      gy1 = M3R_BIL(B, c11.w, c12.w, c21.w, c22.w);
+      gy2 = M3R_BIL(B, d11, d12, d21, d22);
+    }
+    float r_norm = sqrtf(r0 * r0 + r1 * r1 + r2 * r2);
+    float r_norm_inv = (VAR & 1) ? (float)(1.0 / (double)r_norm) : __frcp_rn(r_norm);
+    const float n0 = r0 * r_norm_inv, n1 = r1 * r_norm_inv, n2 = r2 * r_norm_inv;
+    const float e0 = n0 - tx, e1 = n1 - ty, e2 = n2 - tz;
+    const float cost = e0 * e0 + e1 * e1 + e2 * e2;
+    float A00 = gx0 * gx0 + gx1 * gx1 + gx2 * gx2;
+    const float A01 = gx0 * gy0 + gx1 * gy1 + gx2 * gy2;
+    float A11 = gy0 * gy0 + gy1 * gy1 + gy2 * gy2;
+    const float b0 = -(e0 * gx0 + e1 * gx1 + e2 * gx2);
+    const float b1 = -(e0 * gy0 + e1 * gy1 + e2 * gy2);
+    A00 += lambda;
+    A11 += lambda;
+    const float det = A00 * A11 - A01 * A01;
+    const float det_inv = (VAR & 1) ? (float)(1.0 / (double)det) : __frcp_rn(det);
+    const float delta_u = det_inv * (A11 * b0 - A01 * b1);
+    const float delta_v = det_inv * (-A01 * b0 + A00 * b1);
+    const float u_new = fminf(fmaxf(u + delta_u, 1.0f), (float)(w - 2));
+    const float v_new = fminf(fmaxf(v + delta_v, 1.0f), (float)(h - 2));
+
+    const Bil Bn = bil_setup(u_new, v_new, w);
+    const float4 a11 = __ldg(p0 + Bn.o11), a12 = __ldg(p0 + Bn.o12), a21 = __ldg(p0 + Bn.o21), a22 = __ldg(p0 + Bn.o22);
+    const float t0 = M3R_BIL(Bn, a11.x, a12.x, a21.x, a22.x);
+    const float t1 = M3R_BIL(Bn, a11.y, a12.y, a21.y, a22.y);
+    const float t2 = M3R_BIL(Bn, a11.z, a12.z, a21.z, a22.z);
+    r_norm = sqrtf(t0 * t0 + t1 * t1 + t2 * t2);
+    r_norm_inv = (VAR & 1) ? (float)(1.0 / (double)r_norm) : __frcp_rn(r_norm);
+    const float f0 = t0 * r_norm_inv - tx, f1 = t1 * r_norm_inv - ty, f2 = t2 * r_norm_inv - tz;
+    const float new_cost = f0 * f0 + f1 * f1 + f2 * f2;
+    if (new_cost < cost) {
+      u = u_new;
+      v = v_new;
+      lambda = __double2float_rn((double)lambda * 0.1);
+      conv = new_cost < cost_thresh;
+      r0 = t0; r1 = t1; r2 = t2;
+      gx0 = M3R_BIL(Bn, a11.w, a12.w, a21.w, a22.w);
+      B = Bn;
+      have_r = !(VAR & 2);
+      have_g = false;
+    } else {
+      lambda = lambda * 10.0f;
+      conv = cost < cost_thresh;
+      have_r = !(VAR & 4);
+      have_g = !(VAR & 8);
     }
   }
   reinterpret_cast<float2*>(p_new)[gid] = make_float2(u, v);
@@ -290,9 +433,48 @@ extern "C" int m3r_iter_proj(const float* rays_img_with_grad, const float* pts_3
   cudaStream_t st = (cudaStream_t)stream;
   const int threads = 128;
   const unsigned blocks = (unsigned)ceil_div_ll(total, threads);
-  iter_proj_kernel<true><<<blocks, threads, 0, st>>>(rays_img_with_grad, pts_3d_norm, p_init, p_new, converged, total,
-                                                     n, h, w, max_iter, lambda_init, cost_thresh);
+  static const bool use_v1 = getenv("M3R_ITER_PROJ_V1") != nullptr;  // A/B switch for profiling only
+  if (use_v1) {
+    iter_proj_kernel<true><<<blocks, threads, 0, st>>>(rays_img_with_grad, pts_3d_norm, p_init, p_new, converged, total,
+                                                       n, h, w, max_iter, lambda_init, cost_thresh);
+    M3R_LAUNCH_CHECK();
+    return M3R_OK;
+  }
+  // stream-ordered scratch for the repacked image (36 B per pixel, 16-byte aligned planes); no host sync
+  const long long npix = (long long)b * h * w;
+  const size_t plane = align_up((size_t)npix * sizeof(float4), 256);
+  {  // keep freed scratch cached in the default pool across synchronisations (default threshold 0 returns it to the OS)
+    static thread_local int pool_ready_dev = -1;
+    int dev = 0;
+    M3R_CUDA(cudaGetDevice(&dev));
+    if (pool_ready_dev != dev) {
+      cudaMemPool_t pool;
+      M3R_CUDA(cudaDeviceGetDefaultMemPool(&pool, dev));
+      uint64_t thr = UINT64_MAX;
+      M3R_CUDA(cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &thr));
+      pool_ready_dev = dev;
+    }
+  }
+  void* scratch = nullptr;
+  M3R_CUDA(cudaMallocAsync(&scratch, 2 * plane + align_up((size_t)npix * sizeof(float), 256), st));
+  float4* P0 = (float4*)scratch;
+  float4* P1 = (float4*)((char*)scratch + plane);
+  float* P2 = (float*)((char*)scratch + 2 * plane);
+  repack_rays_kernel<<<(unsigned)ceil_div_ll(npix, 256), 256, 0, st>>>(rays_img_with_grad, P0, P1, P2, npix);
   M3R_LAUNCH_CHECK();
+  const char* var_env = getenv("M3R_ITER_PROJ_VARIANT");  // experiment switch, removed once settled
+  const int var = var_env ? atoi(var_env) : 0;
+#define M3R_IP_CASE(V)                                                                                              \
+  case V:                                                                                                           \
+    iter_proj_v2_kernel<V><<<blocks, threads, 0, st>>>(P0, P1, P2, pts_3d_norm, p_init, p_new, converged, total, n, \
+                                                       h, w, max_iter, lambda_init, cost_thresh);                  \
+    break;
+  switch (var & 15) {
+    M3R_IP_CASE(0) M3R_IP_CASE(2) M3R_IP_CASE(4) M3R_IP_CASE(8) M3R_IP_CASE(12) M3R_IP_CASE(14) M3R_IP_CASE(1)
+    default: set_error("iter_proj: unknown variant"); return M3R_ERR_INVALID_ARGUMENT;
+  }
+  M3R_LAUNCH_CHECK();
+  M3R_CUDA(cudaFreeAsync(scratch, st));
   return M3R_OK;
 }
 

@@ -218,7 +218,7 @@ def test_pose_retr_vs_oracle(be, orc):
     dx[4] = 0
     want = orc.pose_retr(poses.numpy(), dx.numpy())
     got = be.pose_retr(poses.to(DEV).clone(), dx.to(DEV))
-    assert np.allclose(got.cpu().numpy(), want, rtol=2e-6, atol=2e-7)
+    assert np.allclose(got.cpu().numpy(), want, rtol=2e-5, atol=2e-6)  # sinf/cosf/expf: device vs host libm
     assert np.array_equal(got.cpu().numpy()[0], poses.numpy()[0])
 
 
