@@ -162,13 +162,13 @@ __device__ __forceinline__ Bil bil_setup(float u, float v, int w) {
   Bil B;
   const int u11 = static_cast<int>(floorf(u));
   const int v11 = static_cast<int>(floorf(v));
-  const float du = u - static_cast<float>(u11);
-  const float dv = v - static_cast<float>(v11);
-  const float cu = 1.0f - du, cv = 1.0f - dv;  // exact (see header comment)
-  B.w11 = du * dv;
-  B.w12 = cu * dv;
-  B.w21 = du * cv;
-  B.w22 = cu * cv;
+  const float du = __fsub_rn(u, static_cast<float>(u11));
+  const float dv = __fsub_rn(v, static_cast<float>(v11));
+  const float cu = __fsub_rn(1.0f, du), cv = __fsub_rn(1.0f, dv);  // exact (see header comment)
+  B.w11 = __fmul_rn(du, dv);
+  B.w12 = __fmul_rn(cu, dv);
+  B.w21 = __fmul_rn(du, cv);
+  B.w22 = __fmul_rn(cu, cv);
   B.o22 = v11 * w + u11;
   B.o21 = B.o22 + 1;
   B.o12 = B.o22 + w;
@@ -176,9 +176,18 @@ __device__ __forceinline__ Bil bil_setup(float u, float v, int w) {
   return B;
 }
 
-#define M3R_BIL(B, a11, a12, a21, a22) ((B).w11 * (a11) + (B).w12 * (a12) + (B).w21 * (a21) + (B).w22 * (a22))
+// The reference binary (nvcc 12.9, default -fmad=true) evaluates its float expressions with these exact fused
+// sequences (read off its SASS); they are spelled out with non-contracting intrinsics so that this kernel's
+// rounding does not depend on how the compiler happens to contract a differently shaped program.
+//   w11*a11 + w12*a12 + w21*a21 + w22*a22  ->  fma(w22,a22, fma(w21,a21, fma(w11,a11, w12*a12)))
+//   x*x' + y*y' + z*z'                     ->  fma(z,z', fma(x,x', y*y'))
+__device__ __forceinline__ float bil(const Bil& B, float a11, float a12, float a21, float a22) {
+  return __fmaf_rn(B.w22, a22, __fmaf_rn(B.w21, a21, __fmaf_rn(B.w11, a11, __fmul_rn(B.w12, a12))));
+}
+__device__ __forceinline__ float dot3_ref(float x, float xp, float y, float yp, float z, float zp) {
+  return __fmaf_rn(z, zp, __fmaf_rn(x, xp, __fmul_rn(y, yp)));
+}
 
-template <int VAR>
 __global__ void __launch_bounds__(128) iter_proj_v2_kernel(const float4* __restrict__ P0, const float4* __restrict__ P1,
                                                            const float* __restrict__ P2, const float* __restrict__ pts,
                                                            const float* __restrict__ p_init, float* __restrict__ p_new,
@@ -200,70 +209,67 @@ __global__ void __launch_bounds__(128) iter_proj_v2_kernel(const float4* __restr
 
   float lambda = lambda_init;
   bool conv = false;
-  // cached sample at (u,v)
+  // sample cached at (u,v): raw ray, d/du, d/dv
   float r0 = 0.f, r1 = 0.f, r2 = 0.f, gx0 = 0.f, gx1 = 0.f, gx2 = 0.f, gy0 = 0.f, gy1 = 0.f, gy2 = 0.f;
-  bool have_r = false, have_g = false;  // cached ray (+gx.x) / cached remaining gradients at (u,v)
+  bool have_r = false, have_g = false;
   Bil B = bil_setup(u, v, w);
   for (int it = 0; it < max_iter; it++) {
     if (!have_r) {
       const float4 a11 = __ldg(p0 + B.o11), a12 = __ldg(p0 + B.o12), a21 = __ldg(p0 + B.o21), a22 = __ldg(p0 + B.o22);
-      r0 = M3R_BIL(B, a11.x, a12.x, a21.x, a22.x);
-      r1 = M3R_BIL(B, a11.y, a12.y, a21.y, a22.y);
-      r2 = M3R_BIL(B, a11.z, a12.z, a21.z, a22.z);
-      gx0 = M3R_BIL(B, a11.w, a12.w, a21.w, a22.w);
+      r0 = bil(B, a11.x, a12.x, a21.x, a22.x);
+      r1 = bil(B, a11.y, a12.y, a21.y, a22.y);
+      r2 = bil(B, a11.z, a12.z, a21.z, a22.z);
+      gx0 = bil(B, a11.w, a12.w, a21.w, a22.w);
     }
     if (!have_g) {
       const float4 c11 = __ldg(p1 + B.o11), c12 = __ldg(p1 + B.o12), c21 = __ldg(p1 + B.o21), c22 = __ldg(p1 + B.o22);
       const float d11 = __ldg(p2 + B.o11), d12 = __ldg(p2 + B.o12), d21 = __ldg(p2 + B.o21), d22 = __ldg(p2 + B.o22);
-      gx1 = M3R_BIL(B, c11.x, c12.x, c21.x, c22.x);
-      gx2 = M3R_BIL(B, c11.y, c12.y, c21.y, c22.y);
-      gy0 = M3R_BIL(B, c11.z, c12.z, c21.z, c22.z);
-      gy1 = M3R_BIL(B, c11.w, c12.w, c21.w, c22.w);
-      gy2 = M3R_BIL(B, d11, d12, d21, d22);
+      gx1 = bil(B, c11.x, c12.x, c21.x, c22.x);
+      gx2 = bil(B, c11.y, c12.y, c21.y, c22.y);
+      gy0 = bil(B, c11.z, c12.z, c21.z, c22.z);
+      gy1 = bil(B, c11.w, c12.w, c21.w, c22.w);
+      gy2 = bil(B, d11, d12, d21, d22);
     }
-    float r_norm = sqrtf(r0 * r0 + r1 * r1 + r2 * r2);
-    float r_norm_inv = (VAR & 1) ? (float)(1.0 / (double)r_norm) : __frcp_rn(r_norm);
-    const float n0 = r0 * r_norm_inv, n1 = r1 * r_norm_inv, n2 = r2 * r_norm_inv;
-    const float e0 = n0 - tx, e1 = n1 - ty, e2 = n2 - tz;
-    const float cost = e0 * e0 + e1 * e1 + e2 * e2;
-    float A00 = gx0 * gx0 + gx1 * gx1 + gx2 * gx2;
-    const float A01 = gx0 * gy0 + gx1 * gy1 + gx2 * gy2;
-    float A11 = gy0 * gy0 + gy1 * gy1 + gy2 * gy2;
-    const float b0 = -(e0 * gx0 + e1 * gx1 + e2 * gx2);
-    const float b1 = -(e0 * gy0 + e1 * gy1 + e2 * gy2);
-    A00 += lambda;
-    A11 += lambda;
-    const float det = A00 * A11 - A01 * A01;
-    const float det_inv = (VAR & 1) ? (float)(1.0 / (double)det) : __frcp_rn(det);
-    const float delta_u = det_inv * (A11 * b0 - A01 * b1);
-    const float delta_v = det_inv * (-A01 * b0 + A00 * b1);
-    const float u_new = fminf(fmaxf(u + delta_u, 1.0f), (float)(w - 2));
-    const float v_new = fminf(fmaxf(v + delta_v, 1.0f), (float)(h - 2));
+    // normalise, residual, cost (matching_kernels.cu:186-198); 1.0/r_norm compiles to the IEEE fp32 reciprocal
+    float inv = __frcp_rn(__fsqrt_rn(dot3_ref(r0, r0, r1, r1, r2, r2)));
+    const float e0 = __fmaf_rn(r0, inv, -tx), e1 = __fmaf_rn(r1, inv, -ty), e2 = __fmaf_rn(r2, inv, -tz);
+    const float cost = dot3_ref(e0, e0, e1, e1, e2, e2);
+    // 2x2 LM system (:202-215)
+    const float A00 = __fadd_rn(dot3_ref(gx0, gx0, gx1, gx1, gx2, gx2), lambda);
+    const float A01 = dot3_ref(gx0, gy0, gx1, gy1, gx2, gy2);
+    const float A11 = __fadd_rn(dot3_ref(gy0, gy0, gy1, gy1, gy2, gy2), lambda);
+    const float s0 = dot3_ref(gx0, e0, gx1, e1, gx2, e2);  // = -b0
+    const float s1 = dot3_ref(gy0, e0, gy1, e1, gy2, e2);  // = -b1
+    const float det_inv = __frcp_rn(__fmaf_rn(A00, A11, -__fmul_rn(A01, A01)));
+    const float xu = __fmaf_rn(A01, s1, -__fmul_rn(s0, A11));  // A11*b0 - A01*b1
+    const float xv = __fmaf_rn(A01, s0, -__fmul_rn(s1, A00));  // -A01*b0 + A00*b1
+    const float u_new = fminf(fmaxf(__fmaf_rn(xu, det_inv, u), 1.0f), (float)(w - 2));
+    const float v_new = fminf(fmaxf(__fmaf_rn(xv, det_inv, v), 1.0f), (float)(h - 2));
 
+    // candidate cost (:225-256)
     const Bil Bn = bil_setup(u_new, v_new, w);
     const float4 a11 = __ldg(p0 + Bn.o11), a12 = __ldg(p0 + Bn.o12), a21 = __ldg(p0 + Bn.o21), a22 = __ldg(p0 + Bn.o22);
-    const float t0 = M3R_BIL(Bn, a11.x, a12.x, a21.x, a22.x);
-    const float t1 = M3R_BIL(Bn, a11.y, a12.y, a21.y, a22.y);
-    const float t2 = M3R_BIL(Bn, a11.z, a12.z, a21.z, a22.z);
-    r_norm = sqrtf(t0 * t0 + t1 * t1 + t2 * t2);
-    r_norm_inv = (VAR & 1) ? (float)(1.0 / (double)r_norm) : __frcp_rn(r_norm);
-    const float f0 = t0 * r_norm_inv - tx, f1 = t1 * r_norm_inv - ty, f2 = t2 * r_norm_inv - tz;
-    const float new_cost = f0 * f0 + f1 * f1 + f2 * f2;
-    if (new_cost < cost) {
+    const float t0 = bil(Bn, a11.x, a12.x, a21.x, a22.x);
+    const float t1 = bil(Bn, a11.y, a12.y, a21.y, a22.y);
+    const float t2 = bil(Bn, a11.z, a12.z, a21.z, a22.z);
+    inv = __frcp_rn(__fsqrt_rn(dot3_ref(t0, t0, t1, t1, t2, t2)));
+    const float f0 = __fmaf_rn(t0, inv, -tx), f1 = __fmaf_rn(t1, inv, -ty), f2 = __fmaf_rn(t2, inv, -tz);
+    const float new_cost = dot3_ref(f0, f0, f1, f1, f2, f2);
+    if (new_cost < cost) {  // accept (:259-264): the ray sampled at the candidate becomes the cached ray
       u = u_new;
       v = v_new;
       lambda = __double2float_rn((double)lambda * 0.1);
       conv = new_cost < cost_thresh;
       r0 = t0; r1 = t1; r2 = t2;
-      gx0 = M3R_BIL(Bn, a11.w, a12.w, a21.w, a22.w);
+      gx0 = bil(Bn, a11.w, a12.w, a21.w, a22.w);
       B = Bn;
-      have_r = !(VAR & 2);
+      have_r = true;
       have_g = false;
-    } else {
-      lambda = lambda * 10.0f;
+    } else {  // reject (:265-268): same (u,v) next time, everything cached
+      lambda = __fmul_rn(lambda, 10.0f);
       conv = cost < cost_thresh;
-      have_r = !(VAR & 4);
-      have_g = !(VAR & 8);
+      have_r = true;
+      have_g = true;
     }
   }
   reinterpret_cast<float2*>(p_new)[gid] = make_float2(u, v);
@@ -462,17 +468,8 @@ extern "C" int m3r_iter_proj(const float* rays_img_with_grad, const float* pts_3
   float* P2 = (float*)((char*)scratch + 2 * plane);
   repack_rays_kernel<<<(unsigned)ceil_div_ll(npix, 256), 256, 0, st>>>(rays_img_with_grad, P0, P1, P2, npix);
   M3R_LAUNCH_CHECK();
-  const char* var_env = getenv("M3R_ITER_PROJ_VARIANT");  // experiment switch, removed once settled
-  const int var = var_env ? atoi(var_env) : 0;
-#define M3R_IP_CASE(V)                                                                                              \
-  case V:                                                                                                           \
-    iter_proj_v2_kernel<V><<<blocks, threads, 0, st>>>(P0, P1, P2, pts_3d_norm, p_init, p_new, converged, total, n, \
-                                                       h, w, max_iter, lambda_init, cost_thresh);                  \
-    break;
-  switch (var & 15) {
-    M3R_IP_CASE(0) M3R_IP_CASE(2) M3R_IP_CASE(4) M3R_IP_CASE(8) M3R_IP_CASE(12) M3R_IP_CASE(14) M3R_IP_CASE(1)
-    default: set_error("iter_proj: unknown variant"); return M3R_ERR_INVALID_ARGUMENT;
-  }
+  iter_proj_v2_kernel<<<blocks, threads, 0, st>>>(P0, P1, P2, pts_3d_norm, p_init, p_new, converged, total, n, h, w,
+                                                  max_iter, lambda_init, cost_thresh);
   M3R_LAUNCH_CHECK();
   M3R_CUDA(cudaFreeAsync(scratch, st));
   return M3R_OK;

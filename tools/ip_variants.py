@@ -9,7 +9,7 @@ m = syn.make_match_problem(1, 384, 512, seed=1235, device=dev)
 rays, pts, p0 = m["rays_img_with_grad"], m["pts_3d_norm"], m["p_init"]
 args = (mt["max_iter"], mt["lambda_init"], mt["convergence_thresh"])
 p_r, c_r = ref.iter_proj(rays, pts, p0, *args); torch.cuda.synchronize()
-for var in (0, 4, 8, 12, 2, 14):
+for var in (0,):
     os.environ["M3R_ITER_PROJ_VARIANT"] = str(var)
     p, c = be.iter_proj(rays, pts, p0, *args); torch.cuda.synchronize()
     e = (p - p_r).abs().amax(-1)
