@@ -220,14 +220,55 @@ __device__ __forceinline__ void pixel_accumulate(float (&acc)[kAcc], const EdgeC
 
 // ------------------------------------------------------------------------------------------------ Hessian kernel
 // grid.x = num_edges * tiles; block = 256 threads; each CTA reduces kTilePix pixels of one edge to kAcc floats.
+// ncu on the first version (2048-px tiles, no prefetch) showed it latency-bound, not HBM-bound: long_scoreboard stalls
+// on the dependent record -> gather chain at 25 % occupancy, plus 175 shuffles and a serial edge set-up per 8 pixels of
+// work (profiles/r1_hessian_v1_ncu_full.txt).  This version therefore
+//   * gives every thread kTilePix/256 = 32 pixels (prologue/epilogue amortised 4x),
+//   * software-pipelines the loads two stages deep: edge records are fetched two batches ahead and the point records
+//     (sequential x_j, gathered x_i) one batch ahead of the arithmetic that consumes them,
+//   * reduces 32 of the 35 accumulators with a transposing butterfly (31 shuffles instead of 160).
+struct PixBatch {
+  float4 xj[2], xi[2];
+  int idx[2];
+  float sq[2];
+};
+
+__device__ __forceinline__ void load_recs(const EdgeRec* __restrict__ er, int kb, int k1, int (&idx)[2], float (&sq)[2]) {
+#pragma unroll
+  for (int u = 0; u < 2; u++) {
+    const int k = kb + u * kHessThreads;
+    idx[u] = -1;
+    sq[u] = 0.0f;
+    if (k < k1) {
+      const float2 raw = __ldg(reinterpret_cast<const float2*>(er + k));
+      idx[u] = __float_as_int(raw.x);
+      sq[u] = raw.y;
+    }
+  }
+}
+
+__device__ __forceinline__ void load_points(const float4* __restrict__ xci, const float4* __restrict__ xcj, int kb,
+                                            const int (&idx)[2], const float (&sq)[2], PixBatch& pb) {
+#pragma unroll
+  for (int u = 0; u < 2; u++) {
+    pb.idx[u] = idx[u];
+    pb.sq[u] = sq[u];
+    if (idx[u] >= 0) {
+      pb.xj[u] = __ldg(xcj + kb + u * kHessThreads);
+      pb.xi[u] = __ldg(xci + idx[u]);
+    }
+  }
+}
+
 template <int KIND, int ROBUST>
-__global__ void __launch_bounds__(kHessThreads) hessian_kernel(const float* __restrict__ Twc, const float* __restrict__ K,
-                                                               const float4* __restrict__ xc,
-                                                               const EdgeRec* __restrict__ rec,
-                                                               const int* __restrict__ ie, const int* __restrict__ je,
-                                                               float* __restrict__ partial,
-                                                               const int* __restrict__ state, int num_pts, int tiles,
-                                                               PixParams pp) {
+__global__ void __launch_bounds__(kHessThreads, 2) hessian_kernel(const float* __restrict__ Twc,
+                                                                  const float* __restrict__ K,
+                                                                  const float4* __restrict__ xc,
+                                                                  const EdgeRec* __restrict__ rec,
+                                                                  const int* __restrict__ ie, const int* __restrict__ je,
+                                                                  float* __restrict__ partial,
+                                                                  const int* __restrict__ state, int num_pts, int tiles,
+                                                                  PixParams pp) {
   if (state[kDone]) return;
   const int e = blockIdx.x / tiles;
   const int tile = blockIdx.x - e * tiles;
@@ -240,48 +281,50 @@ __global__ void __launch_bounds__(kHessThreads) hessian_kernel(const float* __re
   for (int i = 0; i < kAcc; i++) acc[i] = 0.0f;
 
   if (ix >= 0 && jx >= 0) {
-    if (threadIdx.x == 0) edge_setup(Twc, ix, jx, KIND == M3R_GN_CALIB ? K : nullptr, &s_c);
-    __syncthreads();
-    const EdgeConst c = s_c;
     const float4* __restrict__ xci = xc + (size_t)ix * num_pts;
     const float4* __restrict__ xcj = xc + (size_t)jx * num_pts;
     const EdgeRec* __restrict__ er = rec + (size_t)e * num_pts;
     const int k0 = tile * kTilePix;
     const int k1 = min(num_pts, k0 + kTilePix);
-    constexpr int U = 4;
-    for (int kb = k0 + threadIdx.x; kb < k1; kb += U * kHessThreads) {
-      EdgeRec r[U];
-      float4 xj[U], xi[U];
+    constexpr int kStep = 2 * kHessThreads;
+    // stage 0: records of the first two batches are in flight while thread 0 builds the edge constants
+    int idx_a[2], idx_b[2];
+    float sq_a[2], sq_b[2];
+    int kb = k0 + threadIdx.x;
+    load_recs(er, kb, k1, idx_a, sq_a);
+    load_recs(er, kb + kStep, k1, idx_b, sq_b);
+    if (threadIdx.x == 0) edge_setup(Twc, ix, jx, KIND == M3R_GN_CALIB ? K : nullptr, &s_c);
+    __syncthreads();
+    const EdgeConst c = s_c;
+    PixBatch cur, nxt;
+    load_points(xci, xcj, kb, idx_a, sq_a, cur);
+    for (; kb < k1; kb += kStep) {
+      // points of the next batch (its records arrived a stage ago), records two batches ahead
+      load_points(xci, xcj, kb + kStep, idx_b, sq_b, nxt);
+      load_recs(er, kb + 2 * kStep, k1, idx_b, sq_b);
 #pragma unroll
-      for (int u = 0; u < U; u++) {
-        const int k = kb + u * kHessThreads;
-        r[u].idx = -1;
-        r[u].sq = 0.0f;
-        if (k < k1) {
-          const float2 raw = __ldg(reinterpret_cast<const float2*>(er + k));
-          r[u].idx = __float_as_int(raw.x);
-          r[u].sq = raw.y;
-        }
-      }
-#pragma unroll
-      for (int u = 0; u < U; u++) {
-        const int k = kb + u * kHessThreads;
-        if (r[u].idx >= 0) {
-          xj[u] = __ldg(xcj + k);
-          xi[u] = __ldg(xci + r[u].idx);
-        }
-      }
-#pragma unroll
-      for (int u = 0; u < U; u++) {
-        if (r[u].idx >= 0) pixel_accumulate<KIND, ROBUST>(acc, c, pp, xi[u], xj[u], r[u].idx, r[u].sq);
-      }
+      for (int u = 0; u < 2; u++)
+        if (cur.idx[u] >= 0) pixel_accumulate<KIND, ROBUST>(acc, c, pp, cur.xi[u], cur.xj[u], cur.idx[u], cur.sq[u]);
+      cur = nxt;
     }
   }
 
-  // warp tree (shuffle) -> shared memory -> one value per thread
+  // ---- block reduction: transposing butterfly for acc[0..31] (lane l ends up with the warp total of acc[l]),
+  //      plain xor-tree for the remaining kAcc-32 values, then 8 warps through shared memory
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
 #pragma unroll
-  for (int i = 0; i < kAcc; i++) {
+  for (int s = 16; s >= 1; s >>= 1) {
+    const bool upper = (lane & s) != 0;
+#pragma unroll
+    for (int i = 0; i < s; i++) {
+      const float send = upper ? acc[i] : acc[i + s];
+      const float keep = upper ? acc[i + s] : acc[i];
+      acc[i] = keep + __shfl_xor_sync(0xffffffffu, send, s);
+    }
+  }
+  s_red[warp][lane] = acc[0];
+#pragma unroll
+  for (int i = 32; i < kAcc; i++) {
     float v = acc[i];
     v += __shfl_xor_sync(0xffffffffu, v, 16);
     v += __shfl_xor_sync(0xffffffffu, v, 8);

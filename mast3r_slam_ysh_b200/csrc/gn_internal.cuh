@@ -7,7 +7,7 @@ namespace m3r {
 constexpr int kPoseDim = 7;          // sim(3) tangent (tau, omega, sigma)
 constexpr int kAcc = 35;             // 28 lower-triangle entries of S = sum w J J^T  +  7 entries of g = sum w e J
 constexpr int kAccStride = 36;       // padded stride of one tile's partial sums
-constexpr int kTilePix = 2048;       // pixels of one edge handled by one CTA of the Hessian kernel
+constexpr int kTilePix = 8192;       // pixels of one edge handled by one CTA of the Hessian kernel (32 per thread)
 constexpr int kHessThreads = 256;
 constexpr int kBlk = 32;             // Cholesky block size
 constexpr int kBlockDoubles = 56;    // per-edge block: M (7x7 row-major) + v (7)
