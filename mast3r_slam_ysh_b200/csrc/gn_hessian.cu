@@ -240,7 +240,7 @@ __device__ __forceinline__ void load_recs(const EdgeRec* __restrict__ er, int kb
     idx[u] = -1;
     sq[u] = 0.0f;
     if (k < k1) {
-      const float2 raw = __ldg(reinterpret_cast<const float2*>(er + k));
+      const float2 raw = __ldcs(reinterpret_cast<const float2*>(er + k));  // streamed once: evict-first in L2
       idx[u] = __float_as_int(raw.x);
       sq[u] = raw.y;
     }

@@ -28,7 +28,7 @@ struct __align__(8) EdgeRec {
 struct GnLayout {
   int num_kf, num_pts, num_edges, n_free, n, ld, nblk, tiles;
   size_t off_xc, off_rec, off_ie, off_je, off_io, off_jo, off_partial, off_blocks, off_inc_off, off_inc_list, off_sys,
-      off_lfac, off_dx, off_state, off_uniq_flag, off_all, off_K, total;
+      off_lfac, off_pflag, off_dx, off_state, off_uniq_flag, off_all, off_K, total;
 };
 
 GnLayout gn_layout(int num_kf, int num_pts, int num_edges, int num_all_edges);
@@ -46,6 +46,7 @@ struct GnWs {
   int* inc_list() const { return (int*)(base + L.off_inc_list); }
   double* sys() const { return (double*)(base + L.off_sys); }
   double* lfac() const { return (double*)(base + L.off_lfac); }
+  int* pflag() const { return (int*)(base + L.off_pflag); }
   float* dx() const { return (float*)(base + L.off_dx); }
   int* state() const { return (int*)(base + L.off_state); }
   int* uniq_flag() const { return (int*)(base + L.off_uniq_flag); }

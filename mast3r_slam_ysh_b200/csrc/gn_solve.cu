@@ -173,7 +173,8 @@ __device__ __forceinline__ double shfl_d(double v, int src) {
 constexpr int kPanelRows = 64;
 
 __global__ void __launch_bounds__(kPanelRows) panel_kernel(double* __restrict__ sys, double* __restrict__ lfac,
-                                                          int* __restrict__ state, int n, int ld, int kb) {
+                                                          int* __restrict__ state, int* __restrict__ pflag, int n,
+                                                          int ld, int kb) {
   if (state[kDone]) return;
   __shared__ double sL[kBlk][kBlk + 1];
   __shared__ double sInv[kBlk];
@@ -194,8 +195,8 @@ __global__ void __launch_bounds__(kPanelRows) panel_kernel(double* __restrict__ 
     for (int j = 0; j < kBlk; j++) {
       const double djj = shfl_d(a[j], j);
       if (!(djj > 0.0)) bad = true;  // also catches NaN
-      const double dj = sqrt(djj);
-      const double inv = 1.0 / dj;
+      const double inv = rsqrt(djj);  // one MUFU + Newton instead of sqrt + divide on the serial chain
+      const double dj = djj * inv;
       const double l = (lane == j) ? dj : a[j] * inv;  // column j of L (valid for lane >= j)
       a[j] = l;
       if (lane == 0) sInv[j] = inv;
@@ -217,11 +218,16 @@ __global__ void __launch_bounds__(kPanelRows) panel_kernel(double* __restrict__ 
   __syncthreads();
   // rows below the (valid part of the) diagonal block handled by this CTA; row n is the right-hand side
   const int row = c0 + nb + blockIdx.x * kPanelRows + threadIdx.x;
+  int nonzero = 0;
   if (row <= n && nb == kBlk) {
     double x[kBlk];
     double* src = sys + (size_t)row * ld + c0;
 #pragma unroll
-    for (int c = 0; c < kBlk; c++) x[c] = src[c];
+    for (int c = 0; c < kBlk; c++) {
+      x[c] = src[c];
+      nonzero |= (x[c] != 0.0);
+    }
+    if (nonzero) {
 #pragma unroll
     for (int j = 0; j < kBlk; j++) {
       const double xj = x[j] * sInv[j];
@@ -231,7 +237,9 @@ __global__ void __launch_bounds__(kPanelRows) panel_kernel(double* __restrict__ 
     }
 #pragma unroll
     for (int c = 0; c < kBlk; c++) src[c] = x[c];
+    }
   } else if (row <= n) {  // last, partial block column: only the rhs row can be below it
+    nonzero = 1;
     double* src = sys + (size_t)row * ld + c0;
     for (int j = 0; j < nb; j++) {
       const double xj = src[j] * sInv[j];
@@ -239,20 +247,25 @@ __global__ void __launch_bounds__(kPanelRows) panel_kernel(double* __restrict__ 
       for (int c = j + 1; c < nb; c++) src[c] -= xj * sL[c][j];
     }
   }
+  // block-sparsity flag of this 64-row tile of the panel: an all-zero tile stays zero through the TRSM and makes
+  // every trailing-update tile that would use it a no-op (0 - 0*x), so update CTAs can exit early
+  const int any_nz = __syncthreads_or(nonzero);
+  if (threadIdx.x == 0) pflag[blockIdx.x] = any_nz;
 }
 
 constexpr int kUpdTile = 64;
 
 // C[r][c] -= sum_k X[r][k] X[c][k], r in row tile, c in col tile, tiles on/below the diagonal of the trailing
 // matrix that starts at t0 = (kb+1)*32.  256 threads, 4x4 outputs each.
-__global__ void __launch_bounds__(256) update_kernel(double* __restrict__ sys, const int* __restrict__ state, int n,
-                                                     int ld, int kb) {
+__global__ void __launch_bounds__(256) update_kernel(double* __restrict__ sys, const int* __restrict__ state,
+                                                     const int* __restrict__ pflag, int n, int ld, int kb) {
   if (state[kDone]) return;
   // map linear block id -> (tr, tc) with tc <= tr
   int tr = (int)((sqrtf(8.0f * (float)blockIdx.x + 1.0f) - 1.0f) * 0.5f);
   while ((tr + 1) * (tr + 2) / 2 <= (int)blockIdx.x) tr++;
   while (tr * (tr + 1) / 2 > (int)blockIdx.x) tr--;
   const int tc = blockIdx.x - tr * (tr + 1) / 2;
+  if (pflag[tr] == 0 || pflag[tc] == 0) return;  // structurally zero panel tile: nothing to subtract
   const int c0 = kb * kBlk;
   const int t0 = c0 + kBlk;
   const int r_base = t0 + tr * kUpdTile, c_base = t0 + tc * kUpdTile;
@@ -544,11 +557,11 @@ int launch_cholesky(const GnWs& ws, cudaStream_t st) {
     const int rb = (kb + 1) * kBlk < n ? (kb + 1) * kBlk : n;
     const int rows_below = n + 1 - rb;  // rows rb .. n (row n = rhs), always >= 1
     const int pgrid = ceil_div(rows_below, kPanelRows);
-    panel_kernel<<<pgrid, kPanelRows, 0, st>>>(ws.sys(), ws.lfac(), ws.state(), n, ld, kb);
+    panel_kernel<<<pgrid, kPanelRows, 0, st>>>(ws.sys(), ws.lfac(), ws.state(), ws.pflag(), n, ld, kb);
     M3R_LAUNCH_CHECK();
     if ((kb + 1) * kBlk < n) {
       const int T = ceil_div(rows_below, kUpdTile);
-      update_kernel<<<T * (T + 1) / 2, 256, 0, st>>>(ws.sys(), ws.state(), n, ld, kb);
+      update_kernel<<<T * (T + 1) / 2, 256, 0, st>>>(ws.sys(), ws.state(), ws.pflag(), n, ld, kb);
       M3R_LAUNCH_CHECK();
     }
   }
