@@ -63,12 +63,16 @@ GnLayout gn_layout(int num_kf, int num_pts, int num_edges, int num_all_edges) {
   L.off_all = take(sizeof(long long) * (2 * Ea + 2));
   L.off_uniq_flag = take(sizeof(int) * (2 * Ea + 2));
   L.off_blocks = take(sizeof(double) * kBlockDoubles * (E + 1));
-  L.off_partial = take(sizeof(float) * kAccStride * (E * (size_t)L.tiles + 1));
+  L.off_partial = take(sizeof(float) * kAccStride * (E + kMaxHessCtas + 1));
+  L.off_ecount = take(sizeof(int) * (E + 1));
+  L.off_eoff = take(sizeof(long long) * (E + 2));
+  L.off_tstate = take(sizeof(int) * (E * (size_t)L.tiles + 2));
   L.off_sys = take(sizeof(double) * (size_t)L.ld * (size_t)(L.n + 1));
   L.off_lfac = take(sizeof(double) * kBlk * kBlk * (size_t)(L.nblk + 1));
   L.off_pflag = take(sizeof(int) * (size_t)(L.n / 64 + 4));
   L.off_xc = take(sizeof(float4) * (size_t)num_kf * (size_t)num_pts);
   L.off_rec = take(sizeof(EdgeRec) * E * (size_t)num_pts);
+  L.off_sqv = take(sizeof(float) * E * (size_t)num_pts);
   L.total = o;
   return L;
 }

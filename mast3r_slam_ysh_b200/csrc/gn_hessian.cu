@@ -23,29 +23,148 @@ __global__ void __launch_bounds__(256) pack_points_kernel(const float* __restric
   xc[p] = make_float4(__ldg(Xs + 3 * p), __ldg(Xs + 3 * p + 1), __ldg(Xs + 3 * p + 2), __ldg(Cs + p));
 }
 
+// Gate + compact.  One CTA per (edge, 8192-pixel tile); work items are handed out by a ticket so that the owners of
+// the earlier tiles of an edge are guaranteed to be running (or finished) when a CTA looks back at them.
+//   phase 1: every warp walks 1024 consecutive pixels (coalesced), evaluates the pose-independent gates and parks the
+//            match index (or -1) in shared memory; survivors are counted with ballots.  The 8-byte index is only
+//            fetched where valid_match and the Q gate pass, so whole sectors of it are never read outside the overlap
+//            region of the two frames.
+//   scan   : the CTA publishes its own count at once, then warp 0 sums the counts of the earlier tiles of the same edge
+//            (decoupled look-back: nobody waits on a chain, only on each predecessor's phase 1).
+//   phase 2: warps re-walk their pixels and write the survivors, in pixel order, to rec/sqv at the scanned offset.
+__device__ __forceinline__ int ld_acquire(const int* p) {
+  int v;
+  asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_release(int* p, int v) {
+  asm volatile("st.release.gpu.global.s32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+
 __global__ void __launch_bounds__(256) pack_edges_kernel(const float* __restrict__ Cs, const int64_t* __restrict__ idx,
                                                          const uint8_t* __restrict__ valid, const float* __restrict__ Q,
                                                          const int* __restrict__ ie, const int* __restrict__ je,
-                                                         EdgeRec* __restrict__ rec, int num_pts, long long total,
-                                                         float C_thresh, float Q_thresh) {
-  const long long g = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-  if (g >= total) return;
-  const int e = (int)(g / num_pts);
-  const int k = (int)(g - (long long)e * num_pts);
+                                                         EdgeRec* __restrict__ rec, float* __restrict__ sqv,
+                                                         int* __restrict__ ecount, int* __restrict__ tstate,
+                                                         int num_pts, int tiles, float C_thresh, float Q_thresh) {
+  __shared__ int s_idx[kTilePix];
+  __shared__ int s_work, s_base, s_wcnt[8];
+  if (threadIdx.x == 0) s_work = atomicAdd(&tstate[0], 1);
+  __syncthreads();
+  const int work = s_work;
+  const int e = work / tiles, tile = work - e * tiles;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int ix = ie[e], jx = je[e];
-  EdgeRec r;
-  r.idx = -1;
-  const float q = __ldg(Q + g);
-  r.sq = sqrtf(q);
-  if (ix >= 0 && jx >= 0 && valid[g]) {
-    const long long ind = idx[g];
-    if (ind >= 0 && ind < num_pts) {
-      const float ci = __ldg(Cs + (size_t)ix * num_pts + ind);
-      const float cj = __ldg(Cs + (size_t)jx * num_pts + k);
-      if ((q > Q_thresh) & (ci > C_thresh) & (cj > C_thresh)) r.idx = (int)ind;
+  const bool edge_ok = ix >= 0 && jx >= 0;
+  const int kw = tile * kTilePix + warp * 1024;  // first pixel of this warp
+  const size_t eb = (size_t)e * num_pts;
+  const float* __restrict__ Ci = Cs + (size_t)(edge_ok ? ix : 0) * num_pts;
+  const float* __restrict__ Cj = Cs + (size_t)(edge_ok ? jx : 0) * num_pts;
+  const long long* __restrict__ idx_e = reinterpret_cast<const long long*>(idx) + eb;
+  int cnt = 0;
+  constexpr int kU = 8;
+  for (int it0 = 0; it0 < 32; it0 += kU) {
+    float q[kU];
+    uint8_t vm[kU];
+    long long ind[kU];
+    float ci[kU], cj[kU];
+#pragma unroll
+    for (int u = 0; u < kU; u++) {
+      const int k = kw + (it0 + u) * 32 + lane;
+      const bool in = edge_ok && k < num_pts;
+      q[u] = in ? __ldg(Q + eb + k) : 0.0f;  // re-read in phase 2: keep it in L2
+      vm[u] = in ? __ldcs(valid + eb + k) : (uint8_t)0;
+    }
+#pragma unroll
+    for (int u = 0; u < kU; u++) {
+      const int k = kw + (it0 + u) * 32 + lane;
+      ind[u] = (vm[u] && q[u] > Q_thresh) ? __ldcs(idx_e + k) : -1;
+    }
+#pragma unroll
+    for (int u = 0; u < kU; u++) {
+      const int k = kw + (it0 + u) * 32 + lane;
+      const bool ok = ind[u] >= 0 && ind[u] < num_pts;
+      ci[u] = ok ? __ldg(Ci + ind[u]) : 0.0f;
+      cj[u] = ok ? __ldg(Cj + k) : 0.0f;
+      if (!ok) ind[u] = -1;
+    }
+#pragma unroll
+    for (int u = 0; u < kU; u++) {
+      const int id = (ind[u] >= 0 && ci[u] > C_thresh && cj[u] > C_thresh) ? (int)ind[u] : -1;
+      s_idx[warp * 1024 + (it0 + u) * 32 + lane] = id;
+      cnt += __popc(__ballot_sync(0xffffffffu, id >= 0));
     }
   }
-  rec[g] = r;
+  if (lane == 0) s_wcnt[warp] = cnt;
+  __syncthreads();
+  if (warp == 0) {
+    int run = 0;
+    if (lane == 0) {
+#pragma unroll
+      for (int wv = 0; wv < 8; wv++) {
+        const int c = s_wcnt[wv];
+        s_wcnt[wv] = run;
+        run += c;
+      }
+      st_release(&tstate[1 + work], run + 1);  // own count, visible before anyone needs it
+    }
+    int before = 0;
+    for (int t = lane; t < tile; t += 32) {  // counts of the earlier tiles of this edge
+      int v;
+      while ((v = ld_acquire(&tstate[1 + work - tile + t])) == 0) __nanosleep(32);
+      before += v - 1;
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) before += __shfl_xor_sync(0xffffffffu, before, o);
+    if (lane == 0) {
+      s_base = before;
+      if (tile == tiles - 1) ecount[e] = before + run;
+    }
+  }
+  __syncthreads();
+  int wbase = s_base + s_wcnt[warp];
+  const unsigned lt = (1u << lane) - 1u;
+#pragma unroll 4
+  for (int it = 0; it < 32; it++) {
+    const int id = s_idx[warp * 1024 + it * 32 + lane];
+    const unsigned bal = __ballot_sync(0xffffffffu, id >= 0);
+    if (id >= 0) {
+      const int k = kw + it * 32 + lane;
+      const int pos = wbase + __popc(bal & lt);
+      rec[eb + pos] = make_int2(id, k);
+      sqv[eb + pos] = sqrtf(__ldcs(Q + eb + k));
+    }
+    wbase += __popc(bal);
+  }
+}
+
+// eoff[e] = sum of ecount[0..e) (long long: E*N can exceed 2^31).  Single CTA; E is a few thousand at most.
+__global__ void __launch_bounds__(1024) edge_offsets_kernel(const int* __restrict__ ecount, long long* __restrict__ eoff,
+                                                            int num_edges) {
+  __shared__ long long s_part[1024];
+  const int per = (num_edges + 1023) / 1024;
+  const int b = threadIdx.x * per;
+  long long sum = 0;
+  for (int i = 0; i < per; i++)
+    if (b + i < num_edges) sum += ecount[b + i];
+  s_part[threadIdx.x] = sum;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    long long run = 0;
+    for (int i = 0; i < 1024; i++) {
+      const long long c = s_part[i];
+      s_part[i] = run;
+      run += c;
+    }
+    eoff[num_edges] = run;
+  }
+  __syncthreads();
+  long long run = s_part[threadIdx.x];
+  for (int i = 0; i < per; i++)
+    if (b + i < num_edges) {
+      eoff[b + i] = run;
+      run += ecount[b + i];
+    }
 }
 
 // ------------------------------------------------------------------------------------------------ robust weights
@@ -137,6 +256,12 @@ __device__ void edge_setup(const float* __restrict__ Twc, int ix, int jx, const 
   }
 }
 
+// records per CTA of the persistent Hessian kernel (same formula in the kernel and in finalize_edges_kernel)
+__host__ __device__ __forceinline__ long long hess_chunk(long long V, int grid) {
+  const long long c = (V + grid - 1) / grid;
+  return (c + kHessChunkAlign - 1) / kHessChunkAlign * kHessChunkAlign;
+}
+
 struct PixParams {
   float sa_inv, sb_inv;  // 1/sigma_a, 1/sigma_b
   int width, height, pixel_border;
@@ -219,43 +344,50 @@ __device__ __forceinline__ void pixel_accumulate(float (&acc)[kAcc], const EdgeC
 }
 
 // ------------------------------------------------------------------------------------------------ Hessian kernel
-// grid.x = num_edges * tiles; block = 256 threads; each CTA reduces kTilePix pixels of one edge to kAcc floats.
-// ncu on the first version (2048-px tiles, no prefetch) showed it latency-bound, not HBM-bound: long_scoreboard stalls
-// on the dependent record -> gather chain at 25 % occupancy, plus 175 shuffles and a serial edge set-up per 8 pixels of
-// work (profiles/r1_hessian_v1_ncu_full.txt).  This version therefore
-//   * gives every thread kTilePix/256 = 32 pixels (prologue/epilogue amortised 4x),
-//   * software-pipelines the loads two stages deep: edge records are fetched two batches ahead and the point records
-//     (sequential x_j, gathered x_i) one batch ahead of the arithmetic that consumes them,
-//   * reduces 32 of the 35 accumulators with a transposing butterfly (31 shuffles instead of 160).
+// Persistent, stream-K style: the V = sum_e ecount[e] compacted records of all edges form one flat list; CTA c of a
+// grid of 2 CTAs per SM owns the records [c*chunk, (c+1)*chunk), chunk = V/grid rounded up to 512.  A CTA walks the
+// (at most a few) edge segments inside its range; per segment it builds the edge constants once, streams the records
+// through a two-stage software pipeline (records two batches ahead, the gathered points one batch ahead of the
+// arithmetic), and reduces its 35 accumulators once: transposing butterfly across lanes (31 shuffles for 32 values),
+// shared memory across the 8 warps.  The partial sums of segment (e, c) go to slot e + c, which is unique because
+// consecutive segments advance e, c or both; finalize_edges_kernel sums an edge's slots in fixed order (no atomics).
+// History (profiles/): v1 one CTA per 2048-px tile, latency-bound at 25 % occupancy; v2 8192-px tiles + pipelined
+// loads; v3 (this) drops gated-out pixels in the pre-pass (40-50 % of the lanes idled in v2) and amortises the serial
+// edge set-up, pipeline prologue and block reduction over ~1e5 records per CTA instead of 8192 pixels.
 struct PixBatch {
   float4 xj[2], xi[2];
   int idx[2];
   float sq[2];
 };
 
-__device__ __forceinline__ void load_recs(const EdgeRec* __restrict__ er, int kb, int k1, int (&idx)[2], float (&sq)[2]) {
+struct RecBatch {
+  int2 r[2];
+  float sq[2];
+};
+
+__device__ __forceinline__ void load_recs(const EdgeRec* __restrict__ er, const float* __restrict__ es, int kb, int k1,
+                                          RecBatch& rb) {
 #pragma unroll
   for (int u = 0; u < 2; u++) {
     const int k = kb + u * kHessThreads;
-    idx[u] = -1;
-    sq[u] = 0.0f;
+    rb.r[u] = make_int2(-1, 0);
+    rb.sq[u] = 0.0f;
     if (k < k1) {
-      const float2 raw = __ldcs(reinterpret_cast<const float2*>(er + k));  // streamed once: evict-first in L2
-      idx[u] = __float_as_int(raw.x);
-      sq[u] = raw.y;
+      rb.r[u] = __ldcs(er + k);  // streamed once per iteration: evict-first in L2
+      rb.sq[u] = __ldcs(es + k);
     }
   }
 }
 
-__device__ __forceinline__ void load_points(const float4* __restrict__ xci, const float4* __restrict__ xcj, int kb,
-                                            const int (&idx)[2], const float (&sq)[2], PixBatch& pb) {
+__device__ __forceinline__ void load_points(const float4* __restrict__ xci, const float4* __restrict__ xcj,
+                                            const RecBatch& rb, PixBatch& pb) {
 #pragma unroll
   for (int u = 0; u < 2; u++) {
-    pb.idx[u] = idx[u];
-    pb.sq[u] = sq[u];
-    if (idx[u] >= 0) {
-      pb.xj[u] = __ldg(xcj + kb + u * kHessThreads);
-      pb.xi[u] = __ldg(xci + idx[u]);
+    pb.idx[u] = rb.r[u].x;
+    pb.sq[u] = rb.sq[u];
+    if (rb.r[u].x >= 0) {
+      pb.xj[u] = __ldg(xcj + rb.r[u].y);
+      pb.xi[u] = __ldg(xci + rb.r[u].x);
     }
   }
 }
@@ -265,91 +397,117 @@ __global__ void __launch_bounds__(kHessThreads, 2) hessian_kernel(const float* _
                                                                   const float* __restrict__ K,
                                                                   const float4* __restrict__ xc,
                                                                   const EdgeRec* __restrict__ rec,
+                                                                  const float* __restrict__ sqv,
+                                                                  const long long* __restrict__ eoff,
                                                                   const int* __restrict__ ie, const int* __restrict__ je,
                                                                   float* __restrict__ partial,
-                                                                  const int* __restrict__ state, int num_pts, int tiles,
-                                                                  PixParams pp) {
+                                                                  const int* __restrict__ state, int num_pts,
+                                                                  int num_edges, PixParams pp) {
   if (state[kDone]) return;
-  const int e = blockIdx.x / tiles;
-  const int tile = blockIdx.x - e * tiles;
-  const int ix = ie[e], jx = je[e];
+  const long long V = eoff[num_edges];
+  const long long chunk = hess_chunk(V, gridDim.x);
+  long long p = (long long)blockIdx.x * chunk;
+  const long long p_end = min(V, p + chunk);
+  if (p >= p_end) return;
   __shared__ EdgeConst s_c;
+  __shared__ int s_e;
   __shared__ float s_red[kHessThreads / 32][kAccStride];
-
-  float acc[kAcc];
-#pragma unroll
-  for (int i = 0; i < kAcc; i++) acc[i] = 0.0f;
-
-  if (ix >= 0 && jx >= 0) {
-    const float4* __restrict__ xci = xc + (size_t)ix * num_pts;
-    const float4* __restrict__ xcj = xc + (size_t)jx * num_pts;
-    const EdgeRec* __restrict__ er = rec + (size_t)e * num_pts;
-    const int k0 = tile * kTilePix;
-    const int k1 = min(num_pts, k0 + kTilePix);
-    constexpr int kStep = 2 * kHessThreads;
-    // stage 0: records of the first two batches are in flight while thread 0 builds the edge constants
-    int idx_a[2], idx_b[2];
-    float sq_a[2], sq_b[2];
-    int kb = k0 + threadIdx.x;
-    load_recs(er, kb, k1, idx_a, sq_a);
-    load_recs(er, kb + kStep, k1, idx_b, sq_b);
-    if (threadIdx.x == 0) edge_setup(Twc, ix, jx, KIND == M3R_GN_CALIB ? K : nullptr, &s_c);
-    __syncthreads();
-    const EdgeConst c = s_c;
-    PixBatch cur, nxt;
-    load_points(xci, xcj, kb, idx_a, sq_a, cur);
-    for (; kb < k1; kb += kStep) {
-      // points of the next batch (its records arrived a stage ago), records two batches ahead
-      load_points(xci, xcj, kb + kStep, idx_b, sq_b, nxt);
-      load_recs(er, kb + 2 * kStep, k1, idx_b, sq_b);
-#pragma unroll
-      for (int u = 0; u < 2; u++)
-        if (cur.idx[u] >= 0) pixel_accumulate<KIND, ROBUST>(acc, c, pp, cur.xi[u], cur.xj[u], cur.idx[u], cur.sq[u]);
-      cur = nxt;
-    }
-  }
-
-  // ---- block reduction: transposing butterfly for acc[0..31] (lane l ends up with the warp total of acc[l]),
-  //      plain xor-tree for the remaining kAcc-32 values, then 8 warps through shared memory
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-#pragma unroll
-  for (int s = 16; s >= 1; s >>= 1) {
-    const bool upper = (lane & s) != 0;
-#pragma unroll
-    for (int i = 0; i < s; i++) {
-      const float send = upper ? acc[i] : acc[i + s];
-      const float keep = upper ? acc[i + s] : acc[i];
-      acc[i] = keep + __shfl_xor_sync(0xffffffffu, send, s);
+  int e = -1;
+  while (p < p_end) {
+    // ---- next segment: thread 0 finds the edge that owns record p (binary search once, then a forward walk over
+    //      empty edges) and builds the edge constants
+    if (threadIdx.x == 0) {
+      int en;
+      if (e < 0) {
+        int lo = 0, hi = num_edges - 1;  // last edge with eoff[edge] <= p
+        while (lo < hi) {
+          const int mid = (lo + hi + 1) >> 1;
+          if (eoff[mid] <= p) lo = mid; else hi = mid - 1;
+        }
+        en = lo;
+      } else {
+        en = e + 1;
+      }
+      while (eoff[en + 1] <= p) en++;
+      s_e = en;
+      edge_setup(Twc, ie[en], je[en], KIND == M3R_GN_CALIB ? K : nullptr, &s_c);
     }
-  }
-  s_red[warp][lane] = acc[0];
+    __syncthreads();
+    e = s_e;
+    const EdgeConst c = s_c;
+    const long long e0 = eoff[e];
+    const long long seg_end = min(p_end, eoff[e + 1]);
+    const int k1 = (int)(seg_end - e0);
+    const float4* __restrict__ xci = xc + (size_t)ie[e] * num_pts;
+    const float4* __restrict__ xcj = xc + (size_t)je[e] * num_pts;
+    const EdgeRec* __restrict__ er = rec + (size_t)e * num_pts;
+    const float* __restrict__ es = sqv + (size_t)e * num_pts;
+
+    float acc[kAcc];
 #pragma unroll
-  for (int i = 32; i < kAcc; i++) {
-    float v = acc[i];
-    v += __shfl_xor_sync(0xffffffffu, v, 16);
-    v += __shfl_xor_sync(0xffffffffu, v, 8);
-    v += __shfl_xor_sync(0xffffffffu, v, 4);
-    v += __shfl_xor_sync(0xffffffffu, v, 2);
-    v += __shfl_xor_sync(0xffffffffu, v, 1);
-    if (lane == 0) s_red[warp][i] = v;
-  }
-  __syncthreads();
-  if (threadIdx.x < kAcc) {
-    float v = 0.0f;
+    for (int i = 0; i < kAcc; i++) acc[i] = 0.0f;
+    {
+      constexpr int kStep = 2 * kHessThreads;
+      int kb = (int)(p - e0) + threadIdx.x;
+      RecBatch ra, rb;
+      load_recs(er, es, kb, k1, ra);
+      load_recs(er, es, kb + kStep, k1, rb);
+      PixBatch cur, nxt;
+      load_points(xci, xcj, ra, cur);
+      for (; kb < k1; kb += kStep) {
+        load_points(xci, xcj, rb, nxt);
+        load_recs(er, es, kb + 2 * kStep, k1, rb);
 #pragma unroll
-    for (int wv = 0; wv < kHessThreads / 32; wv++) v += s_red[wv][threadIdx.x];
-    partial[(size_t)blockIdx.x * kAccStride + threadIdx.x] = v;
+        for (int u = 0; u < 2; u++)
+          if (cur.idx[u] >= 0) pixel_accumulate<KIND, ROBUST>(acc, c, pp, cur.xi[u], cur.xj[u], cur.idx[u], cur.sq[u]);
+        cur = nxt;
+      }
+    }
+    // ---- block reduction: transposing butterfly for acc[0..31] (lane l ends up with the warp total of acc[l]),
+    //      plain xor-tree for the remaining kAcc-32 values, then 8 warps through shared memory
+#pragma unroll
+    for (int s = 16; s >= 1; s >>= 1) {
+      const bool upper = (lane & s) != 0;
+#pragma unroll
+      for (int i = 0; i < s; i++) {
+        const float send = upper ? acc[i] : acc[i + s];
+        const float keep = upper ? acc[i + s] : acc[i];
+        acc[i] = keep + __shfl_xor_sync(0xffffffffu, send, s);
+      }
+    }
+    s_red[warp][lane] = acc[0];
+#pragma unroll
+    for (int i = 32; i < kAcc; i++) {
+      float v = acc[i];
+      v += __shfl_xor_sync(0xffffffffu, v, 16);
+      v += __shfl_xor_sync(0xffffffffu, v, 8);
+      v += __shfl_xor_sync(0xffffffffu, v, 4);
+      v += __shfl_xor_sync(0xffffffffu, v, 2);
+      v += __shfl_xor_sync(0xffffffffu, v, 1);
+      if (lane == 0) s_red[warp][i] = v;
+    }
+    __syncthreads();
+    if (threadIdx.x < kAcc) {
+      float v = 0.0f;
+#pragma unroll
+      for (int wv = 0; wv < kHessThreads / 32; wv++) v += s_red[wv][threadIdx.x];
+      partial[(size_t)(e + (int)blockIdx.x) * kAccStride + threadIdx.x] = v;
+    }
+    p = seg_end;
   }
 }
 
 // ------------------------------------------------------------------------------------------------ per-edge finalize
-// One warp per edge: sum the tile partials in fp64 (fixed order), M = A S A^T, v = A g with
+// One warp per edge: sum the partials of the edge's segments in fp64 (fixed order), M = A S A^T, v = A g with
 // A = [[R/s, 0, 0], [[t]x R/s, R, 0], [t^T R/s, 0, 1]] -- the matrix of apply_Sim3_adj_inv(T_i) (gn_kernels.cu:277-297).
 __global__ void __launch_bounds__(128) finalize_edges_kernel(const float* __restrict__ Twc,
                                                              const float* __restrict__ partial,
+                                                             const long long* __restrict__ eoff,
                                                              const int* __restrict__ ie, const int* __restrict__ je,
                                                              double* __restrict__ blocks,
-                                                             const int* __restrict__ state, int num_edges, int tiles) {
+                                                             const int* __restrict__ state, int num_edges,
+                                                             int hess_grid) {
   if (state[kDone]) return;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int e = blockIdx.x * 4 + warp;
@@ -362,10 +520,15 @@ __global__ void __launch_bounds__(128) finalize_edges_kernel(const float* __rest
     return;
   }
   double s0 = 0.0, s1 = 0.0;
-  const float* p = partial + (size_t)e * tiles * kAccStride;
-  for (int t = 0; t < tiles; t++) {
-    s0 += (double)p[(size_t)t * kAccStride + lane];
-    if (lane < kAcc - 32) s1 += (double)p[(size_t)t * kAccStride + 32 + lane];
+  const long long b0 = eoff[e], b1 = eoff[e + 1];
+  if (b1 > b0) {  // segments (e, c) for the CTAs c whose record range intersects [b0, b1): slot e + c
+    const long long chunk = hess_chunk(eoff[num_edges], hess_grid);
+    const int c_first = (int)(b0 / chunk), c_last = (int)((b1 - 1) / chunk);
+    for (int c = c_first; c <= c_last; c++) {
+      const float* p = partial + (size_t)(e + c) * kAccStride;
+      s0 += (double)p[lane];
+      if (lane < kAcc - 32) s1 += (double)p[32 + lane];
+    }
   }
   // scatter into symmetric S and g
   {
@@ -461,12 +624,23 @@ int launch_pack_points(const GnWs& ws, const float* Xs, const float* Cs, cudaStr
 
 int launch_pack_edges(const GnWs& ws, const m3r_gn_params& p, const float* Cs, const int64_t* idx, const uint8_t* valid,
                       const float* Q, cudaStream_t st) {
-  const long long total = (long long)ws.L.num_edges * ws.L.num_pts;
-  if (total == 0) return M3R_OK;
-  pack_edges_kernel<<<(unsigned)ceil_div_ll(total, 256), 256, 0, st>>>(Cs, idx, valid, Q, ws.ie(), ws.je(), ws.rec(),
-                                                                       ws.L.num_pts, total, p.C_thresh, p.Q_thresh);
+  const int E = ws.L.num_edges, tiles = ws.L.tiles;
+  M3R_CUDA(cudaMemsetAsync(ws.ecount(), 0, sizeof(int) * (size_t)(E + 1), st));
+  if (E > 0 && tiles > 0) {
+    M3R_CUDA(cudaMemsetAsync(ws.tstate(), 0, sizeof(int) * ((size_t)E * tiles + 2), st));
+    pack_edges_kernel<<<(unsigned)((long long)E * tiles), 256, 0, st>>>(Cs, idx, valid, Q, ws.ie(), ws.je(), ws.rec(),
+                                                                          ws.sqv(), ws.ecount(), ws.tstate(),
+                                                                          ws.L.num_pts, tiles, p.C_thresh, p.Q_thresh);
+    M3R_LAUNCH_CHECK();
+  }
+  edge_offsets_kernel<<<1, 1024, 0, st>>>(ws.ecount(), ws.eoff(), E);
   M3R_LAUNCH_CHECK();
   return M3R_OK;
+}
+
+int hessian_grid() {
+  const int g = 2 * sm_count();
+  return g < kMaxHessCtas ? g : kMaxHessCtas;
 }
 
 template <int KIND>
@@ -478,14 +652,16 @@ static int launch_hessian_kind(const GnWs& ws, const m3r_gn_params& p, const flo
   pp.height = p.height;
   pp.pixel_border = p.pixel_border;
   pp.z_eps = p.z_eps;
-  const unsigned grid = (unsigned)((long long)ws.L.num_edges * ws.L.tiles);
-  if (grid == 0) return M3R_OK;
+  if (ws.L.num_edges == 0 || ws.L.num_pts == 0) return M3R_OK;
+  const unsigned grid = (unsigned)hessian_grid();
   if (p.robust == M3R_ROBUST_TUKEY)
     hessian_kernel<KIND, M3R_ROBUST_TUKEY><<<grid, kHessThreads, 0, st>>>(
-        Twc, ws.Kdev(), ws.xc(), ws.rec(), ws.ie(), ws.je(), ws.partial(), ws.state(), ws.L.num_pts, ws.L.tiles, pp);
+        Twc, ws.Kdev(), ws.xc(), ws.rec(), ws.sqv(), ws.eoff(), ws.ie(), ws.je(), ws.partial(), ws.state(), ws.L.num_pts,
+        ws.L.num_edges, pp);
   else
     hessian_kernel<KIND, M3R_ROBUST_HUBER><<<grid, kHessThreads, 0, st>>>(
-        Twc, ws.Kdev(), ws.xc(), ws.rec(), ws.ie(), ws.je(), ws.partial(), ws.state(), ws.L.num_pts, ws.L.tiles, pp);
+        Twc, ws.Kdev(), ws.xc(), ws.rec(), ws.sqv(), ws.eoff(), ws.ie(), ws.je(), ws.partial(), ws.state(), ws.L.num_pts,
+        ws.L.num_edges, pp);
   M3R_LAUNCH_CHECK();
   return M3R_OK;
 }
@@ -502,8 +678,9 @@ int launch_hessian(const GnWs& ws, const m3r_gn_params& p, const float* Twc, cud
 
 int launch_finalize_edges(const GnWs& ws, const float* Twc, cudaStream_t st) {
   if (ws.L.num_edges == 0) return M3R_OK;
-  finalize_edges_kernel<<<ceil_div(ws.L.num_edges, 4), 128, 0, st>>>(Twc, ws.partial(), ws.ie(), ws.je(), ws.blocks(),
-                                                                      ws.state(), ws.L.num_edges, ws.L.tiles);
+  finalize_edges_kernel<<<ceil_div(ws.L.num_edges, 4), 128, 0, st>>>(Twc, ws.partial(), ws.eoff(), ws.ie(), ws.je(),
+                                                                      ws.blocks(), ws.state(), ws.L.num_edges,
+                                                                      hessian_grid());
   M3R_LAUNCH_CHECK();
   return M3R_OK;
 }

@@ -7,27 +7,26 @@ namespace m3r {
 constexpr int kPoseDim = 7;          // sim(3) tangent (tau, omega, sigma)
 constexpr int kAcc = 35;             // 28 lower-triangle entries of S = sum w J J^T  +  7 entries of g = sum w e J
 constexpr int kAccStride = 36;       // padded stride of one tile's partial sums
-constexpr int kTilePix = 8192;       // pixels of one edge handled by one CTA of the Hessian kernel (32 per thread)
+constexpr int kTilePix = 8192;       // pixels of one edge compacted by one CTA of the packing pre-pass (32 per thread)
 constexpr int kHessThreads = 256;
+constexpr int kHessChunkAlign = 512; // the Hessian kernel's per-CTA range of compacted records is a multiple of this
+constexpr int kMaxHessCtas = 1024;   // upper bound on the persistent Hessian grid (2 CTAs per SM), sizes `partial`
 constexpr int kBlk = 32;             // Cholesky block size
 constexpr int kBlockDoubles = 56;    // per-edge block: M (7x7 row-major) + v (7)
 
 // device-resident solver state (ints)
 enum StateSlot { kDone = 0, kIters = 1, kFailCount = 2, kFailNow = 3, kBadEdges = 4, kConverged = 5, kStateInts = 8 };
 
-// Edge record produced once per solve by the packing pre-pass (iteration-invariant part of the per-pixel work):
-//   idx >= 0 : index of the matched pixel in frame i, all pose-independent gates passed
-//              (valid_match & q > Q_thresh & c_i > C_thresh & c_j > C_thresh, gn_kernels.cu:953-957)
-//   idx <  0 : pixel contributes exactly zero (the reference multiplies it by a zero weight, :963-964)
-//   sq       : sqrtf(q)
-struct __align__(8) EdgeRec {
-  int idx;
-  float sq;
-};
+// Edge records produced once per solve by the packing pre-pass (iteration-invariant part of the per-pixel work).
+// Only pixels that pass every pose-independent gate (valid_match & q > Q_thresh & c_i > C_thresh & c_j > C_thresh,
+// gn_kernels.cu:953-957) get a record; the others contribute exactly zero in the reference (zero weight, :963-964)
+// and are dropped.  Records of edge e are compacted, in pixel order, into rec[e*num_pts + 0 .. ecount[e]):
+//   rec.x = index of the matched pixel in frame i, rec.y = pixel index k in frame j, sqv = sqrtf(q)
+typedef int2 EdgeRec;
 
 struct GnLayout {
   int num_kf, num_pts, num_edges, n_free, n, ld, nblk, tiles;
-  size_t off_xc, off_rec, off_ie, off_je, off_io, off_jo, off_partial, off_blocks, off_inc_off, off_inc_list, off_sys,
+  size_t off_xc, off_rec, off_ie, off_je, off_io, off_jo, off_partial, off_blocks, off_sqv, off_ecount, off_eoff, off_tstate, off_inc_off, off_inc_list, off_sys,
       off_lfac, off_pflag, off_dx, off_state, off_uniq_flag, off_all, off_K, total;
 };
 
@@ -38,6 +37,10 @@ struct GnWs {
   char* base;
   float4* xc() const { return (float4*)(base + L.off_xc); }
   EdgeRec* rec() const { return (EdgeRec*)(base + L.off_rec); }
+  float* sqv() const { return (float*)(base + L.off_sqv); }
+  int* ecount() const { return (int*)(base + L.off_ecount); }      // [E] records per edge
+  long long* eoff() const { return (long long*)(base + L.off_eoff); }  // [E+1] exclusive prefix of ecount
+  int* tstate() const { return (int*)(base + L.off_tstate); }      // [0] ticket, [1 + e*tiles + t] chained-scan state
   int* ie() const { return (int*)(base + L.off_ie); }
   int* je() const { return (int*)(base + L.off_je); }
   float* partial() const { return (float*)(base + L.off_partial); }
@@ -58,6 +61,7 @@ struct GnWs {
 int launch_pack_points(const GnWs& ws, const float* Xs, const float* Cs, cudaStream_t st);
 int launch_pack_edges(const GnWs& ws, const m3r_gn_params& p, const float* Cs, const int64_t* idx, const uint8_t* valid,
                       const float* Q, cudaStream_t st);
+int hessian_grid();
 int launch_hessian(const GnWs& ws, const m3r_gn_params& p, const float* Twc, cudaStream_t st);
 int launch_finalize_edges(const GnWs& ws, const float* Twc, cudaStream_t st);
 int launch_export_blocks(const GnWs& ws, float* Hs, float* gs, cudaStream_t st);

@@ -508,12 +508,13 @@ int launch_index_prep(const GnWs& ws, const int64_t* local_ii, const int64_t* lo
   init_state_kernel<<<1, 32, 0, st>>>(ws.state());
   M3R_LAUNCH_CHECK();
   const int E = ws.L.num_edges;
-  if (num_all_edges == 0) return M3R_OK;
   const int count = 2 * num_all_edges;
-  concat_ids_kernel<<<ceil_div(num_all_edges, 256), 256, 0, st>>>(all_ii, all_jj, num_all_edges, ws.all_ids());
-  M3R_LAUNCH_CHECK();
-  uniq_first_kernel<<<ceil_div(count, 256), 256, 0, st>>>(ws.all_ids(), ws.uniq_flag(), count);
-  M3R_LAUNCH_CHECK();
+  if (num_all_edges > 0) {
+    concat_ids_kernel<<<ceil_div(num_all_edges, 256), 256, 0, st>>>(all_ii, all_jj, num_all_edges, ws.all_ids());
+    M3R_LAUNCH_CHECK();
+    uniq_first_kernel<<<ceil_div(count, 256), 256, 0, st>>>(ws.all_ids(), ws.uniq_flag(), count);
+    M3R_LAUNCH_CHECK();
+  }
   if (E > 0) {
     edge_rank_kernel<<<ceil_div(2 * E, 256), 256, 0, st>>>(ws.all_ids(), ws.uniq_flag(), count, local_ii, local_jj, E,
                                                            ws.L.num_kf, ws.ie(), ws.je(), ws.state());

@@ -18,6 +18,7 @@ T = g["Twc"].clone()
 mk = lambda: md.ShardedGaussNewton(P, T, g["Xs"], g["Cs"], g["ii"], g["jj"], g["idx_ii2jj"], g["valid_match"], g["Q"], g["all_ii"], g["all_jj"])
 s = mk(); torch.cuda.synchronize()
 res = {"nkf": nkf, "E": int(g["ii"].numel()), "n": 7 * (nkf - 1)}
+tmp = mk(); del tmp; torch.cuda.synchronize()  # leave a cached block of workspace size so begin_ms excludes cudaMalloc
 res["begin_ms"] = timed(lambda: mk(), 3)
 lib = s.lib; import ctypes as C
 acc = lambda: _lib.check(lib.m3r_gn_accumulate(C.byref(P), C.c_void_p(T.data_ptr()), s.num_kf, s.num_pts, s.E, C.c_void_p(s.ws_ptr), s._stream()), "acc")
