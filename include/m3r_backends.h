@@ -161,6 +161,11 @@ M3R_API int m3r_gn_hessian_pass(const m3r_gn_params* params, const float* Twc, i
 /* pose_retr_kernel (gn_kernels.cu:415-453): poses (num_poses,8) in place, dx (num_poses-num_fix,7) */
 M3R_API int m3r_pose_retr(float* poses, const float* dx, int num_poses, int num_fix, void* stream);
 
+/* diagnostics: phase timeline of the fused solver kernel.  dev_buf = 2*cap device uint64; [0] counts the marks that
+ * follow as (tag, globaltimer ns) pairs written by CTA 0; pass NULL to switch it off (default).  No reference
+ * counterpart (the reference's solve runs on the host, gn_kernels.cu:1199-1222). */
+M3R_API void m3r_debug_set_timeline(unsigned long long* dev_buf, int cap);
+
 /* ---------------------------------------------------------------------------------------------------------
  * Host-buffer convenience wrappers (end-to-end path: pageable/pinned HOST pointers in, results back on the host).
  * They allocate device buffers, copy, run the device entry point on `stream`, copy back and synchronise.

@@ -60,6 +60,7 @@ GnLayout gn_layout(int num_kf, int num_pts, int num_edges, int num_all_edges) {
   L.off_jo = take(8);
   L.off_inc_off = take(sizeof(int) * (size_t)(L.n_free + 2));
   L.off_inc_list = take(sizeof(int) * (2 * E + 2));
+  L.off_inc_other = take(sizeof(int) * (2 * E + 2));
   L.off_all = take(sizeof(long long) * (2 * Ea + 2));
   L.off_uniq_flag = take(sizeof(int) * (2 * Ea + 2));
   L.off_blocks = take(sizeof(double) * kBlockDoubles * (E + 1));
@@ -143,20 +144,21 @@ static int gn_begin_impl(GnWs& ws, const m3r_gn_params* p, const float* Xs, cons
   return M3R_OK;
 }
 
+// one GN iteration = the Hessian kernel + ONE fused solver launch; the sharded path splits the latter at the all-reduce
 static int gn_accumulate_impl(GnWs& ws, const m3r_gn_params* p, const float* Twc, cudaStream_t st) {
   int rc;
   if ((rc = launch_hessian(ws, *p, Twc, st)) != M3R_OK) return rc;
-  if ((rc = launch_finalize_edges(ws, Twc, st)) != M3R_OK) return rc;
-  if ((rc = launch_assemble(ws, st)) != M3R_OK) return rc;
-  return M3R_OK;
+  return launch_fused(ws, const_cast<float*>(Twc), p->delta_thresh, M3R_PH_FINALIZE | M3R_PH_ASSEMBLE, st);
 }
 
 static int gn_solve_impl(GnWs& ws, const m3r_gn_params* p, float* Twc, cudaStream_t st) {
+  return launch_fused(ws, Twc, p->delta_thresh, M3R_PH_FACTOR | M3R_PH_BACKSOLVE, st);
+}
+
+static int gn_iterate_impl(GnWs& ws, const m3r_gn_params* p, float* Twc, cudaStream_t st) {
   int rc;
-  if (ws.L.n_free <= 0) return M3R_OK;
-  if ((rc = launch_cholesky(ws, st)) != M3R_OK) return rc;
-  if ((rc = launch_backsolve_retract(ws, Twc, p->delta_thresh, st)) != M3R_OK) return rc;
-  return M3R_OK;
+  if ((rc = launch_hessian(ws, *p, Twc, st)) != M3R_OK) return rc;
+  return launch_fused(ws, Twc, p->delta_thresh, M3R_PH_ALL, st);
 }
 
 static int gn_end_impl(GnWs& ws, float* dx_out, int32_t* info_out, cudaStream_t st) {
@@ -281,8 +283,7 @@ extern "C" int m3r_gauss_newton(const m3r_gn_params* params, float* Twc, const f
   if ((rc = gn_begin_impl(ws, params, Xs, Cs, ii, jj, idx_ii2jj, valid_match, Q, ii, jj, num_edges, st)) != M3R_OK)
     return rc;
   for (int it = 0; it < params->max_iter; it++) {
-    if ((rc = gn_accumulate_impl(ws, params, Twc, st)) != M3R_OK) return rc;
-    if ((rc = gn_solve_impl(ws, params, Twc, st)) != M3R_OK) return rc;
+    if ((rc = gn_iterate_impl(ws, params, Twc, st)) != M3R_OK) return rc;
   }
   return gn_end_impl(ws, dx_out, info_out, st);
 }

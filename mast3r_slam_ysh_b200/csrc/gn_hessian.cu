@@ -11,7 +11,7 @@
 //     become one float4 record (one LDG.128 per gather), and idx/valid/Q/C-gates become one 8-byte edge record.
 //   * 2-D decomposition: grid = edges x pixel tiles (the reference runs one 256-thread block per edge), fp32
 //     warp-shuffle + shared-memory tree per tile, deterministic fp64 second stage across tiles (no atomics).
-#include "gn_internal.cuh"
+#include "gn_finalize.cuh"
 
 namespace m3r {
 
@@ -47,8 +47,12 @@ __global__ void __launch_bounds__(256) pack_edges_kernel(const float* __restrict
                                                          EdgeRec* __restrict__ rec, float* __restrict__ sqv,
                                                          int* __restrict__ ecount, int* __restrict__ tstate,
                                                          int num_pts, int tiles, float C_thresh, float Q_thresh) {
-  __shared__ int s_idx[kTilePix];
-  __shared__ int s_work, s_base, s_wcnt[8];
+  // Every lane handles 4 consecutive pixels per pass (one LDG.32 of valid, one LDG.128 of Q, two predicated LDG.128 of
+  // the 8-byte indices), 8 passes of 1024 pixels per tile: a quarter of the instructions of the one-pixel-per-lane
+  // version, which was issue-bound at 52 % with 208 M warp instructions (profiles/r1_pack_v3a_ncu.txt).
+  constexpr int kPasses = kTilePix / 1024;
+  __shared__ __align__(16) int s_idx[kTilePix];
+  __shared__ int s_work, s_base, s_cnt[kPasses * 8];
   if (threadIdx.x == 0) s_work = atomicAdd(&tstate[0], 1);
   __syncthreads();
   const int work = s_work;
@@ -56,58 +60,84 @@ __global__ void __launch_bounds__(256) pack_edges_kernel(const float* __restrict
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int ix = ie[e], jx = je[e];
   const bool edge_ok = ix >= 0 && jx >= 0;
-  const int kw = tile * kTilePix + warp * 1024;  // first pixel of this warp
   const size_t eb = (size_t)e * num_pts;
+  // vector path: every edge row of Q / idx starts 16-byte aligned and of valid 4-byte aligned
+  const bool vec_ok = ((num_pts & 3) == 0) && ((reinterpret_cast<uintptr_t>(Q) & 15) == 0) &&
+                      ((reinterpret_cast<uintptr_t>(idx) & 15) == 0) && ((reinterpret_cast<uintptr_t>(valid) & 3) == 0);
   const float* __restrict__ Ci = Cs + (size_t)(edge_ok ? ix : 0) * num_pts;
   const float* __restrict__ Cj = Cs + (size_t)(edge_ok ? jx : 0) * num_pts;
   const long long* __restrict__ idx_e = reinterpret_cast<const long long*>(idx) + eb;
-  int cnt = 0;
-  constexpr int kU = 8;
-  for (int it0 = 0; it0 < 32; it0 += kU) {
-    float q[kU];
-    uint8_t vm[kU];
-    long long ind[kU];
-    float ci[kU], cj[kU];
+#pragma unroll 2
+  for (int p = 0; p < kPasses; p++) {
+    const int lk = p * 1024 + warp * 128 + lane * 4;  // pixel offset inside the tile
+    const int k = tile * kTilePix + lk;
+    float q[4] = {0.f, 0.f, 0.f, 0.f};
+    unsigned vm = 0;
+    long long ind[4] = {-1, -1, -1, -1};
+    if (edge_ok && k < num_pts) {
+      if (vec_ok) {  // k + 3 < num_pts because num_pts % 4 == 0
+        const float4 qv = __ldg(reinterpret_cast<const float4*>(Q + eb + k));  // re-read in phase 2: keep it in L2
+        q[0] = qv.x; q[1] = qv.y; q[2] = qv.z; q[3] = qv.w;
+        vm = __ldcs(reinterpret_cast<const unsigned*>(valid + eb + k));
+      } else {
 #pragma unroll
-    for (int u = 0; u < kU; u++) {
-      const int k = kw + (it0 + u) * 32 + lane;
-      const bool in = edge_ok && k < num_pts;
-      q[u] = in ? __ldg(Q + eb + k) : 0.0f;  // re-read in phase 2: keep it in L2
-      vm[u] = in ? __ldcs(valid + eb + k) : (uint8_t)0;
-    }
+        for (int j = 0; j < 4; j++)
+          if (k + j < num_pts) {
+            q[j] = __ldg(Q + eb + k + j);
+            vm |= (unsigned)(valid[eb + k + j] != 0) << (8 * j);
+          }
+      }
+      bool pass[4];
 #pragma unroll
-    for (int u = 0; u < kU; u++) {
-      const int k = kw + (it0 + u) * 32 + lane;
-      ind[u] = (vm[u] && q[u] > Q_thresh) ? __ldcs(idx_e + k) : -1;
-    }
+      for (int j = 0; j < 4; j++) pass[j] = ((vm >> (8 * j)) & 0xffu) != 0 && q[j] > Q_thresh;
+      if (vec_ok) {
+        if (pass[0] | pass[1]) {
+          const longlong2 v = __ldcs(reinterpret_cast<const longlong2*>(idx_e + k));
+          ind[0] = v.x; ind[1] = v.y;
+        }
+        if (pass[2] | pass[3]) {
+          const longlong2 v = __ldcs(reinterpret_cast<const longlong2*>(idx_e + k + 2));
+          ind[2] = v.x; ind[3] = v.y;
+        }
+      } else {
 #pragma unroll
-    for (int u = 0; u < kU; u++) {
-      const int k = kw + (it0 + u) * 32 + lane;
-      const bool ok = ind[u] >= 0 && ind[u] < num_pts;
-      ci[u] = ok ? __ldg(Ci + ind[u]) : 0.0f;
-      cj[u] = ok ? __ldg(Cj + k) : 0.0f;
-      if (!ok) ind[u] = -1;
-    }
+        for (int j = 0; j < 4; j++)
+          if (pass[j]) ind[j] = idx_e[k + j];
+      }
 #pragma unroll
-    for (int u = 0; u < kU; u++) {
-      const int id = (ind[u] >= 0 && ci[u] > C_thresh && cj[u] > C_thresh) ? (int)ind[u] : -1;
-      s_idx[warp * 1024 + (it0 + u) * 32 + lane] = id;
-      cnt += __popc(__ballot_sync(0xffffffffu, id >= 0));
+      for (int j = 0; j < 4; j++)
+        if (!pass[j] || ind[j] >= num_pts) ind[j] = -1;
     }
+    float ci[4], cj[4];
+#pragma unroll
+    for (int j = 0; j < 4; j++) {
+      ci[j] = ind[j] >= 0 ? __ldg(Ci + ind[j]) : 0.0f;
+      cj[j] = ind[j] >= 0 ? __ldg(Cj + k + j) : 0.0f;
+    }
+    int4 id;
+    id.x = (ind[0] >= 0 && ci[0] > C_thresh && cj[0] > C_thresh) ? (int)ind[0] : -1;
+    id.y = (ind[1] >= 0 && ci[1] > C_thresh && cj[1] > C_thresh) ? (int)ind[1] : -1;
+    id.z = (ind[2] >= 0 && ci[2] > C_thresh && cj[2] > C_thresh) ? (int)ind[2] : -1;
+    id.w = (ind[3] >= 0 && ci[3] > C_thresh && cj[3] > C_thresh) ? (int)ind[3] : -1;
+    *reinterpret_cast<int4*>(&s_idx[lk]) = id;
+    const int c = (id.x >= 0) + (id.y >= 0) + (id.z >= 0) + (id.w >= 0);
+    const int tot = __reduce_add_sync(0xffffffffu, c);
+    if (lane == 0) s_cnt[p * 8 + warp] = tot;
   }
-  if (lane == 0) s_wcnt[warp] = cnt;
   __syncthreads();
   if (warp == 0) {
-    int run = 0;
-    if (lane == 0) {
+    // exclusive scan of the 64 (pass, warp) counts in pixel order, two per lane
+    const int c0 = s_cnt[2 * lane], c1 = s_cnt[2 * lane + 1];
+    int incl = c0 + c1;
 #pragma unroll
-      for (int wv = 0; wv < 8; wv++) {
-        const int c = s_wcnt[wv];
-        s_wcnt[wv] = run;
-        run += c;
-      }
-      st_release(&tstate[1 + work], run + 1);  // own count, visible before anyone needs it
+    for (int o = 1; o < 32; o <<= 1) {
+      const int v = __shfl_up_sync(0xffffffffu, incl, o);
+      if (lane >= o) incl += v;
     }
+    const int run = __shfl_sync(0xffffffffu, incl, 31);
+    s_cnt[2 * lane] = incl - c0 - c1;
+    s_cnt[2 * lane + 1] = incl - c1;
+    if (lane == 0) st_release(&tstate[1 + work], run + 1);  // own count, visible before anyone needs it
     int before = 0;
     for (int t = lane; t < tile; t += 32) {  // counts of the earlier tiles of this edge
       int v;
@@ -122,19 +152,31 @@ __global__ void __launch_bounds__(256) pack_edges_kernel(const float* __restrict
     }
   }
   __syncthreads();
-  int wbase = s_base + s_wcnt[warp];
   const unsigned lt = (1u << lane) - 1u;
-#pragma unroll 4
-  for (int it = 0; it < 32; it++) {
-    const int id = s_idx[warp * 1024 + it * 32 + lane];
-    const unsigned bal = __ballot_sync(0xffffffffu, id >= 0);
-    if (id >= 0) {
-      const int k = kw + it * 32 + lane;
-      const int pos = wbase + __popc(bal & lt);
-      rec[eb + pos] = make_int2(id, k);
-      sqv[eb + pos] = sqrtf(__ldcs(Q + eb + k));
+  const int base = s_base;
+#pragma unroll 2
+  for (int p = 0; p < kPasses; p++) {
+    const int lk = p * 1024 + warp * 128 + lane * 4;
+    const int k = tile * kTilePix + lk;
+    const int4 id = *reinterpret_cast<const int4*>(&s_idx[lk]);
+    const unsigned b0 = __ballot_sync(0xffffffffu, id.x >= 0), b1 = __ballot_sync(0xffffffffu, id.y >= 0);
+    const unsigned b2 = __ballot_sync(0xffffffffu, id.z >= 0), b3 = __ballot_sync(0xffffffffu, id.w >= 0);
+    if ((b0 | b1 | b2 | b3) == 0) continue;
+    int pos = base + s_cnt[p * 8 + warp] + __popc(b0 & lt) + __popc(b1 & lt) + __popc(b2 & lt) + __popc(b3 & lt);
+    {
+      float q[4];
+      if (vec_ok && k < num_pts) {
+        const float4 qv = __ldcs(reinterpret_cast<const float4*>(Q + eb + k));
+        q[0] = qv.x; q[1] = qv.y; q[2] = qv.z; q[3] = qv.w;
+      } else {
+#pragma unroll
+        for (int j = 0; j < 4; j++) q[j] = (k + j < num_pts) ? Q[eb + k + j] : 0.0f;
+      }
+      if (id.x >= 0) { rec[eb + pos] = make_int2(id.x, k);     sqv[eb + pos] = sqrtf(q[0]); pos++; }
+      if (id.y >= 0) { rec[eb + pos] = make_int2(id.y, k + 1); sqv[eb + pos] = sqrtf(q[1]); pos++; }
+      if (id.z >= 0) { rec[eb + pos] = make_int2(id.z, k + 2); sqv[eb + pos] = sqrtf(q[2]); pos++; }
+      if (id.w >= 0) { rec[eb + pos] = make_int2(id.w, k + 3); sqv[eb + pos] = sqrtf(q[3]); pos++; }
     }
-    wbase += __popc(bal);
   }
 }
 
@@ -254,12 +296,6 @@ __device__ void edge_setup(const float* __restrict__ Twc, int ix, int jx, const 
     c->fx = c->fy = 1.0f;
     c->cx = c->cy = 0.0f;
   }
-}
-
-// records per CTA of the persistent Hessian kernel (same formula in the kernel and in finalize_edges_kernel)
-__host__ __device__ __forceinline__ long long hess_chunk(long long V, int grid) {
-  const long long c = (V + grid - 1) / grid;
-  return (c + kHessChunkAlign - 1) / kHessChunkAlign * kHessChunkAlign;
 }
 
 struct PixParams {
@@ -499,99 +535,17 @@ __global__ void __launch_bounds__(kHessThreads, 2) hessian_kernel(const float* _
 }
 
 // ------------------------------------------------------------------------------------------------ per-edge finalize
-// One warp per edge: sum the partials of the edge's segments in fp64 (fixed order), M = A S A^T, v = A g with
-// A = [[R/s, 0, 0], [[t]x R/s, R, 0], [t^T R/s, 0, 1]] -- the matrix of apply_Sim3_adj_inv(T_i) (gn_kernels.cu:277-297).
-__global__ void __launch_bounds__(128) finalize_edges_kernel(const float* __restrict__ Twc,
-                                                             const float* __restrict__ partial,
-                                                             const long long* __restrict__ eoff,
-                                                             const int* __restrict__ ie, const int* __restrict__ je,
-                                                             double* __restrict__ blocks,
-                                                             const int* __restrict__ state, int num_edges,
+// Diagnostics path only (m3r_gn_edge_blocks); the solver runs finalize_edge inside its fused kernel (gn_fused.cu).
+__global__ void __launch_bounds__(128) finalize_edges_kernel(const float* Twc, const float* partial,
+                                                             const long long* eoff, const int* ie, const int* je,
+                                                             double* blocks, const int* state, int num_edges,
                                                              int hess_grid) {
   if (state[kDone]) return;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int e = blockIdx.x * 4 + warp;
-  __shared__ double sS[4][49], sA[4][49], sB[4][49], sg[4][7];
+  __shared__ FinalizeScratch sc[4];
   if (e >= num_edges) return;
-  double* out = blocks + (size_t)e * kBlockDoubles;
-  const int ix = ie[e], jx = je[e];
-  if (ix < 0 || jx < 0) {
-    for (int l = lane; l < kBlockDoubles; l += 32) out[l] = 0.0;
-    return;
-  }
-  double s0 = 0.0, s1 = 0.0;
-  const long long b0 = eoff[e], b1 = eoff[e + 1];
-  if (b1 > b0) {  // segments (e, c) for the CTAs c whose record range intersects [b0, b1): slot e + c
-    const long long chunk = hess_chunk(eoff[num_edges], hess_grid);
-    const int c_first = (int)(b0 / chunk), c_last = (int)((b1 - 1) / chunk);
-    for (int c = c_first; c <= c_last; c++) {
-      const float* p = partial + (size_t)(e + c) * kAccStride;
-      s0 += (double)p[lane];
-      if (lane < kAcc - 32) s1 += (double)p[32 + lane];
-    }
-  }
-  // scatter into symmetric S and g
-  {
-    int l = lane;  // entries 0..31
-    if (l < 28) {
-      int a = 0;
-      while ((a + 1) * (a + 2) / 2 <= l) a++;
-      const int b = l - a * (a + 1) / 2;
-      sS[warp][a * 7 + b] = s0;
-      sS[warp][b * 7 + a] = s0;
-    } else {
-      sg[warp][l - 28] = s0;
-    }
-    if (lane < kAcc - 32) sg[warp][32 + lane - 28] = s1;
-  }
-  if (lane == 0) {
-    const float* T = Twc + (size_t)ix * 8;
-    const double t[3] = {T[0], T[1], T[2]};
-    const double x = T[3], y = T[4], z = T[5], w = T[6];
-    const double s_inv = 1.0 / (double)T[7];
-    double R[9];
-    R[0] = 1.0 - 2.0 * (y * y + z * z); R[1] = 2.0 * (x * y - w * z); R[2] = 2.0 * (x * z + w * y);
-    R[3] = 2.0 * (x * y + w * z); R[4] = 1.0 - 2.0 * (x * x + z * z); R[5] = 2.0 * (y * z - w * x);
-    R[6] = 2.0 * (x * z - w * y); R[7] = 2.0 * (y * z + w * x); R[8] = 1.0 - 2.0 * (x * x + y * y);
-    double* A = sA[warp];
-    for (int i = 0; i < 49; i++) A[i] = 0.0;
-    for (int r = 0; r < 3; r++)
-      for (int c = 0; c < 3; c++) {
-        A[r * 7 + c] = s_inv * R[r * 3 + c];
-        A[(3 + r) * 7 + 3 + c] = R[r * 3 + c];
-      }
-    // rows 3..5, cols 0..2: s_inv * [t]x R ; row 6, cols 0..2: s_inv * t^T R
-    for (int c = 0; c < 3; c++) {
-      const double r0 = R[0 * 3 + c], r1 = R[1 * 3 + c], r2 = R[2 * 3 + c];
-      A[3 * 7 + c] = s_inv * (t[1] * r2 - t[2] * r1);
-      A[4 * 7 + c] = s_inv * (t[2] * r0 - t[0] * r2);
-      A[5 * 7 + c] = s_inv * (t[0] * r1 - t[1] * r0);
-      A[6 * 7 + c] = s_inv * (t[0] * r0 + t[1] * r1 + t[2] * r2);
-    }
-    A[6 * 7 + 6] = 1.0;
-  }
-  __syncwarp();
-  for (int l = lane; l < 49; l += 32) {  // B = A S
-    const int r = l / 7, c = l % 7;
-    double v = 0.0;
-    for (int k = 0; k < 7; k++) v += sA[warp][r * 7 + k] * sS[warp][k * 7 + c];
-    sB[warp][l] = v;
-  }
-  __syncwarp();
-  for (int l = lane; l < 49; l += 32) {  // M = B A^T, only lower computed then mirrored for exact symmetry
-    const int r = l / 7, c = l % 7;
-    if (c <= r) {
-      double v = 0.0;
-      for (int k = 0; k < 7; k++) v += sB[warp][r * 7 + k] * sA[warp][c * 7 + k];
-      out[r * 7 + c] = v;
-      out[c * 7 + r] = v;
-    }
-  }
-  if (lane < 7) {
-    double v = 0.0;
-    for (int k = 0; k < 7; k++) v += sA[warp][lane * 7 + k] * sg[warp][k];
-    out[49 + lane] = v;
-  }
+  finalize_edge(e, lane, sc[warp], Twc, partial, eoff, ie, je, blocks, num_edges, hess_grid);
 }
 
 // diagnostic export in the reference's Hs/gs layout (gn_kernels.cu:1097-1137)

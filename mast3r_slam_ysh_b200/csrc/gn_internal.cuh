@@ -15,7 +15,14 @@ constexpr int kBlk = 32;             // Cholesky block size
 constexpr int kBlockDoubles = 56;    // per-edge block: M (7x7 row-major) + v (7)
 
 // device-resident solver state (ints)
-enum StateSlot { kDone = 0, kIters = 1, kFailCount = 2, kFailNow = 3, kBadEdges = 4, kConverged = 5, kStateInts = 8 };
+enum StateSlot {
+  kDone = 0, kIters = 1, kFailCount = 2, kFailNow = 3, kBadEdges = 4, kConverged = 5,
+  kBarCount = 6, kBarGen = 7,  // grid barrier of the fused solver kernel
+  kStateInts = 8
+};
+
+// phases of the fused solver kernel (gn_fused.cu)
+enum FusedPhase { M3R_PH_FINALIZE = 1, M3R_PH_ASSEMBLE = 2, M3R_PH_FACTOR = 4, M3R_PH_BACKSOLVE = 8, M3R_PH_ALL = 15 };
 
 // Edge records produced once per solve by the packing pre-pass (iteration-invariant part of the per-pixel work).
 // Only pixels that pass every pose-independent gate (valid_match & q > Q_thresh & c_i > C_thresh & c_j > C_thresh,
@@ -26,7 +33,7 @@ typedef int2 EdgeRec;
 
 struct GnLayout {
   int num_kf, num_pts, num_edges, n_free, n, ld, nblk, tiles;
-  size_t off_xc, off_rec, off_ie, off_je, off_io, off_jo, off_partial, off_blocks, off_sqv, off_ecount, off_eoff, off_tstate, off_inc_off, off_inc_list, off_sys,
+  size_t off_xc, off_rec, off_ie, off_je, off_io, off_jo, off_partial, off_blocks, off_sqv, off_ecount, off_eoff, off_tstate, off_inc_off, off_inc_list, off_inc_other, off_sys,
       off_lfac, off_pflag, off_dx, off_state, off_uniq_flag, off_all, off_K, total;
 };
 
@@ -47,6 +54,7 @@ struct GnWs {
   double* blocks() const { return (double*)(base + L.off_blocks); }
   int* inc_off() const { return (int*)(base + L.off_inc_off); }
   int* inc_list() const { return (int*)(base + L.off_inc_list); }
+  int* inc_other() const { return (int*)(base + L.off_inc_other); }  // per list entry: other end's free index, see gn_solve.cu
   double* sys() const { return (double*)(base + L.off_sys); }
   double* lfac() const { return (double*)(base + L.off_lfac); }
   int* pflag() const { return (int*)(base + L.off_pflag); }
@@ -70,9 +78,9 @@ int launch_export_blocks(const GnWs& ws, float* Hs, float* gs, cudaStream_t st);
 int launch_index_prep(const GnWs& ws, const int64_t* local_ii, const int64_t* local_jj, const int64_t* all_ii,
                       const int64_t* all_jj, int num_all_edges, cudaStream_t st);
 int launch_direct_edge_index(const GnWs& ws, const int64_t* ii_edge, const int64_t* jj_edge, cudaStream_t st);
-int launch_assemble(const GnWs& ws, cudaStream_t st);
-int launch_cholesky(const GnWs& ws, cudaStream_t st);
-int launch_backsolve_retract(const GnWs& ws, float* Twc, float delta_thresh, cudaStream_t st);
+
+// gn_fused.cu
+int launch_fused(const GnWs& ws, float* Twc, float delta_thresh, int phases, cudaStream_t st);
 int launch_pose_retr(float* poses, const float* dx, int num_poses, int num_fix, cudaStream_t st);
 
 }  // namespace m3r

@@ -2,7 +2,7 @@
 # One gpurun call: GPU tests, bench, phase timings, launch list, ncu full captures (each ncu pass only after the
 # plain run exited 0).  Outputs under gpurun_out/.   usage: tools/gpu_round.sh [quick]
 mkdir -p gpurun_out; O=gpurun_out; : > $O/rc.txt
-KREG='regex:hessian_kernel|pack_|finalize_edges|assemble_kernel|panel_kernel|update_kernel|backsolve|chol|edge_|uniq_|incidence|iter_proj|refine_matches|repack|finish_kernel|init_state|concat_ids|zero_f32'
+KREG='regex:hessian_kernel|pack_|finalize_edges|gn_fused|gn_small|edge_|uniq_|incidence|iter_proj|refine_matches|repack|finish_kernel|init_state|concat_ids|zero_f32'
 timeout 900 python -m pytest tests -m gpu -x -q > $O/pytest_gpu.log 2>&1; echo "pytest rc=$?" | tee -a $O/rc.txt
 timeout 300 python tools/time_phases.py 32 8 > $O/phases_32.json 2>&1
 timeout 300 python tools/time_phases.py 256 0 > $O/phases_256.json 2>&1
