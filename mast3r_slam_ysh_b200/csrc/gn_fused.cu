@@ -270,71 +270,120 @@ __device__ __forceinline__ void panel_phase(const FusedArgs& A, int kb, PanelSme
   if (threadIdx.x < kPanelRows / 64) A.pflag[blockIdx.x * (kPanelRows / 64) + threadIdx.x] = sm.nz[threadIdx.x];
 }
 
-// C[r][c] -= sum_k X[r][k] X[c][k] for one 64x64 tile (tr, tc), tc <= tr, of the trailing matrix that starts at
-// t0 = c0 + 32.  256 threads, 4x4 outputs each.
-__device__ __forceinline__ void update_tile(const FusedArgs& A, int kb, int tr, int tc, UpdateSmem& sm) {
-  const int n = A.n, ld = A.ld;
-  const int c0 = kb * kBlk;
+// C[r][c] -= sum_k X[r][k] X[c][k] on 64x64 tiles (tr, tc), tc <= tr, of the trailing matrix that starts at
+// t0 = c0 + 32; 256 threads, 4x4 outputs each.  A CTA walks its live tiles with a two-deep pipeline: the panel rows of
+// the NEXT tile and the old C values of the current one are in flight (registers) while the current tile is multiplied
+// out of shared memory, so a tile costs its arithmetic plus one shared-memory round trip instead of three dependent L2
+// round trips (load panels -> compute -> read-modify-write C), which made a tile 6 us for 2 us of DFMAs (r1).
+struct TileRegs {
+  double2 r[4], c[4];
+};
+
+__device__ __forceinline__ void tile_decode(int t, int& tr, int& tc) {
+  tr = (int)((sqrtf(8.0f * (float)t + 1.0f) - 1.0f) * 0.5f);
+  while ((tr + 1) * (tr + 2) / 2 <= t) tr++;
+  while (tr * (tr + 1) / 2 > t) tr--;
+  tc = t - tr * (tr + 1) / 2;
+}
+
+__device__ __forceinline__ void tile_load(const FusedArgs& A, int c0, int tr, int tc, TileRegs& g) {
   const int t0 = c0 + kBlk;
   const int r_base = t0 + tr * kUpdTile, c_base = t0 + tc * kUpdTile;
-  __syncthreads();  // previous tile's readers are done with sm
-  for (int l = threadIdx.x; l < kUpdTile * kBlk / 2; l += kFusedThreads) {
-    const int r = l / (kBlk / 2), k2 = l - r * (kBlk / 2);
+#pragma unroll
+  for (int q = 0; q < 4; q++) {
+    const int l = threadIdx.x + q * kFusedThreads;
+    const int r = l >> 4, k2 = l & 15;
     const int gr = r_base + r, gc = c_base + r;
-    double2 vr = make_double2(0.0, 0.0), vc = make_double2(0.0, 0.0);
-    if (gr <= n) vr = __ldcg(reinterpret_cast<const double2*>(A.sys + (size_t)gr * ld + c0) + k2);
-    if (gc < n) vc = __ldcg(reinterpret_cast<const double2*>(A.sys + (size_t)gc * ld + c0) + k2);
-    sm.R[r][2 * k2] = vr.x;
-    sm.R[r][2 * k2 + 1] = vr.y;
-    sm.C[r][2 * k2] = vc.x;
-    sm.C[r][2 * k2 + 1] = vc.y;
+    g.r[q] = make_double2(0.0, 0.0);
+    g.c[q] = make_double2(0.0, 0.0);
+    if (gr <= A.n) g.r[q] = __ldcg(reinterpret_cast<const double2*>(A.sys + (size_t)gr * A.ld + c0) + k2);
+    if (gc < A.n) g.c[q] = __ldcg(reinterpret_cast<const double2*>(A.sys + (size_t)gc * A.ld + c0) + k2);
   }
-  __syncthreads();
-  const int ty = threadIdx.x / 16, tx = threadIdx.x % 16;
-  double acc[4][4];
+}
+
+__device__ __forceinline__ void tile_store(UpdateSmem& sm, const TileRegs& g) {
 #pragma unroll
-  for (int i = 0; i < 4; i++)
-#pragma unroll
-    for (int j = 0; j < 4; j++) acc[i][j] = 0.0;
-#pragma unroll 8
-  for (int k = 0; k < kBlk; k++) {
-    double a[4], b[4];
-#pragma unroll
-    for (int i = 0; i < 4; i++) a[i] = sm.R[ty + 16 * i][k];
-#pragma unroll
-    for (int j = 0; j < 4; j++) b[j] = sm.C[tx + 16 * j][k];
-#pragma unroll
-    for (int i = 0; i < 4; i++)
-#pragma unroll
-      for (int j = 0; j < 4; j++) acc[i][j] = fma(a[i], b[j], acc[i][j]);
-  }
-#pragma unroll
-  for (int i = 0; i < 4; i++) {
-    const int gr = r_base + ty + 16 * i;
-    if (gr > n) continue;
-#pragma unroll
-    for (int j = 0; j < 4; j++) {
-      const int gc = c_base + tx + 16 * j;
-      if (gc < n && gc <= gr) {
-        double* p = A.sys + (size_t)gr * ld + gc;
-        *p = __ldcg(p) - acc[i][j];
-      }
-    }
+  for (int q = 0; q < 4; q++) {
+    const int l = threadIdx.x + q * kFusedThreads;
+    const int r = l >> 4, k2 = l & 15;
+    sm.R[r][2 * k2] = g.r[q].x;
+    sm.R[r][2 * k2 + 1] = g.r[q].y;
+    sm.C[r][2 * k2] = g.c[q].x;
+    sm.C[r][2 * k2 + 1] = g.c[q].y;
   }
 }
 
 __device__ __forceinline__ void update_phase(const FusedArgs& A, int kb, int nfac, UpdateSmem& sm) {
-  const int rows_below = A.n + 1 - (kb + 1) * kBlk;  // rows t0 .. n
+  const int n = A.n, ld = A.ld;
+  const int c0 = kb * kBlk, t0 = c0 + kBlk;
+  const int rows_below = n + 1 - t0;  // rows t0 .. n
   if (rows_below <= 0) return;
   const int T = (rows_below + kUpdTile - 1) / kUpdTile;
   const int ntiles = T * (T + 1) / 2;
-  for (int t = blockIdx.x; t < ntiles; t += nfac) {
-    int tr = (int)((sqrtf(8.0f * (float)t + 1.0f) - 1.0f) * 0.5f);
-    while ((tr + 1) * (tr + 2) / 2 <= t) tr++;
-    while (tr * (tr + 1) / 2 > t) tr--;
-    const int tc = t - tr * (tr + 1) / 2;
-    if (__ldcg(A.pflag + tr) == 0 || __ldcg(A.pflag + tc) == 0) continue;  // structurally zero panel tile
-    update_tile(A, kb, tr, tc, sm);
+  __shared__ int s_pf[128];
+  __syncthreads();
+  for (int i = threadIdx.x; i < T && i < 128; i += kFusedThreads) s_pf[i] = __ldcg(A.pflag + i);
+  __syncthreads();
+  auto next_live = [&](int t, int& tr, int& tc) {  // first tile >= t of this CTA whose two panel tiles are non-zero
+    for (; t < ntiles; t += nfac) {
+      tile_decode(t, tr, tc);
+      if (s_pf[tr & 127] != 0 && s_pf[tc & 127] != 0) return t;
+    }
+    return -1;
+  };
+  int tr, tc;
+  int t = next_live(blockIdx.x, tr, tc);
+  if (t < 0) return;
+  TileRegs g;
+  tile_load(A, c0, tr, tc, g);
+  const int ty = threadIdx.x / 16, tx = threadIdx.x % 16;
+  while (t >= 0) {
+    __syncthreads();  // readers of the previous tile are done with sm
+    tile_store(sm, g);
+    __syncthreads();
+    int ntr = 0, ntc = 0;
+    const int tn = next_live(t + nfac, ntr, ntc);
+    if (tn >= 0) tile_load(A, c0, ntr, ntc, g);  // in flight during the multiply
+    const int r_base = t0 + tr * kUpdTile, c_base = t0 + tc * kUpdTile;
+    double cold[4][4];
+#pragma unroll
+    for (int i = 0; i < 4; i++) {
+      const int gr = r_base + ty + 16 * i;
+#pragma unroll
+      for (int j = 0; j < 4; j++) {
+        const int gc = c_base + tx + 16 * j;
+        cold[i][j] = (gr <= n && gc < n && gc <= gr) ? __ldcg(A.sys + (size_t)gr * ld + gc) : 0.0;
+      }
+    }
+    double acc[4][4];
+#pragma unroll
+    for (int i = 0; i < 4; i++)
+#pragma unroll
+      for (int j = 0; j < 4; j++) acc[i][j] = 0.0;
+#pragma unroll 8
+    for (int k = 0; k < kBlk; k++) {
+      double a[4], b[4];
+#pragma unroll
+      for (int i = 0; i < 4; i++) a[i] = sm.R[ty + 16 * i][k];
+#pragma unroll
+      for (int j = 0; j < 4; j++) b[j] = sm.C[tx + 16 * j][k];
+#pragma unroll
+      for (int i = 0; i < 4; i++)
+#pragma unroll
+        for (int j = 0; j < 4; j++) acc[i][j] = fma(a[i], b[j], acc[i][j]);
+    }
+#pragma unroll
+    for (int i = 0; i < 4; i++) {
+      const int gr = r_base + ty + 16 * i;
+#pragma unroll
+      for (int j = 0; j < 4; j++) {
+        const int gc = c_base + tx + 16 * j;
+        if (gr <= n && gc < n && gc <= gr) A.sys[(size_t)gr * ld + gc] = cold[i][j] - acc[i][j];
+      }
+    }
+    t = tn;
+    tr = ntr;
+    tc = ntc;
   }
 }
 
@@ -468,13 +517,14 @@ __global__ void __launch_bounds__(kFusedThreads, 1) gn_fused_kernel(const FusedA
   }
   if (A.phases & M3R_PH_FACTOR) {
     if (A.phases & M3R_PH_ASSEMBLE) grid_barrier(A.state, gridDim.x);
-    // only the CTAs that can get work in the widest (first) block column take part in the factorisation
-    const int T0 = (A.n + 1 - kBlk + kUpdTile - 1) / kUpdTile;
-    int nfac = T0 > 0 ? T0 * (T0 + 1) / 2 : 1;
-    if (nfac > (int)gridDim.x) nfac = gridDim.x;
-    if ((int)blockIdx.x >= nfac) return;
+    // only the CTAs that can get work in block column kb take part in its two barriers; the trailing matrix shrinks, so
+    // the set is non-increasing and a CTA that drops out never comes back
     tl_mark(A, 5);
     for (int kb = 0; kb < A.nblk; kb++) {
+      const int Tk = (A.n + 1 - (kb + 1) * kBlk + kUpdTile - 1) / kUpdTile;
+      int nfac = Tk > 0 ? Tk * (Tk + 1) / 2 : 1;
+      if (nfac > (int)gridDim.x) nfac = gridDim.x;
+      if ((int)blockIdx.x >= nfac) return;
       panel_phase(A, kb, sm.panel);
       tl_mark(A, 1000 + kb);
       grid_barrier(A.state, nfac);
@@ -524,6 +574,10 @@ __global__ void __launch_bounds__(kSmallThreads, 1) gn_small_kernel(const FusedA
     double* y = reinterpret_cast<double*>(&ax + 1);
     double* dinv = y + A.nblk * kBlk;
     small_cholesky_solve(M, ax, A.sys, A.n, A.nblk, y, dinv, A.timeline, A.timeline_cap);
+#ifdef M3R_SMALL_TWICE  // experiment: a second, instruction-cache-warm pass over the same system
+    __syncthreads();
+    small_cholesky_solve(M, ax, A.sys, A.n, A.nblk, y, dinv, A.timeline, A.timeline_cap);
+#endif
     tl_mark(A, 7);
     finish_solution(A, y, &ax.bad, ax.norm);
     tl_mark(A, 6);

@@ -278,7 +278,9 @@ __device__ __forceinline__ void small_cholesky_solve(double* M, SmallAux& ax, co
     const int nb = min(kBlk, n - c0);
     small_mark(ax, 2 + 3 * kb, 1000 + kb);
     const int first = c0 + nb;  // first row below the block; rows first..n
+#ifndef M3R_X_NO_TRSM
     for (int row = first + tid; row <= n; row += blockDim.x) small_trsm_row(M, ax, c0, nb, row, row - first);
+#endif
     __syncthreads();
     small_mark(ax, 3 + 3 * kb, 2000 + kb);
     if (kb + 1 < nblk) {  // nb == 32 here
@@ -293,14 +295,20 @@ __device__ __forceinline__ void small_cholesky_solve(double* M, SmallAux& ax, co
       __syncthreads();
       continue;
 #endif
+#ifndef M3R_X_NO_UPDATE
       small_update_diag(M, c0, n);
+#endif
       __syncthreads();
       if (warp == 0) {
+#ifndef M3R_X_NO_FACTOR
         const int c1 = c0 + kBlk;
         const bool bad = small_factor_diag(M, ax, dinv, c1, min(kBlk, n - c1), lane);
         if (bad && lane == 0) ax.bad = 1;
+#endif
       } else {
+#ifndef M3R_X_NO_UPDATE
         small_update(M, ax, c0, n, 2, warp - 1, nwarps - 1, lane);
+#endif
       }
       __syncthreads();
     }
@@ -309,6 +317,9 @@ __device__ __forceinline__ void small_cholesky_solve(double* M, SmallAux& ax, co
   // back substitution: y = row n; blocks from the bottom
   for (int c = tid; c < nblk * kBlk; c += blockDim.x) y[c] = (c < n) ? M[prow(n) + c] : 0.0;
   __syncthreads();
+#ifdef M3R_X_NO_BACKSOLVE
+  if (true) return;
+#endif
   for (int kb = nblk - 1; kb >= 0; kb--) {
     const int c0 = kb * kBlk;
     const int nb = min(kBlk, n - c0);

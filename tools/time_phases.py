@@ -8,7 +8,7 @@ span = int(sys.argv[2]) if len(sys.argv) > 2 else 8
 dev = torch.device("cuda:0"); lo = syn.LOCAL_OPT
 edges = syn.ring_edges(nkf, span) if span > 0 else syn.loop_closure_edges(nkf)
 g = syn.make_gn_problem(nkf, 384, 512, edges, seed=1236, device=dev)
-P = _lib.GnParams(_lib.M3R_GN_RAYS, 0, lo["sigma_ray"], lo["sigma_dist"], lo["C_conf"], lo["Q_conf"], None, 0, 0, 0, 0.0, 10, 1e-8)
+P = _lib.GnParams(_lib.M3R_GN_RAYS, 0, lo["sigma_ray"], lo["sigma_dist"], lo["C_conf"], lo["Q_conf"], None, 0, 0, 0, 0.0, 10, -1.0)
 def ev(): return torch.cuda.Event(enable_timing=True)
 def timed(fn, reps):
     torch.cuda.synchronize(); a, b = ev(), ev(); a.record()
