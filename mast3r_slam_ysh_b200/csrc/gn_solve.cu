@@ -135,12 +135,181 @@ __global__ void pose_retr_kernel(float* __restrict__ poses, const float* __restr
 }
 
 // ============================================================================================== launchers
+// ---- all of the above in ONE single-CTA kernel for graphs whose id list fits in shared memory (the usual case):
+//      bitonic sort of the concatenated ids, unique, rank = lower_bound (== torch::_unique + searchsorted,
+//      gn_kernels.cu:161-170), incidence lists, state reset.  The separate kernels cost 150 us per solve at 512 edges
+//      (five launches, O(count^2) scans through global memory); this one takes ~15 us.
+constexpr int kPrepThreads = 1024;
+constexpr int kPrepMaxCount = 16384;
+
+__global__ void __launch_bounds__(kPrepThreads) index_prep_kernel(const int64_t* __restrict__ all_ii,
+                                                                  const int64_t* __restrict__ all_jj, int num_all,
+                                                                  const int64_t* __restrict__ ii,
+                                                                  const int64_t* __restrict__ jj, int num_edges,
+                                                                  int num_kf, int padded, int* __restrict__ ie,
+                                                                  int* __restrict__ je, int* __restrict__ inc_off,
+                                                                  int* __restrict__ inc_list,
+                                                                  int* __restrict__ inc_other, int* __restrict__ state) {
+  extern __shared__ __align__(16) unsigned char s_prep[];
+  long long* ids = reinterpret_cast<long long*>(s_prep);                 // [padded]
+  int* s_ie = reinterpret_cast<int*>(ids + padded);                       // [num_edges]
+  int* s_je = s_ie + num_edges;                                           // [num_edges]
+  int* s_deg = s_je + num_edges;                                          // [num_kf + 1]
+  __shared__ int s_warp[kPrepThreads / 32];
+  __shared__ int s_nuniq, s_bad;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const long long kInf = 0x7fffffffffffffffLL;
+  const int count = 2 * num_all;
+  if (tid < kStateInts) state[tid] = 0;
+  if (tid == 0) s_bad = 0;
+  for (int k = tid; k < padded; k += kPrepThreads)
+    ids[k] = k < num_all ? (long long)all_ii[k] : (k < count ? (long long)all_jj[k - num_all] : kInf);
+  __syncthreads();
+  for (int size = 2; size <= padded; size <<= 1)
+    for (int stride = size >> 1; stride > 0; stride >>= 1) {
+      for (int t = tid; t < (padded >> 1); t += kPrepThreads) {
+        const int lo = 2 * t - (t & (stride - 1));
+        const int hi = lo + stride;
+        const bool up = (lo & size) == 0;
+        const long long a = ids[lo], b = ids[hi];
+        if ((a > b) == up) {
+          ids[lo] = b;
+          ids[hi] = a;
+        }
+      }
+      __syncthreads();
+    }
+  // unique, compacted in place: every thread reads its chunk first, the writes (always to the left) come after a barrier
+  const int per = (padded + kPrepThreads - 1) / kPrepThreads;  // <= 16
+  long long mine[16];
+  int nmine = 0;
+  for (int q = 0; q < per; q++) {
+    const int i = tid * per + q;
+    if (i < padded) {
+      const long long v = ids[i];
+      if (v != kInf && (i == 0 || ids[i - 1] != v)) mine[nmine++] = v;
+    }
+  }
+  int incl = nmine;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const int v = __shfl_up_sync(0xffffffffu, incl, o);
+    if (lane >= o) incl += v;
+  }
+  if (lane == 31) s_warp[warp] = incl;
+  __syncthreads();
+  if (warp == 0) {
+    int w = s_warp[lane];
+    int wi = w;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const int v = __shfl_up_sync(0xffffffffu, wi, o);
+      if (lane >= o) wi += v;
+    }
+    s_warp[lane] = wi - w;
+    if (lane == 31) s_nuniq = wi;
+  }
+  __syncthreads();
+  {
+    int pos = s_warp[warp] + incl - nmine;
+    for (int q = 0; q < nmine; q++) ids[pos++] = mine[q];
+  }
+  __syncthreads();
+  const int nuniq = s_nuniq;
+  // rank of every local edge end
+  for (int t = tid; t < 2 * num_edges; t += kPrepThreads) {
+    const int e = t >> 1;
+    const long long v = (t & 1) ? (long long)jj[e] : (long long)ii[e];
+    int lo = 0, hi = nuniq;  // lower_bound
+    while (lo < hi) {
+      const int mid = (lo + hi) >> 1;
+      if (ids[mid] < v) lo = mid + 1; else hi = mid;
+    }
+    int r = lo;
+    if (r >= num_kf) {  // more distinct keyframe ids than rows of Twc/Xs: the reference would read out of bounds
+      r = -1;
+      atomicAdd(&s_bad, 1);
+    }
+    if (t & 1) {
+      je[e] = r;
+      s_je[e] = r;
+    } else {
+      ie[e] = r;
+      s_ie[e] = r;
+    }
+  }
+  __syncthreads();
+  if (tid == 0) state[kBadEdges] = s_bad;
+  // incidence lists (see incidence_kernel)
+  const int n_free = num_kf > 0 ? num_kf - 1 : 0;
+  for (int a = tid; a < n_free; a += kPrepThreads) {
+    int d = 0;
+    for (int e = 0; e < num_edges; e++) {
+      const int i = s_ie[e], j = s_je[e];
+      if (i < 0 || j < 0) continue;
+      d += (i - 1 == a) + (j - 1 == a);
+    }
+    s_deg[a] = d;
+  }
+  __syncthreads();
+  if (tid == 0) {
+    int run = 0;
+    for (int a = 0; a < n_free; a++) {
+      const int d = s_deg[a];
+      s_deg[a] = run;
+      inc_off[a] = run;
+      run += d;
+    }
+    s_deg[n_free] = run;
+    inc_off[n_free] = run;
+  }
+  __syncthreads();
+  for (int a = tid; a < n_free; a += kPrepThreads) {
+    const int beg = s_deg[a];
+    int o = beg;
+    for (int e = 0; e < num_edges; e++) {
+      const int i = s_ie[e], j = s_je[e];
+      if (i < 0 || j < 0) continue;
+      if (i - 1 == a) inc_list[o++] = 2 * e;
+      if (j - 1 == a) inc_list[o++] = 2 * e + 1;
+    }
+    for (int l = beg; l < o; l++) {
+      const int ent = inc_list[l];
+      const int e = ent >> 1;
+      int other = ((ent & 1) ? s_ie[e] : s_je[e]) - 1;
+      if (other >= 0 && other < a) {
+        bool first = true;
+        for (int l2 = beg; l2 < l; l2++) first = first && ((inc_other[l2] & 0x3fffffff) != other || inc_other[l2] < 0);
+        if (first) other |= 1 << 30;
+      }
+      inc_other[l] = other;
+    }
+  }
+}
+
 int launch_index_prep(const GnWs& ws, const int64_t* local_ii, const int64_t* local_jj, const int64_t* all_ii,
                       const int64_t* all_jj, int num_all_edges, cudaStream_t st) {
-  init_state_kernel<<<1, 32, 0, st>>>(ws.state());
-  M3R_LAUNCH_CHECK();
   const int E = ws.L.num_edges;
   const int count = 2 * num_all_edges;
+  if (count <= kPrepMaxCount) {
+    int padded = 2;
+    while (padded < count) padded <<= 1;
+    const size_t smem = sizeof(long long) * (size_t)padded + sizeof(int) * (size_t)(2 * E + ws.L.num_kf + 2);
+    if (smem <= 200 * 1024) {
+      static size_t attr = 0;
+      if (smem > 48 * 1024 && smem > attr) {
+        M3R_CUDA(cudaFuncSetAttribute(index_prep_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        attr = smem;
+      }
+      index_prep_kernel<<<1, kPrepThreads, smem, st>>>(all_ii, all_jj, num_all_edges, local_ii, local_jj, E,
+                                                         ws.L.num_kf, padded, ws.ie(), ws.je(), ws.inc_off(),
+                                                         ws.inc_list(), ws.inc_other(), ws.state());
+      M3R_LAUNCH_CHECK();
+      return M3R_OK;
+    }
+  }
+  init_state_kernel<<<1, 32, 0, st>>>(ws.state());
+  M3R_LAUNCH_CHECK();
   if (num_all_edges > 0) {
     concat_ids_kernel<<<ceil_div(num_all_edges, 256), 256, 0, st>>>(all_ii, all_jj, num_all_edges, ws.all_ids());
     M3R_LAUNCH_CHECK();

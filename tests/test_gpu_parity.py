@@ -205,6 +205,24 @@ def test_gn_medium_graph_vs_oracle(be, orc):
     assert np.linalg.norm(dx.cpu().numpy() - dx_o) / np.linalg.norm(dx_o) <= 2e-3  # 2nd-iteration dx is tiny
 
 
+def test_gn_loop_closure_graph_multi_cta_solver(be, orc):
+    """46 keyframes with loop-closure edges -> n = 315 > 224: the multi-CTA blocked Cholesky with fill-in from the
+    long-range edges (10 panels, last one partial), against the oracle's dense fp64 solve; pixel count a multiple of 4
+    (vector path of the packing pre-pass)."""
+    from mast3r_slam_ysh_b200 import synthetic as syn
+    nkf, h, w = 46, 16, 24
+    g = syn.make_gn_problem(nkf, h, w, syn.loop_closure_edges(nkf, n_loop=2, seed=3), seed=11, yaw_step_deg=5.0)
+    args = [g[k] for k in ("Xs", "Cs", "ii", "jj", "idx_ii2jj", "valid_match", "Q")]
+    P = (LO["sigma_ray"], LO["sigma_dist"], LO["C_conf"], LO["Q_conf"])
+    T_o = g["Twc"].numpy().copy()
+    (dx_o,), _ = orc.gauss_newton_rays(T_o, *[a.numpy() for a in args], *P, 1, 1e-8)
+    T = g["Twc"].to(DEV)
+    (dx,), info = be.gauss_newton_rays(T, *[a.to(DEV) for a in args], *P, 1, 1e-8, return_info=True)
+    assert info.cpu().numpy()[2] == 0  # no failed factorisation
+    assert np.linalg.norm(dx.cpu().numpy() - dx_o) / np.linalg.norm(dx_o) <= 1e-4  # north_star tolerance
+    assert np.linalg.norm(T.cpu().numpy() - T_o) / np.linalg.norm(T_o) <= 1e-4   # |dx| = 2.6 here: same bar on the poses
+
+
 def test_pose_retr_vs_oracle(be, orc):
     g = torch.Generator().manual_seed(5)
     poses = torch.randn(9, 8, generator=g)
