@@ -365,8 +365,15 @@ def matching_extra(be, syn, dev, torch):
         fn_ip = lambda: be.iter_proj(rays, pts, p0, mt["max_iter"], mt["lambda_init"], mt["convergence_thresh"])
         p1 = fn_ip()[0].long()
         fn_rf = lambda: be.refine_matches(D11, D21, p1, mt["radius"], mt["dilation_max"])
+        # whole match() of matching.py:8-91: fused device path (m3r_match) vs the reference's torch glue around the
+        # two drop-in kernels
+        from mast3r_slam_ysh_b200 import matching as mm
+        margs = (m["X11"], m["X21"], m["D11"], m["D21"])
+        fn_mf = lambda: mm.match(*margs)
+        fn_mu = lambda: mm.match_unfused(*margs)
         res = {}
-        for name, fn in (("iter_proj", fn_ip), ("refine_matches", fn_rf)):
+        for name, fn in (("iter_proj", fn_ip), ("refine_matches", fn_rf), ("match_fused", fn_mf),
+                         ("match_unfused_torch_glue", fn_mu)):
             for _ in range(3):
                 fn()
             torch.cuda.synchronize()
@@ -383,7 +390,7 @@ def matching_extra(be, syn, dev, torch):
         peak, _ = measured_peak()
         res["iter_proj_hbm_frac"] = ITER_PROJ_BYTES_PER_QUERY * b * N_PIX / (res["iter_proj_ms"] * 1e-3) / 1e9 / peak
         out[f"matching_b{b}"] = res
-        del m, rays, pts, p0, D11, D21
+        del m, rays, pts, p0, D11, D21, margs
     return out
 
 

@@ -42,6 +42,8 @@ SYMBOLS = {
     "m3r_iter_proj": (_i, [_vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _f, _f, _vp]),
     "m3r_refine_matches_f16": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _vp]),
     "m3r_refine_matches_f32": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _vp]),
+    "m3r_match": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _f, _f, _f, _i, _i, _vp]),
+    "m3r_ray_image": (_i, [_vp, _vp, _i, _i, _i, _vp]),
     "m3r_gn_workspace_bytes": (_sz, [_i, _i, _i]),
     "m3r_gauss_newton": (_i, [_PP, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _vp, _vp, _vp, _sz, _vp]),
     "m3r_gn_begin": (_i, [_PP, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _vp, _vp, _i, _vp, _sz, _vp]),

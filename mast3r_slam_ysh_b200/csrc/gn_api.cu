@@ -32,6 +32,20 @@ int sm_count() {
   return cached;
 }
 
+int keep_async_pool() {
+  static thread_local int ready_dev = -1;
+  int dev = 0;
+  M3R_CUDA(cudaGetDevice(&dev));
+  if (ready_dev != dev) {
+    cudaMemPool_t pool;
+    M3R_CUDA(cudaDeviceGetDefaultMemPool(&pool, dev));
+    uint64_t thr = UINT64_MAX;
+    M3R_CUDA(cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &thr));
+    ready_dev = dev;
+  }
+  return M3R_OK;
+}
+
 // ---- workspace layout ---------------------------------------------------------------------------------------------
 GnLayout gn_layout(int num_kf, int num_pts, int num_edges, int num_all_edges) {
   GnLayout L;

@@ -44,6 +44,8 @@ static inline int ceil_div(int a, int b) { return (a + b - 1) / b; }
 static inline long long ceil_div_ll(long long a, long long b) { return (a + b - 1) / b; }
 
 int sm_count();
+// keep stream-ordered scratch cached in the default pool across synchronisations (the default threshold returns it to the OS)
+int keep_async_pool();
 
 // ---- read-only vector loads -----------------------------------------------------------------------------------
 __device__ __forceinline__ float4 ldg4(const float4* p) { return __ldg(p); }

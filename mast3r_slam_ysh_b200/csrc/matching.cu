@@ -14,7 +14,7 @@
 #include <float.h>
 #include <stdlib.h>
 
-#include "m3r_common.cuh"
+#include "matching_core.cuh"
 
 namespace m3r {
 
@@ -153,41 +153,6 @@ __global__ void __launch_bounds__(256) repack_rays_kernel(const float* __restric
   P2[p] = __ldg(s + 8);
 }
 
-struct Bil {
-  float w11, w12, w21, w22;
-  int o22, o21, o12, o11;  // pixel offsets of (v,u), (v,u+1), (v+1,u), (v+1,u+1)
-};
-
-__device__ __forceinline__ Bil bil_setup(float u, float v, int w) {
-  Bil B;
-  const int u11 = static_cast<int>(floorf(u));
-  const int v11 = static_cast<int>(floorf(v));
-  const float du = __fsub_rn(u, static_cast<float>(u11));
-  const float dv = __fsub_rn(v, static_cast<float>(v11));
-  const float cu = __fsub_rn(1.0f, du), cv = __fsub_rn(1.0f, dv);  // exact (see header comment)
-  B.w11 = __fmul_rn(du, dv);
-  B.w12 = __fmul_rn(cu, dv);
-  B.w21 = __fmul_rn(du, cv);
-  B.w22 = __fmul_rn(cu, cv);
-  B.o22 = v11 * w + u11;
-  B.o21 = B.o22 + 1;
-  B.o12 = B.o22 + w;
-  B.o11 = B.o12 + 1;
-  return B;
-}
-
-// The reference binary (nvcc 12.9, default -fmad=true) evaluates its float expressions with these exact fused
-// sequences (read off its SASS); they are spelled out with non-contracting intrinsics so that this kernel's
-// rounding does not depend on how the compiler happens to contract a differently shaped program.
-//   w11*a11 + w12*a12 + w21*a21 + w22*a22  ->  fma(w22,a22, fma(w21,a21, fma(w11,a11, w12*a12)))
-//   x*x' + y*y' + z*z'                     ->  fma(z,z', fma(x,x', y*y'))
-__device__ __forceinline__ float bil(const Bil& B, float a11, float a12, float a21, float a22) {
-  return __fmaf_rn(B.w22, a22, __fmaf_rn(B.w21, a21, __fmaf_rn(B.w11, a11, __fmul_rn(B.w12, a12))));
-}
-__device__ __forceinline__ float dot3_ref(float x, float xp, float y, float yp, float z, float zp) {
-  return __fmaf_rn(z, zp, __fmaf_rn(x, xp, __fmul_rn(y, yp)));
-}
-
 __global__ void __launch_bounds__(128) iter_proj_v2_kernel(const float4* __restrict__ P0, const float4* __restrict__ P1,
                                                            const float* __restrict__ P2, const float* __restrict__ pts,
                                                            const float* __restrict__ p_init, float* __restrict__ p_new,
@@ -207,71 +172,8 @@ __global__ void __launch_bounds__(128) iter_proj_v2_kernel(const float4* __restr
   float v = fminf(fmaxf(pi.y, 1.0f), (float)(h - 2));
   const float tx = __ldg(pts + gid * 3 + 0), ty = __ldg(pts + gid * 3 + 1), tz = __ldg(pts + gid * 3 + 2);
 
-  float lambda = lambda_init;
   bool conv = false;
-  // sample cached at (u,v): raw ray, d/du, d/dv
-  float r0 = 0.f, r1 = 0.f, r2 = 0.f, gx0 = 0.f, gx1 = 0.f, gx2 = 0.f, gy0 = 0.f, gy1 = 0.f, gy2 = 0.f;
-  bool have_r = false, have_g = false;
-  Bil B = bil_setup(u, v, w);
-  for (int it = 0; it < max_iter; it++) {
-    if (!have_r) {
-      const float4 a11 = __ldg(p0 + B.o11), a12 = __ldg(p0 + B.o12), a21 = __ldg(p0 + B.o21), a22 = __ldg(p0 + B.o22);
-      r0 = bil(B, a11.x, a12.x, a21.x, a22.x);
-      r1 = bil(B, a11.y, a12.y, a21.y, a22.y);
-      r2 = bil(B, a11.z, a12.z, a21.z, a22.z);
-      gx0 = bil(B, a11.w, a12.w, a21.w, a22.w);
-    }
-    if (!have_g) {
-      const float4 c11 = __ldg(p1 + B.o11), c12 = __ldg(p1 + B.o12), c21 = __ldg(p1 + B.o21), c22 = __ldg(p1 + B.o22);
-      const float d11 = __ldg(p2 + B.o11), d12 = __ldg(p2 + B.o12), d21 = __ldg(p2 + B.o21), d22 = __ldg(p2 + B.o22);
-      gx1 = bil(B, c11.x, c12.x, c21.x, c22.x);
-      gx2 = bil(B, c11.y, c12.y, c21.y, c22.y);
-      gy0 = bil(B, c11.z, c12.z, c21.z, c22.z);
-      gy1 = bil(B, c11.w, c12.w, c21.w, c22.w);
-      gy2 = bil(B, d11, d12, d21, d22);
-    }
-    // normalise, residual, cost (matching_kernels.cu:186-198); 1.0/r_norm compiles to the IEEE fp32 reciprocal
-    float inv = __frcp_rn(__fsqrt_rn(dot3_ref(r0, r0, r1, r1, r2, r2)));
-    const float e0 = __fmaf_rn(r0, inv, -tx), e1 = __fmaf_rn(r1, inv, -ty), e2 = __fmaf_rn(r2, inv, -tz);
-    const float cost = dot3_ref(e0, e0, e1, e1, e2, e2);
-    // 2x2 LM system (:202-215)
-    const float A00 = __fadd_rn(dot3_ref(gx0, gx0, gx1, gx1, gx2, gx2), lambda);
-    const float A01 = dot3_ref(gx0, gy0, gx1, gy1, gx2, gy2);
-    const float A11 = __fadd_rn(dot3_ref(gy0, gy0, gy1, gy1, gy2, gy2), lambda);
-    const float s0 = dot3_ref(gx0, e0, gx1, e1, gx2, e2);  // = -b0
-    const float s1 = dot3_ref(gy0, e0, gy1, e1, gy2, e2);  // = -b1
-    const float det_inv = __frcp_rn(__fmaf_rn(A00, A11, -__fmul_rn(A01, A01)));
-    const float xu = __fmaf_rn(A01, s1, -__fmul_rn(s0, A11));  // A11*b0 - A01*b1
-    const float xv = __fmaf_rn(A01, s0, -__fmul_rn(s1, A00));  // -A01*b0 + A00*b1
-    const float u_new = fminf(fmaxf(__fmaf_rn(xu, det_inv, u), 1.0f), (float)(w - 2));
-    const float v_new = fminf(fmaxf(__fmaf_rn(xv, det_inv, v), 1.0f), (float)(h - 2));
-
-    // candidate cost (:225-256)
-    const Bil Bn = bil_setup(u_new, v_new, w);
-    const float4 a11 = __ldg(p0 + Bn.o11), a12 = __ldg(p0 + Bn.o12), a21 = __ldg(p0 + Bn.o21), a22 = __ldg(p0 + Bn.o22);
-    const float t0 = bil(Bn, a11.x, a12.x, a21.x, a22.x);
-    const float t1 = bil(Bn, a11.y, a12.y, a21.y, a22.y);
-    const float t2 = bil(Bn, a11.z, a12.z, a21.z, a22.z);
-    inv = __frcp_rn(__fsqrt_rn(dot3_ref(t0, t0, t1, t1, t2, t2)));
-    const float f0 = __fmaf_rn(t0, inv, -tx), f1 = __fmaf_rn(t1, inv, -ty), f2 = __fmaf_rn(t2, inv, -tz);
-    const float new_cost = dot3_ref(f0, f0, f1, f1, f2, f2);
-    if (new_cost < cost) {  // accept (:259-264): the ray sampled at the candidate becomes the cached ray
-      u = u_new;
-      v = v_new;
-      lambda = __double2float_rn((double)lambda * 0.1);
-      conv = new_cost < cost_thresh;
-      r0 = t0; r1 = t1; r2 = t2;
-      gx0 = bil(Bn, a11.w, a12.w, a21.w, a22.w);
-      B = Bn;
-      have_r = true;
-      have_g = false;
-    } else {  // reject (:265-268): same (u,v) next time, everything cached
-      lambda = __fmul_rn(lambda, 10.0f);
-      conv = cost < cost_thresh;
-      have_r = true;
-      have_g = true;
-    }
-  }
+  iter_proj_core(p0, p1, p2, tx, ty, tz, w, h, max_iter, lambda_init, cost_thresh, u, v, conv);
   reinterpret_cast<float2*>(p_new)[gid] = make_float2(u, v);
   converged[gid] = conv ? 1 : 0;
 }
@@ -295,62 +197,9 @@ __global__ void __launch_bounds__(128) refine_matches_f16_kernel(const uint4* __
     p1_new[gid] = p;
     return;
   }
-  __half2 q[NV * 4];
-#pragma unroll
-  for (int i = 0; i < NV; i++) {
-    const uint4 t = __ldg(D21 + gid * NV + i);
-    q[4 * i + 0] = *reinterpret_cast<const __half2*>(&t.x);
-    q[4 * i + 1] = *reinterpret_cast<const __half2*>(&t.y);
-    q[4 * i + 2] = *reinterpret_cast<const __half2*>(&t.z);
-    q[4 * i + 3] = *reinterpret_cast<const __half2*>(&t.w);
-  }
-  const uint4* __restrict__ img = D11 + (size_t)b * h * w * NV;
-  int u0 = (int)p.x, v0 = (int)p.y;
-  int u_new = u0, v_new = v0;
-  float max_score = 0.0f;  // cuda::std::numeric_limits<c10::Half>::min() == Half() == +0 (matching_kernels.cu:47)
-  for (int d = dilation_max; d > 0; d--) {
-    const int rd = radius * d;
-    const int diam = 2 * rd + 1;
-    for (int i = 0; i < diam; i += d) {
-      const int u = u0 - rd + i;
-      if (u < 0 || u >= w) continue;
-      for (int j = 0; j < diam; j += d) {
-        const int v = v0 - rd + j;
-        if (v < 0 || v >= h) continue;
-        const uint4* c = img + ((size_t)v * w + u) * NV;
-        __half score = __ushort_as_half(0);
-#pragma unroll
-        for (int k = 0; k < NV; k++) {
-          const uint4 t = __ldg(c + k);
-          const __half2 a0 = *reinterpret_cast<const __half2*>(&t.x);
-          const __half2 a1 = *reinterpret_cast<const __half2*>(&t.y);
-          const __half2 a2 = *reinterpret_cast<const __half2*>(&t.z);
-          const __half2 a3 = *reinterpret_cast<const __half2*>(&t.w);
-          __half2 pr;
-          pr = __hmul2_rn(q[4 * k + 0], a0);
-          score = __hadd_rn(score, __low2half(pr));
-          score = __hadd_rn(score, __high2half(pr));
-          pr = __hmul2_rn(q[4 * k + 1], a1);
-          score = __hadd_rn(score, __low2half(pr));
-          score = __hadd_rn(score, __high2half(pr));
-          pr = __hmul2_rn(q[4 * k + 2], a2);
-          score = __hadd_rn(score, __low2half(pr));
-          score = __hadd_rn(score, __high2half(pr));
-          pr = __hmul2_rn(q[4 * k + 3], a3);
-          score = __hadd_rn(score, __low2half(pr));
-          score = __hadd_rn(score, __high2half(pr));
-        }
-        const float s = __half2float(score);
-        if (s > max_score) {
-          max_score = s;
-          u_new = u;
-          v_new = v;
-        }
-      }
-    }
-    u0 = u_new;
-    v0 = v_new;
-  }
+  int u_new, v_new;
+  refine_core_f16<FDIM>(D21, D11 + (size_t)b * h * w * NV, gid, h, w, radius, dilation_max, (int)p.x, (int)p.y, u_new,
+                        v_new);
   p1_new[gid] = make_longlong2((long long)u_new, (long long)v_new);
 }
 
@@ -449,17 +298,9 @@ extern "C" int m3r_iter_proj(const float* rays_img_with_grad, const float* pts_3
   // stream-ordered scratch for the repacked image (36 B per pixel, 16-byte aligned planes); no host sync
   const long long npix = (long long)b * h * w;
   const size_t plane = align_up((size_t)npix * sizeof(float4), 256);
-  {  // keep freed scratch cached in the default pool across synchronisations (default threshold 0 returns it to the OS)
-    static thread_local int pool_ready_dev = -1;
-    int dev = 0;
-    M3R_CUDA(cudaGetDevice(&dev));
-    if (pool_ready_dev != dev) {
-      cudaMemPool_t pool;
-      M3R_CUDA(cudaDeviceGetDefaultMemPool(&pool, dev));
-      uint64_t thr = UINT64_MAX;
-      M3R_CUDA(cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &thr));
-      pool_ready_dev = dev;
-    }
+  {
+    const int rc = keep_async_pool();
+    if (rc != M3R_OK) return rc;
   }
   void* scratch = nullptr;
   M3R_CUDA(cudaMallocAsync(&scratch, 2 * plane + align_up((size_t)npix * sizeof(float), 256), st));

@@ -278,15 +278,16 @@ def prep_for_iter_proj(X11, X21, idx_init=None):
     return rays_with_grad, pts3d_norm, p_init
 
 
-def make_match_problem(b, h, w, seed=1235, device="cpu", yaw_step_deg=12.0, fdim=24, warm_start=False):
+def make_match_problem(b, h, w, seed=1235, device="cpu", yaw_step_deg=12.0, fdim=24, warm_start=False,
+                       point_noise=0.005):
     """b image pairs (frame 2c+1 seen from camera 2c): X11, X21 (b,h,w,3) f32, D11, D21 (b,h,w,fdim) f32 plus
     the three iter_proj inputs and the int64 p1 a caller would hand to refine_matches."""
     T = camera_poses(2 * b, yaw_step_deg=yaw_step_deg, seed=seed)
     X11, X21, D11, D21 = [], [], [], []
     for p in range(b):
         T1, T2 = T[2 * p].to(device), T[2 * p + 1].to(device)
-        x1 = pointmap(T[2 * p], h, w, seed=seed * 100 + 2 * p, device=device) * T1[7]  # metric, camera 1
-        x2 = pointmap(T[2 * p + 1], h, w, seed=seed * 100 + 2 * p + 1, device=device)
+        x1 = pointmap(T[2 * p], h, w, noise=point_noise, seed=seed * 100 + 2 * p, device=device) * T1[7]  # metric, camera 1
+        x2 = pointmap(T[2 * p + 1], h, w, noise=point_noise, seed=seed * 100 + 2 * p + 1, device=device)
         x2_w = sim3_act(T2, x2)
         T1m = T1.clone()
         T1m[7] = 1.0
