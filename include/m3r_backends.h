@@ -164,10 +164,11 @@ M3R_API int m3r_pose_retr(float* poses, const float* dx, int num_poses, int num_
 /* Fused dense matching = the whole of match_iterative_proj (mast3r_slam/matching.py:52-91): ray image +
  * Scharr gradients (matching.py:25-49, image.py:5-38), query normalisation, iter_proj (gn.h:89-95), occlusion test
  * (matching.py:70-76), refine_matches in fp16 (gn.h:112-117, skipped when radius == 0), pixel_to_lin (:14-16).
- *   X11, X21 (b,h,w,3) f32; D11_f16 (b,h,w,fdim), D21_f16 (b,h*w,fdim) fp16 (fdim 16 or 24, 16-byte aligned);
+ *   X11, X21 (b,h,w,3) f32; D11 (b,h,w,fdim), D21 (b,h*w,fdim) f32 as match() receives them (fdim 16 or 24, 16-byte
+ *   aligned; rounded to fp16 on the device like the glue's .half(), matching.py:80-81);
  *   idx_1_to_2_init (b,h*w) int64 or NULL (identity); out: idx_1_to_2 (b,h*w) int64, valid_match (b,h*w) bool.
  * Additive: the reference has no single entry point for this, its Python glue calls iter_proj and refine_matches. */
-M3R_API int m3r_match(const float* X11, const float* X21, const uint16_t* D11_f16, const uint16_t* D21_f16,
+M3R_API int m3r_match(const float* X11, const float* X21, const float* D11, const float* D21,
                       const int64_t* idx_1_to_2_init, int64_t* idx_1_to_2, uint8_t* valid_match, int b, int h, int w,
                       int fdim, int max_iter, float lambda_init, float cost_thresh, float dist_thresh, int radius,
                       int dilation_max, void* stream);

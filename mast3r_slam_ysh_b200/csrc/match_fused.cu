@@ -1,5 +1,5 @@
 // Fused dense matching for sm_100a: the whole of match_iterative_proj (mast3r_slam/matching.py:52-91) on the device
-// in four launches -- SURVEY.md section 8(f) rank 1 ("fuse the Python pre/post of matching").  The reference builds a
+// in five launches -- SURVEY.md section 8(f) rank 1 ("fuse the Python pre/post of matching").  The reference builds a
 // 9-channel ray image with ~6 eager torch ops (normalize, two depthwise 3x3 convolutions on a reflect-padded copy, cat,
 // permute, contiguous; matching.py:25-49, image.py:5-38), normalises the query points, expands the initial indices to
 // float pixels, calls iter_proj, gathers X11 at the matches for the occlusion test (matching.py:70-76), calls
@@ -9,7 +9,8 @@
 //                          the 36-byte AoS image and its repack are never materialised
 //   match_proj_kernel    : normalise X21 on the fly, initial pixel from the index, 10 LM iterations (iter_proj_core),
 //                          truncation to integer pixels, occlusion test against X11, valid flag
-//   match_refine_kernel  : descriptor refinement (refine_core_f16) + pixel -> linear index
+//   desc_half_kernel     : D11 fp32 -> fp16 (the .half() of matching.py:80)
+//   match_refine_kernel  : D21 -> fp16 on the fly, descriptor refinement (refine_core_f16) + pixel -> linear index
 // Additive entry point (m3r_match); the five legacy signatures are untouched.
 #include "matching_core.cuh"
 
@@ -92,8 +93,24 @@ __global__ void __launch_bounds__(128) match_proj_kernel(const float4* __restric
   valid[gid] = (conv && dist < dist_thresh) ? 1 : 0;
 }
 
+// fp32 (h,w,fdim) descriptors -> fp16, same layout (the .half() of matching.py:80).  A chunk-planar repack was tried
+// and measured no faster (0.377 vs 0.386 ms at 512x384): the refinement is bound by L1 tag look-ups of scattered
+// 16-byte gathers, not by the 48-byte stride (tools/time_refine.py, r1).
+__global__ void __launch_bounds__(256) desc_half_kernel(const float* __restrict__ D, uint4* __restrict__ P,
+                                                        long long total) {
+  const long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;  // one 8-float chunk per thread
+  if (t >= total) return;
+  const float4 a = __ldg(reinterpret_cast<const float4*>(D) + 2 * t), c = __ldg(reinterpret_cast<const float4*>(D) + 2 * t + 1);
+  uint4 o;
+  *reinterpret_cast<__half2*>(&o.x) = __floats2half2_rn(a.x, a.y);
+  *reinterpret_cast<__half2*>(&o.y) = __floats2half2_rn(a.z, a.w);
+  *reinterpret_cast<__half2*>(&o.z) = __floats2half2_rn(c.x, c.y);
+  *reinterpret_cast<__half2*>(&o.w) = __floats2half2_rn(c.z, c.w);
+  P[t] = o;
+}
+
 template <int FDIM>
-__global__ void __launch_bounds__(128) match_refine_kernel(const uint4* __restrict__ D11, const uint4* __restrict__ D21,
+__global__ void __launch_bounds__(128) match_refine_kernel(const uint4* __restrict__ planes, const float* __restrict__ D21,
                                                            const int2* __restrict__ p1, int64_t* __restrict__ idx_out,
                                                            long long total, int n, int h, int w, int radius,
                                                            int dilation_max) {
@@ -102,8 +119,14 @@ __global__ void __launch_bounds__(128) match_refine_kernel(const uint4* __restri
   if (gid >= total) return;
   const int b = (int)(gid / n);
   const int2 p = p1[gid];
+  __half2 q[FDIM / 2];
+  load_query_f32<FDIM>(D21, gid, q);
   int u_new, v_new;
-  refine_core_f16<FDIM>(D21, D11 + (size_t)b * h * w * NV, gid, h, w, radius, dilation_max, p.x, p.y, u_new, v_new);
+  if (radius == 3)
+    refine_core_f16<FDIM, 3>(q, planes + (size_t)b * NV * h * w, NV, 1, h, w, 3, dilation_max, p.x, p.y, u_new, v_new);
+  else
+    refine_core_f16<FDIM, 0>(q, planes + (size_t)b * NV * h * w, NV, 1, h, w, radius, dilation_max, p.x, p.y, u_new,
+                             v_new);
   idx_out[gid] = (int64_t)u_new + (int64_t)w * (int64_t)v_new;  // pixel_to_lin (matching.py:14-16)
 }
 
@@ -119,7 +142,7 @@ __global__ void __launch_bounds__(256) match_lin_kernel(const int2* __restrict__
 
 using namespace m3r;
 
-extern "C" int m3r_match(const float* X11, const float* X21, const uint16_t* D11_f16, const uint16_t* D21_f16,
+extern "C" int m3r_match(const float* X11, const float* X21, const float* D11, const float* D21,
                          const int64_t* idx_1_to_2_init, int64_t* idx_1_to_2, uint8_t* valid_match, int b, int h, int w,
                          int fdim, int max_iter, float lambda_init, float cost_thresh, float dist_thresh, int radius,
                          int dilation_max, void* stream) {
@@ -131,9 +154,9 @@ extern "C" int m3r_match(const float* X11, const float* X21, const uint16_t* D11
   M3R_REQUIRE((long long)h * w * 9 < (1LL << 31), "match: image too large for 32-bit offsets");
   const bool refine = radius > 0 && dilation_max > 0;
   if (refine) {
-    M3R_REQUIRE(D11_f16 && D21_f16, "match: null descriptor pointer");
-    if (!((fdim == 24 || fdim == 16) && ((((uintptr_t)D11_f16 | (uintptr_t)D21_f16) & 15) == 0))) {
-      set_error("match: fused path needs 16-byte aligned fp16 descriptors with fdim 16 or 24 (got %d)", fdim);
+    M3R_REQUIRE(D11 && D21, "match: null descriptor pointer");
+    if (!((fdim == 24 || fdim == 16) && ((((uintptr_t)D11 | (uintptr_t)D21) & 15) == 0))) {
+      set_error("match: fused path needs 16-byte aligned fp32 descriptors with fdim 16 or 24 (got %d)", fdim);
       return M3R_ERR_UNSUPPORTED;
     }
   }
@@ -141,17 +164,20 @@ extern "C" int m3r_match(const float* X11, const float* X21, const uint16_t* D11
   const size_t plane = align_up((size_t)npix * sizeof(float4), 256);
   const size_t p2b = align_up((size_t)npix * sizeof(float), 256);
   const size_t p1b = align_up((size_t)npix * sizeof(int2), 256);
+  const int nv = refine ? fdim / 8 : 0;
+  const size_t dpb = align_up((size_t)npix * nv * sizeof(uint4), 256);
   {
     const int rc = keep_async_pool();
     if (rc != M3R_OK) return rc;
   }
   void* scratch = nullptr;
-  M3R_CUDA(cudaMallocAsync(&scratch, 3 * plane + p2b + p1b, st));
+  M3R_CUDA(cudaMallocAsync(&scratch, 3 * plane + p2b + p1b + dpb, st));
   float4* R = (float4*)scratch;
   float4* P0 = (float4*)((char*)scratch + plane);
   float4* P1 = (float4*)((char*)scratch + 2 * plane);
   float* P2 = (float*)((char*)scratch + 3 * plane);
   int2* p1 = (int2*)((char*)scratch + 3 * plane + p2b);
+  uint4* dplanes = (uint4*)((char*)scratch + 3 * plane + p2b + p1b);
   const unsigned g256 = (unsigned)ceil_div_ll(npix, 256), g128 = (unsigned)ceil_div_ll(npix, 128);
   ray_normalize_kernel<<<g256, 256, 0, st>>>(X11, R, npix);
   M3R_LAUNCH_CHECK();
@@ -162,12 +188,14 @@ extern "C" int m3r_match(const float* X11, const float* X21, const uint16_t* D11
   M3R_LAUNCH_CHECK();
   if (!refine) {
     match_lin_kernel<<<g256, 256, 0, st>>>(p1, idx_1_to_2, npix, w);
-  } else if (fdim == 24) {
-    match_refine_kernel<24><<<g128, 128, 0, st>>>((const uint4*)D11_f16, (const uint4*)D21_f16, p1, idx_1_to_2, npix,
-                                                  h * w, h, w, radius, dilation_max);
   } else {
-    match_refine_kernel<16><<<g128, 128, 0, st>>>((const uint4*)D11_f16, (const uint4*)D21_f16, p1, idx_1_to_2, npix,
-                                                  h * w, h, w, radius, dilation_max);
+    const long long chunks = npix * nv;
+    desc_half_kernel<<<(unsigned)ceil_div_ll(chunks, 256), 256, 0, st>>>(D11, dplanes, chunks);
+    M3R_LAUNCH_CHECK();
+    if (fdim == 24)
+      match_refine_kernel<24><<<g128, 128, 0, st>>>(dplanes, D21, p1, idx_1_to_2, npix, h * w, h, w, radius, dilation_max);
+    else
+      match_refine_kernel<16><<<g128, 128, 0, st>>>(dplanes, D21, p1, idx_1_to_2, npix, h * w, h, w, radius, dilation_max);
   }
   M3R_LAUNCH_CHECK();
   M3R_CUDA(cudaFreeAsync(scratch, st));

@@ -197,9 +197,15 @@ __global__ void __launch_bounds__(128) refine_matches_f16_kernel(const uint4* __
     p1_new[gid] = p;
     return;
   }
+  __half2 q[FDIM / 2];
+  load_query_f16<FDIM>(D21, gid, q);
   int u_new, v_new;
-  refine_core_f16<FDIM>(D21, D11 + (size_t)b * h * w * NV, gid, h, w, radius, dilation_max, (int)p.x, (int)p.y, u_new,
-                        v_new);
+  if (radius == 3)  // config/base.yaml matching.radius: the 7 candidates of a scan column are fetched together
+    refine_core_f16<FDIM, 3>(q, D11 + (size_t)b * NV * h * w, NV, 1, h, w, 3, dilation_max, (int)p.x, (int)p.y, u_new,
+                             v_new);
+  else
+    refine_core_f16<FDIM, 0>(q, D11 + (size_t)b * NV * h * w, NV, 1, h, w, radius, dilation_max, (int)p.x, (int)p.y,
+                             u_new, v_new);
   p1_new[gid] = make_longlong2((long long)u_new, (long long)v_new);
 }
 
@@ -346,19 +352,17 @@ extern "C" int m3r_refine_matches_f16(const uint16_t* D11, const uint16_t* D21, 
   cudaStream_t st = (cudaStream_t)stream;
   const long long total = (long long)b * n;
   const bool aligned = (((uintptr_t)D11 | (uintptr_t)D21) & 15) == 0;
-  if (fdim == 24 && aligned) {
+  if ((fdim == 24 || fdim == 16) && aligned && (long long)h * w * (fdim / 8) < (1LL << 31)) {
     const int threads = 128;
     const unsigned blocks = (unsigned)ceil_div_ll(total, threads);
-    refine_matches_f16_kernel<24><<<blocks, threads, 0, st>>>((const uint4*)D11, (const uint4*)D21, (const longlong2*)p1,
-                                                              (longlong2*)p1_new, total, n, h, w, radius, dilation_max);
-    M3R_LAUNCH_CHECK();
-    return M3R_OK;
-  }
-  if (fdim == 16 && aligned) {
-    const int threads = 128;
-    const unsigned blocks = (unsigned)ceil_div_ll(total, threads);
-    refine_matches_f16_kernel<16><<<blocks, threads, 0, st>>>((const uint4*)D11, (const uint4*)D21, (const longlong2*)p1,
-                                                              (longlong2*)p1_new, total, n, h, w, radius, dilation_max);
+    if (fdim == 24)
+      refine_matches_f16_kernel<24><<<blocks, threads, 0, st>>>((const uint4*)D11, (const uint4*)D21,
+                                                                (const longlong2*)p1, (longlong2*)p1_new, total, n, h, w,
+                                                                radius, dilation_max);
+    else
+      refine_matches_f16_kernel<16><<<blocks, threads, 0, st>>>((const uint4*)D11, (const uint4*)D21,
+                                                                (const longlong2*)p1, (longlong2*)p1_new, total, n, h, w,
+                                                                radius, dilation_max);
     M3R_LAUNCH_CHECK();
     return M3R_OK;
   }

@@ -115,14 +115,13 @@ __device__ __forceinline__ void iter_proj_core(const float4* __restrict__ p0, co
   conv_out = conv;
 }
 
-// One query of refine_matches in fp16 (matching_kernels.cu:25-81): descriptor row D21[gid], descriptor image `img` of
-// its batch item, start (u0, v0); returns the refined pixel.  Rounding after every multiply and add (see matching.cu).
+// One query of refine_matches in fp16 (matching_kernels.cu:25-81): query descriptor q (fp16 pairs), descriptor image of
+// the query's batch item, start (u0, v0); returns the refined pixel.  Rounding after every multiply and add (see
+// matching.cu).  The image is addressed as img[pixel * pstride + chunk * cstride] in 16-byte units: (NV, 1) for the
+// reference's (h,w,fdim) layout.
 template <int FDIM>
-__device__ __forceinline__ void refine_core_f16(const uint4* __restrict__ D21, const uint4* __restrict__ img,
-                                                long long gid, int h, int w, int radius, int dilation_max, int u0,
-                                                int v0, int& u_out, int& v_out) {
-  constexpr int NV = FDIM / 8;  // uint4 per descriptor
-  __half2 q[NV * 4];
+__device__ __forceinline__ void load_query_f16(const uint4* __restrict__ D21, long long gid, __half2 (&q)[FDIM / 2]) {
+  constexpr int NV = FDIM / 8;
 #pragma unroll
   for (int i = 0; i < NV; i++) {
     const uint4 t = __ldg(D21 + gid * NV + i);
@@ -131,6 +130,54 @@ __device__ __forceinline__ void refine_core_f16(const uint4* __restrict__ D21, c
     q[4 * i + 2] = *reinterpret_cast<const __half2*>(&t.z);
     q[4 * i + 3] = *reinterpret_cast<const __half2*>(&t.w);
   }
+}
+
+template <int FDIM>
+__device__ __forceinline__ void load_query_f32(const float* __restrict__ D21, long long gid, __half2 (&q)[FDIM / 2]) {
+#pragma unroll
+  for (int i = 0; i < FDIM / 4; i++) {  // .half() of the reference glue (matching.py:81): round to nearest even
+    const float4 t = __ldg(reinterpret_cast<const float4*>(D21 + gid * FDIM) + i);
+    q[2 * i + 0] = __floats2half2_rn(t.x, t.y);
+    q[2 * i + 1] = __floats2half2_rn(t.z, t.w);
+  }
+}
+
+// fp16 score of one candidate: a product and a sum rounded after every operation, in descriptor order
+template <int NV>
+__device__ __forceinline__ float score_f16(const __half2* q, const uint4* t) {
+  __half score = __ushort_as_half(0);
+#pragma unroll
+  for (int k = 0; k < NV; k++) {
+    const __half2 a0 = *reinterpret_cast<const __half2*>(&t[k].x);
+    const __half2 a1 = *reinterpret_cast<const __half2*>(&t[k].y);
+    const __half2 a2 = *reinterpret_cast<const __half2*>(&t[k].z);
+    const __half2 a3 = *reinterpret_cast<const __half2*>(&t[k].w);
+    __half2 pr;
+    pr = __hmul2_rn(q[4 * k + 0], a0);
+    score = __hadd_rn(score, __low2half(pr));
+    score = __hadd_rn(score, __high2half(pr));
+    pr = __hmul2_rn(q[4 * k + 1], a1);
+    score = __hadd_rn(score, __low2half(pr));
+    score = __hadd_rn(score, __high2half(pr));
+    pr = __hmul2_rn(q[4 * k + 2], a2);
+    score = __hadd_rn(score, __low2half(pr));
+    score = __hadd_rn(score, __high2half(pr));
+    pr = __hmul2_rn(q[4 * k + 3], a3);
+    score = __hadd_rn(score, __low2half(pr));
+    score = __hadd_rn(score, __high2half(pr));
+  }
+  return __half2float(score);
+}
+
+// RADIUS > 0: compile-time radius; the 2*RADIUS+1 candidates of one scan column are fetched together (all their loads
+// in flight before the first score is reduced) -- the kernel is bound by dependent L1/L2 round trips, one candidate
+// at a time, otherwise.  RADIUS == 0: run-time radius, one candidate at a time.  Scan order and the strict-greater
+// argmax are the reference's (u offset outer, v offset inner, matching_kernels.cu:51-69).
+template <int FDIM, int RADIUS>
+__device__ __forceinline__ void refine_core_f16(const __half2 (&q)[FDIM / 2], const uint4* __restrict__ img, int pstride,
+                                                int cstride, int h, int w, int radius, int dilation_max, int u0, int v0,
+                                                int& u_out, int& v_out) {
+  constexpr int NV = FDIM / 8;  // uint4 per descriptor
   int u_new = u0, v_new = v0;
   float max_score = 0.0f;  // cuda::std::numeric_limits<c10::Half>::min() == Half() == +0 (matching_kernels.cu:47)
   for (int d = dilation_max; d > 0; d--) {
@@ -139,37 +186,42 @@ __device__ __forceinline__ void refine_core_f16(const uint4* __restrict__ D21, c
     for (int i = 0; i < diam; i += d) {
       const int u = u0 - rd + i;
       if (u < 0 || u >= w) continue;
-      for (int j = 0; j < diam; j += d) {
-        const int v = v0 - rd + j;
-        if (v < 0 || v >= h) continue;
-        const uint4* c = img + ((size_t)v * w + u) * NV;
-        __half score = __ushort_as_half(0);
+      if (RADIUS > 0) {
+        constexpr int NJ = 2 * RADIUS + 1;
+        uint4 t[NJ][NV];
+        bool in[NJ];
 #pragma unroll
-        for (int k = 0; k < NV; k++) {
-          const uint4 t = __ldg(c + k);
-          const __half2 a0 = *reinterpret_cast<const __half2*>(&t.x);
-          const __half2 a1 = *reinterpret_cast<const __half2*>(&t.y);
-          const __half2 a2 = *reinterpret_cast<const __half2*>(&t.z);
-          const __half2 a3 = *reinterpret_cast<const __half2*>(&t.w);
-          __half2 pr;
-          pr = __hmul2_rn(q[4 * k + 0], a0);
-          score = __hadd_rn(score, __low2half(pr));
-          score = __hadd_rn(score, __high2half(pr));
-          pr = __hmul2_rn(q[4 * k + 1], a1);
-          score = __hadd_rn(score, __low2half(pr));
-          score = __hadd_rn(score, __high2half(pr));
-          pr = __hmul2_rn(q[4 * k + 2], a2);
-          score = __hadd_rn(score, __low2half(pr));
-          score = __hadd_rn(score, __high2half(pr));
-          pr = __hmul2_rn(q[4 * k + 3], a3);
-          score = __hadd_rn(score, __low2half(pr));
-          score = __hadd_rn(score, __high2half(pr));
+        for (int jj = 0; jj < NJ; jj++) {
+          const int v = v0 - rd + jj * d;
+          in[jj] = v >= 0 && v < h;
+          const uint4* c = img + (size_t)((in[jj] ? v : 0) * w + u) * pstride;
+#pragma unroll
+          for (int k = 0; k < NV; k++) t[jj][k] = in[jj] ? __ldg(c + (size_t)k * cstride) : make_uint4(0, 0, 0, 0);
         }
-        const float s = __half2float(score);
-        if (s > max_score) {
-          max_score = s;
-          u_new = u;
-          v_new = v;
+#pragma unroll
+        for (int jj = 0; jj < NJ; jj++) {
+          if (!in[jj]) continue;
+          const float s = score_f16<NV>(q, t[jj]);
+          if (s > max_score) {
+            max_score = s;
+            u_new = u;
+            v_new = v0 - rd + jj * d;
+          }
+        }
+      } else {
+        for (int j = 0; j < diam; j += d) {
+          const int v = v0 - rd + j;
+          if (v < 0 || v >= h) continue;
+          const uint4* c = img + (size_t)(v * w + u) * pstride;
+          uint4 t[NV];
+#pragma unroll
+          for (int k = 0; k < NV; k++) t[k] = __ldg(c + (size_t)k * cstride);
+          const float s = score_f16<NV>(q, t);
+          if (s > max_score) {
+            max_score = s;
+            u_new = u;
+            v_new = v;
+          }
         }
       }
     }

@@ -55,8 +55,8 @@ def match(X11, X21, D11, D21, idx_1_to_2_init=None, cfg=None):
     n = h * w
     refine = c["radius"] > 0
     if refine:
-        D11h = D11.half().contiguous()  # matching.py:80-81
-        D21h = D21.reshape(b, n, -1).half().contiguous()
+        D11h = D11.float().contiguous()  # fp32 in: the .half() of matching.py:80-81 happens on the device
+        D21h = D21.reshape(b, n, -1).float().contiguous()
         fdim = D11h.shape[-1]
     else:
         D11h = D21h = None
