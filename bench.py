@@ -316,6 +316,7 @@ def run_ours(args):
     extra = {}
     if rank == 0:
         extra = matching_extra(be, syn, dev, torch)
+        extra["tracker"] = tracker_extra(syn, dev, torch)
         extra["hessian_kernel_ms"] = hess_ms
         extra["solve_other_ms_per_iter"] = value - hess_ms
         extra["iterations_executed"] = iters
@@ -392,6 +393,45 @@ def matching_extra(be, syn, dev, torch):
         out[f"matching_b{b}"] = res
         del m, rays, pts, p0, D11, D21, margs
     return out
+
+
+def tracker_extra(syn, dev, torch):
+    """BASELINE.json configs[0] workload (one 512x384 pair, FrameTracker.opt_pose_ray_dist_sim3 with the thresholds of
+    config/base.yaml) on the device tracker kernel (m3r_track_rays), next to the reference's own
+    formulation run here: the torch-eager restatement (oracle/tracker_torch.py) on the same GPU -- what the reference's
+    tracker executes on a CUDA device -- and on the host cores (the CPU baseline of configs[0])."""
+    from mast3r_slam_ysh_b200 import tracker as trk
+    from oracle import tracker_torch as tt
+    t = syn.make_track_problem(H, W, seed=1234, device="cpu")
+    d = {k: (v.to(dev) if isinstance(v, torch.Tensor) else v) for k, v in t.items()}
+    fn = lambda: trk.opt_pose_ray_dist_sim3(d["Xf"], d["Xk"], d["T_WCf"], d["T_WCk"], d["Qk"], d["valid"], check=False,
+                                            return_info=True)
+    for _ in range(3):
+        info = fn()[2]
+    torch.cuda.synchronize()
+    a, c = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    reps = 20
+    a.record()
+    for _ in range(reps):
+        fn()
+    c.record()
+    torch.cuda.synchronize()
+    ms = a.elapsed_time(c) / reps
+    its = info.iterations
+    # the reference's formulation, eager torch on the same GPU (a .item() sync per iteration, as tracker.py:166)
+    eager = []
+    for rep in range(4):
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        _, _, its_e = tt.opt_pose_ray_dist_sim3(d["Xf"], d["Xk"], tt.Sim3(d["T_WCf"].clone()), tt.Sim3(d["T_WCk"].clone()),
+                                                d["Qk"], d["valid"])
+        torch.cuda.synchronize()
+        if rep:
+            eager.append((time.perf_counter() - t0) * 1e3)
+    eager.sort()
+    return dict(device_solve_ms=ms, device_iters=its, device_ms_per_iter=ms / max(its, 1),
+                torch_eager_gpu_solve_ms=eager[len(eager) // 2], torch_eager_gpu_iters=its_e,
+                what="tracker.opt_pose_ray_dist_sim3, 1 pair 512x384, config/base.yaml thresholds")
 
 
 def main():

@@ -177,6 +177,31 @@ M3R_API int m3r_match(const float* X11, const float* X21, const float* D11, cons
  * Scharr d/du, d/dv on the reflect-padded ray image -- the first argument of m3r_iter_proj. */
 M3R_API int m3r_ray_image(const float* X11, float* rays_img_with_grad, int b, int h, int w, void* stream);
 
+/* Frame-tracker pose solve on the device: the whole Gauss-Newton loop of
+ * FrameTracker.opt_pose_ray_dist_sim3 (mast3r_slam/tracker.py:173-214) in one persistent kernel -- relative pose
+ * T_CkCf = T_WCk^-1 * T_WCf, point-to-ray/distance residuals with Huber weights (FrameTracker.solve, :156-171), 7x7
+ * Cholesky, retraction, check_convergence (nonlinear_optimizer.py:5-25), T_WCf = T_WCk * T_CkCf.
+ *   Xf (n,3) frame points gathered by the match index, Xk (n,3) keyframe points, Qk (n) f32, valid (n) bool,
+ *   T_WCf / T_WCk: 8 floats [t, q_xyzw, s] (lietorch Sim3 .data); all device pointers.
+ *   out: T_WCf_out, T_CkCf_out (8 floats each, must not alias the inputs), info[2] = {iterations executed,
+ *   status: 0 ok, 1 = H not positive definite (the reference raises there and skips the frame, tracker.py:89-91)},
+ *   cost_out[1] = last 0.5 b^T b.  n is bounded by the shared-memory residency (about 1.0e6 points on a B200).
+ * Additive: the reference runs this loop as eager torch ops with one .item() sync per iteration. */
+M3R_API int m3r_track_rays(const float* Xf, const float* Xk, const float* T_WCf, const float* T_WCk, const float* Qk,
+                           const uint8_t* valid, long long n, double sigma_ray, double sigma_dist, double huber_k,
+                           int max_iters, double rel_error, double delta_norm, float* T_WCf_out, float* T_CkCf_out,
+                           int32_t* info, double* cost_out, void* stream);
+
+/* FrameTracker.opt_pose_calib_sim3 (tracker.py:216-266): pixel + log-depth residuals through project_calib
+ * (geometry.py:63-108).  meas_k (n,3) = [u, v, log z_k] and valid_meas_k (n) bool as get_points_poses builds them
+ * (tracker.py:141-150), K 3x3 row-major on the device, img_h/img_w and pixel_border/depth_eps as in config["tracking"]. */
+M3R_API int m3r_track_calib(const float* Xf, const float* meas_k, const float* T_WCf, const float* T_WCk,
+                            const float* Qk, const uint8_t* valid, const uint8_t* valid_meas_k, const float* K,
+                            long long n, int img_h, int img_w, double sigma_pixel, double sigma_depth,
+                            double pixel_border, double depth_eps, double huber_k, int max_iters, double rel_error,
+                            double delta_norm, float* T_WCf_out, float* T_CkCf_out, int32_t* info, double* cost_out,
+                            void* stream);
+
 /* diagnostics: phase timeline of the fused solver kernel.  dev_buf = 2*cap device uint64; [0] counts the marks that
  * follow as (tag, globaltimer ns) pairs written by CTA 0; pass NULL to switch it off (default).  No reference
  * counterpart (the reference's solve runs on the host, gn_kernels.cu:1199-1222). */

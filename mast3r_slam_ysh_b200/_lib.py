@@ -33,6 +33,7 @@ class GnParams(C.Structure):
 
 # name -> (restype, argtypes); every symbol include/m3r_backends.h declares
 _vp, _i, _f, _sz = C.c_void_p, C.c_int, C.c_float, C.c_size_t
+_ll, _d = C.c_longlong, C.c_double
 _PP = C.POINTER(GnParams)
 SYMBOLS = {
     "m3r_abi_version": (_i, []),
@@ -44,6 +45,9 @@ SYMBOLS = {
     "m3r_refine_matches_f32": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _vp]),
     "m3r_match": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _f, _f, _f, _i, _i, _vp]),
     "m3r_ray_image": (_i, [_vp, _vp, _i, _i, _i, _vp]),
+    "m3r_track_rays": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _ll, _d, _d, _d, _i, _d, _d, _vp, _vp, _vp, _vp, _vp]),
+    "m3r_track_calib": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _ll, _i, _i, _d, _d, _d, _d, _d, _i, _d, _d,
+                             _vp, _vp, _vp, _vp, _vp]),
     "m3r_gn_workspace_bytes": (_sz, [_i, _i, _i]),
     "m3r_gauss_newton": (_i, [_PP, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _vp, _vp, _vp, _sz, _vp]),
     "m3r_gn_begin": (_i, [_PP, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _vp, _vp, _i, _vp, _sz, _vp]),

@@ -253,6 +253,30 @@ def make_gn_problem(num_kf, h, w, edges, seed=1236, device="cpu", calib=False, p
                 all_ii=all_ii.to(device), all_jj=all_jj.to(device))
 
 
+def make_track_problem(h, w, seed=1234, device="cpu", calib=False, yaw_step_deg=8.0, pose_noise=(0.02, 0.02, 0.01),
+                       point_noise=0.005, C_conf=0.0, Q_conf=1.5, depth_eps=1e-6):
+    """Inputs of FrameTracker.opt_pose_ray_dist_sim3 / opt_pose_calib_sim3 as FrameTracker.track prepares them
+    (tracker.py:27-64, :128-154): keyframe k = camera 0 on the identity pixel grid, frame f = camera 1 gathered by the
+    match index idx_f2k; valid = valid_match & C gates & Q gate.  Returns Xf, Xk (N,3), T_WCf, T_WCk (1,8) [f
+    perturbed], T_WCf_gt, Qk (N,1), valid (N,1) bool, meas_k (N,3), valid_meas_k (N,1) bool, K, img_size."""
+    g = make_gn_problem(2, h, w, ([0], [1]), seed=seed, device=device, calib=calib, pose_noise=pose_noise,
+                        yaw_step_deg=yaw_step_deg, point_noise=point_noise)
+    e = 1  # directed edge ii = 1 (frame f), jj = 0 (keyframe k): pixel n of k matches pixel idx[n] of f
+    idx = g["idx_ii2jj"][e]
+    Xf, Xk = g["Xs"][1][idx].contiguous(), g["Xs"][0].contiguous()
+    Cf, Ck = g["Cs"][1][idx], g["Cs"][0]
+    Qk = g["Q"][e]
+    valid = g["valid_match"][e] & (Cf > C_conf) & (Ck > C_conf) & (Qk > Q_conf)
+    v, u = torch.meshgrid(torch.arange(h, dtype=torch.float32, device=device),
+                          torch.arange(w, dtype=torch.float32, device=device), indexing="ij")
+    valid_meas_k = Xk[..., 2:3] > depth_eps
+    meas_k = torch.cat((u.reshape(-1, 1), v.reshape(-1, 1), torch.log(Xk[..., 2:3])), dim=-1)
+    meas_k[~valid_meas_k.repeat(1, 3)] = 0.0
+    return dict(Xf=Xf, Xk=Xk, T_WCf=g["Twc"][1:2].contiguous(), T_WCk=g["Twc"][0:1].contiguous(),
+                T_WCf_gt=g["Twc_gt"][1:2], Qk=Qk.contiguous(), valid=valid.contiguous(), meas_k=meas_k.contiguous(),
+                valid_meas_k=valid_meas_k.contiguous(), K=g["K"], img_size=(h, w))
+
+
 # ----------------------------------------------------------------------------------------------- matching pairs
 def img_gradient(img):
     """Scharr-like gradient with reflect padding (reference: image.py:5-38). img (b,c,h,w)."""

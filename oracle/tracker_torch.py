@@ -12,7 +12,8 @@ import math
 
 import torch
 
-TRACKING = dict(max_iters=50, rel_error=1e-3, delta_norm=1e-3, huber=1.345, sigma_ray=0.003, sigma_dist=10.0)
+TRACKING = dict(max_iters=50, rel_error=1e-3, delta_norm=1e-3, huber=1.345, sigma_ray=0.003, sigma_dist=10.0,
+                sigma_pixel=1.0, sigma_depth=10.0, pixel_border=-10, depth_eps=1e-6)  # config/base.yaml:16-33
 
 
 def _qmul(a, b):
@@ -73,7 +74,7 @@ class Sim3:
                     B = (Cc - ((b - 1) * sg + a * th) / c) / th2
             cr = torch.linalg.cross(ph, ta)
             t = Cc * ta + A * cr + B * torch.linalg.cross(ph, cr)
-            out.append(torch.cat((t, imag * ph, torch.tensor([real], dtype=xi.dtype), torch.tensor([sc], dtype=xi.dtype))))
+            out.append(torch.cat((t, imag * ph, torch.tensor([real, sc], dtype=xi.dtype, device=xi.device))))
         return Sim3(torch.stack(out))
 
     def retr(self, xi):
@@ -143,6 +144,74 @@ def opt_pose_ray_dist_sim3(Xf, Xk, T_WCf, T_WCk, Qk, valid, cfg=TRACKING, max_it
         r = rd_k - rd_f_Ck
         J = -drd_dX @ dXf_Ck_dT
         tau, new_cost = solve(sqrt_info, r, J, cfg)
+        T_CkCf = T_CkCf.retr(tau)
+        iters += 1
+        rel_dec = math.fabs((old_cost - new_cost) / old_cost) if old_cost != float("inf") else float("inf")
+        if rel_dec < cfg["rel_error"] or torch.linalg.norm(tau) < cfg["delta_norm"]:
+            break
+        old_cost = new_cost
+    return T_WCk * T_CkCf, T_CkCf, iters
+
+
+def project_calib(P, K, img_size, jacobian=False, border=0, z_eps=0.0):  # geometry.py:63-108
+    b = P.shape[:-1]
+    K_rep = K.repeat(*b, 1, 1)
+    p = (K_rep @ P[..., None]).squeeze(-1)
+    p = p / p[..., 2:3]
+    p = p[..., :2]
+    u, v = p.split([1, 1], dim=-1)
+    x, y, z = P.split([1, 1, 1], dim=-1)
+    valid_u = (u > border) & (u < img_size[1] - 1 - border)
+    valid_v = (v > border) & (v < img_size[0] - 1 - border)
+    valid_z = z > z_eps
+    valid = valid_u & valid_v & valid_z
+    logz = torch.log(z)
+    logz[torch.logical_not(valid_z)] = 0.0
+    pz = torch.cat((p, logz), dim=-1)
+    if not jacobian:
+        return pz, valid
+    fx, fy = K[0, 0], K[1, 1]
+    z_inv = 1.0 / z[..., 0]
+    dpz_dP = torch.zeros(*b + (3, 3), device=P.device, dtype=P.dtype)
+    dpz_dP[..., 0, 0] = fx
+    dpz_dP[..., 1, 1] = fy
+    dpz_dP[..., 0, 2] = -fx * x[..., 0] * z_inv
+    dpz_dP[..., 1, 2] = -fy * y[..., 0] * z_inv
+    dpz_dP *= z_inv[..., None, None]
+    dpz_dP[..., 2, 2] = z_inv
+    return pz, dpz_dP, valid
+
+
+def make_meas(Xk, img_size, depth_eps=1e-6):
+    """meas_k / valid_meas_k as FrameTracker.get_points_poses builds them (tracker.py:141-150); Xk (h*w,3) is the
+    keyframe pointmap on the identity pixel grid (already constrained to its rays)."""
+    h, w = img_size
+    u, v = torch.meshgrid(torch.arange(w), torch.arange(h), indexing="xy")  # geometry.py:124-129
+    uv_k = torch.stack((u, v), dim=-1).to(dtype=Xk.dtype).view(-1, 2)
+    meas_k = torch.cat((uv_k, torch.log(Xk[..., 2:3])), dim=-1)
+    valid_meas_k = Xk[..., 2:3] > depth_eps
+    meas_k[~valid_meas_k.repeat(1, 3)] = 0.0
+    return meas_k, valid_meas_k
+
+
+def opt_pose_calib_sim3(Xf, Xk, T_WCf, T_WCk, Qk, valid, meas_k, valid_meas_k, K, img_size, cfg=TRACKING,
+                        max_iters=None):
+    """tracker.py:216-266.  Returns (T_WCf, T_CkCf, iterations executed)."""
+    sqrt_info_pixel = 1 / cfg["sigma_pixel"] * valid * torch.sqrt(Qk)
+    sqrt_info_depth = 1 / cfg["sigma_depth"] * valid * torch.sqrt(Qk)
+    sqrt_info = torch.cat((sqrt_info_pixel.repeat(1, 2), sqrt_info_depth), dim=1)
+    T_CkCf = T_WCk.inv() * T_WCf
+    old_cost = float("inf")
+    iters = 0
+    for step in range(max_iters or cfg["max_iters"]):
+        Xf_Ck, dXf_Ck_dT = act_Sim3(T_CkCf, Xf, jacobian=True)
+        pzf_Ck, dpz_dX, valid_proj = project_calib(Xf_Ck, K, img_size, jacobian=True, border=cfg["pixel_border"],
+                                                   z_eps=cfg["depth_eps"])
+        valid2 = valid_proj & valid_meas_k
+        sqrt_info2 = valid2 * sqrt_info
+        r = meas_k - pzf_Ck
+        J = -dpz_dX @ dXf_Ck_dT
+        tau, new_cost = solve(sqrt_info2, r, J, cfg)
         T_CkCf = T_CkCf.retr(tau)
         iters += 1
         rel_dec = math.fabs((old_cost - new_cost) / old_cost) if old_cost != float("inf") else float("inf")

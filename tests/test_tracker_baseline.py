@@ -43,3 +43,25 @@ def test_tracker_first_step_matches_graph_oracle(orc):
                           g["idx_ii2jj"].numpy()[sel], g["valid_match"].numpy()[sel], g["Q"].numpy()[sel], 0.003, 10.0,
                           0.0, 1.5, 1, 1e-8)
     assert np.allclose(T[1], T_new.data[0].numpy(), rtol=2e-3, atol=2e-4)
+
+
+def test_calib_tracker_port_converges_towards_ground_truth():
+    """opt_pose_calib_sim3 restatement (tracker.py:216-266): pixel + log-depth residuals pull a perturbed frame pose back
+    to the ground truth; meas_k / valid_meas_k built as get_points_poses does (tracker.py:141-150)."""
+    from mast3r_slam_ysh_b200 import synthetic as syn
+    from oracle import tracker_torch as tt
+    t = syn.make_track_problem(48, 64, seed=3, calib=True)
+    m, vm = tt.make_meas(t["Xk"], t["img_size"])
+    assert torch.equal(m, t["meas_k"]) and torch.equal(vm, t["valid_meas_k"])
+    Tw, Tr, iters = tt.opt_pose_calib_sim3(t["Xf"], t["Xk"], tt.Sim3(t["T_WCf"].clone()), tt.Sim3(t["T_WCk"].clone()),
+                                          t["Qk"], t["valid"], t["meas_k"], t["valid_meas_k"], t["K"], t["img_size"])
+    assert 2 <= iters < 50
+    e0 = (t["T_WCf"] - t["T_WCf_gt"]).abs().max().item()
+    e1 = (Tw.data - t["T_WCf_gt"]).abs().max().item()
+    assert e1 < 0.5 * e0
+    # fp64 run of the same restatement agrees with the fp32 one (what the device kernel is tested against)
+    f = lambda x: x.double() if x.dtype.is_floating_point else x
+    Tw64, _, it64 = tt.opt_pose_calib_sim3(f(t["Xf"]), f(t["Xk"]), tt.Sim3(f(t["T_WCf"]).clone()),
+                                           tt.Sim3(f(t["T_WCk"]).clone()), f(t["Qk"]), f(t["valid"]), f(t["meas_k"]),
+                                           t["valid_meas_k"], f(t["K"]), t["img_size"])
+    assert it64 == iters and np.allclose(Tw64.data.numpy(), Tw.data.numpy(), atol=2e-5)
