@@ -428,8 +428,49 @@ __device__ __forceinline__ void load_points(const float4* __restrict__ xci, cons
   }
 }
 
+// ---- v4 load path: the gathered points go global -> shared memory with cp.async (LDGSTS), kRingDepth batches ahead of
+// the arithmetic, into a ring of kRingSlots per-thread slots.  No registers are held by loads in flight, so the depth
+// is not limited by the register file as it was in v3 (points one batch ahead; ncu: 2.6 warps stalled on the long
+// scoreboard per issue at 3.7 warps per scheduler -> 0.74 with the ring, issue-active 59 % -> 67 %).  A thread only ever touches its own slots: no barrier in the loop.
+constexpr int kRingDepth = 1;               // batches in flight (r1, us at 32 kf: depth 1 99.4, 2 101.3, 3 103.0, 4 105.1)
+constexpr int kRingSlots = kRingDepth + 1;  // the slot being computed from is never a copy destination
+struct HessRing {
+  float4 xi[kRingSlots][2][kHessThreads];
+  float4 xj[kRingSlots][2][kHessThreads];
+  float2 meta[kRingSlots][2][kHessThreads];  // (idx as int bits, sq)
+};
+
+__device__ __forceinline__ void cp_async16(void* smem, const void* gmem) {
+  const unsigned sa = (unsigned)__cvta_generic_to_shared(smem);
+  // .cg (L2 only): the gathers have no L1 reuse (hit rate 10 %); with .ca the 256-keyframe case, whose 805 MB of
+  // points do not fit L2, ran 1.60 ms instead of 1.32 ms (r1)
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(sa), "l"(gmem) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() {
+  asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory");
+}
+
+__device__ __forceinline__ void ring_issue(HessRing& ring, int slot, const float4* __restrict__ xci,
+                                           const float4* __restrict__ xcj, const RecBatch& rb) {
+#pragma unroll
+  for (int u = 0; u < 2; u++) {
+    ring.meta[slot][u][threadIdx.x] = make_float2(__int_as_float(rb.r[u].x), rb.sq[u]);
+    if (rb.r[u].x >= 0) {
+      cp_async16(&ring.xj[slot][u][threadIdx.x], xcj + rb.r[u].y);
+      cp_async16(&ring.xi[slot][u][threadIdx.x], xci + rb.r[u].x);
+    }
+  }
+  cp_async_commit();
+}
+
+// 2 CTAs x 256 threads per SM at ~120 registers.  Tried on B200 (r1, us at 32 kf / 256 kf; this shape 99.7 / 1307):
+// 2 x 320 threads 111 / 1394, 3 x 192 109 / 1432, 5 x 128 110 / 1442, 3 x 256 108 / 1405 (all spill or lose ILP to
+// the tighter register cap), 1 x 512 99.3 / 1299 (same occupancy).
+constexpr int kHessCtasPerSm = 2;
 template <int KIND, int ROBUST>
-__global__ void __launch_bounds__(kHessThreads, 2) hessian_kernel(const float* __restrict__ Twc,
+__global__ void __launch_bounds__(kHessThreads, kHessCtasPerSm) hessian_kernel(const float* __restrict__ Twc,
                                                                   const float* __restrict__ K,
                                                                   const float4* __restrict__ xc,
                                                                   const EdgeRec* __restrict__ rec,
@@ -448,6 +489,8 @@ __global__ void __launch_bounds__(kHessThreads, 2) hessian_kernel(const float* _
   __shared__ EdgeConst s_c;
   __shared__ int s_e;
   __shared__ float s_red[kHessThreads / 32][kAccStride];
+  extern __shared__ __align__(16) unsigned char s_ring_raw[];
+  HessRing& ring = *reinterpret_cast<HessRing*>(s_ring_raw);
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   int e = -1;
   while (p < p_end) {
@@ -486,19 +529,42 @@ __global__ void __launch_bounds__(kHessThreads, 2) hessian_kernel(const float* _
     {
       constexpr int kStep = 2 * kHessThreads;
       int kb = (int)(p - e0) + threadIdx.x;
-      RecBatch ra, rb;
-      load_recs(er, es, kb, k1, ra);
-      load_recs(er, es, kb + kStep, k1, rb);
-      PixBatch cur, nxt;
-      load_points(xci, xcj, ra, cur);
-      for (; kb < k1; kb += kStep) {
-        load_points(xci, xcj, rb, nxt);
-        load_recs(er, es, kb + 2 * kStep, k1, rb);
+      // prologue: gathers of batches 0 .. kRingDepth-1 in flight, records of the next two batches in registers
 #pragma unroll
-        for (int u = 0; u < 2; u++)
-          if (cur.idx[u] >= 0) pixel_accumulate<KIND, ROBUST>(acc, c, pp, cur.xi[u], cur.xj[u], cur.idx[u], cur.sq[u]);
-        cur = nxt;
+      for (int d = 0; d < kRingDepth; d++) {
+        RecBatch r0;
+        load_recs(er, es, kb + d * kStep, k1, r0);
+        ring_issue(ring, d, xci, xcj, r0);
       }
+      RecBatch ra, rb;
+      load_recs(er, es, kb + kRingDepth * kStep, k1, ra);
+      load_recs(er, es, kb + (kRingDepth + 1) * kStep, k1, rb);
+      int slot = 0;
+      for (; kb < k1; kb += kStep) {
+        RecBatch rc;
+        load_recs(er, es, kb + (kRingDepth + 2) * kStep, k1, rc);
+        cp_async_wait<kRingDepth - 1>();  // this batch has landed
+        float4 xi[2], xj[2];
+        float2 meta[2];
+#pragma unroll
+        for (int u = 0; u < 2; u++) {
+          meta[u] = ring.meta[slot][u][threadIdx.x];
+          xi[u] = ring.xi[slot][u][threadIdx.x];
+          xj[u] = ring.xj[slot][u][threadIdx.x];
+        }
+        int nslot = slot + kRingDepth;
+        if (nslot >= kRingSlots) nslot -= kRingSlots;
+        ring_issue(ring, nslot, xci, xcj, ra);
+#pragma unroll
+        for (int u = 0; u < 2; u++) {
+          const int idx = __float_as_int(meta[u].x);
+          if (idx >= 0) pixel_accumulate<KIND, ROBUST>(acc, c, pp, xi[u], xj[u], idx, meta[u].y);
+        }
+        ra = rb;
+        rb = rc;
+        slot = slot + 1 == kRingSlots ? 0 : slot + 1;
+      }
+      cp_async_wait<0>();  // drain before the next segment reuses the ring
     }
     // ---- block reduction: transposing butterfly for acc[0..31] (lane l ends up with the warp total of acc[l]),
     //      plain xor-tree for the remaining kAcc-32 values, then 8 warps through shared memory
@@ -593,7 +659,7 @@ int launch_pack_edges(const GnWs& ws, const m3r_gn_params& p, const float* Cs, c
 }
 
 int hessian_grid() {
-  const int g = 2 * sm_count();
+  const int g = kHessCtasPerSm * sm_count();
   return g < kMaxHessCtas ? g : kMaxHessCtas;
 }
 
@@ -608,12 +674,20 @@ static int launch_hessian_kind(const GnWs& ws, const m3r_gn_params& p, const flo
   pp.z_eps = p.z_eps;
   if (ws.L.num_edges == 0 || ws.L.num_pts == 0) return M3R_OK;
   const unsigned grid = (unsigned)hessian_grid();
+  static bool attr_done = false;  // per instantiation (function-local static of a template)
+  if (!attr_done) {
+    M3R_CUDA(cudaFuncSetAttribute(hessian_kernel<KIND, M3R_ROBUST_TUKEY>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                  (int)sizeof(HessRing)));
+    M3R_CUDA(cudaFuncSetAttribute(hessian_kernel<KIND, M3R_ROBUST_HUBER>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                  (int)sizeof(HessRing)));
+    attr_done = true;
+  }
   if (p.robust == M3R_ROBUST_TUKEY)
-    hessian_kernel<KIND, M3R_ROBUST_TUKEY><<<grid, kHessThreads, 0, st>>>(
+    hessian_kernel<KIND, M3R_ROBUST_TUKEY><<<grid, kHessThreads, sizeof(HessRing), st>>>(
         Twc, ws.Kdev(), ws.xc(), ws.rec(), ws.sqv(), ws.eoff(), ws.ie(), ws.je(), ws.partial(), ws.state(), ws.L.num_pts,
         ws.L.num_edges, pp);
   else
-    hessian_kernel<KIND, M3R_ROBUST_HUBER><<<grid, kHessThreads, 0, st>>>(
+    hessian_kernel<KIND, M3R_ROBUST_HUBER><<<grid, kHessThreads, sizeof(HessRing), st>>>(
         Twc, ws.Kdev(), ws.xc(), ws.rec(), ws.sqv(), ws.eoff(), ws.ie(), ws.je(), ws.partial(), ws.state(), ws.L.num_pts,
         ws.L.num_edges, pp);
   M3R_LAUNCH_CHECK();

@@ -9,7 +9,7 @@ constexpr int kAcc = 35;             // 28 lower-triangle entries of S = sum w J
 constexpr int kAccStride = 36;       // padded stride of one tile's partial sums
 constexpr int kTilePix = 8192;       // pixels of one edge compacted by one CTA of the packing pre-pass (32 per thread)
 constexpr int kHessThreads = 256;
-constexpr int kHessChunkAlign = 512; // the Hessian kernel's per-CTA range of compacted records is a multiple of this
+constexpr int kHessChunkAlign = 2 * kHessThreads; // the Hessian kernel's per-CTA range of compacted records is a multiple of this
 constexpr int kMaxHessCtas = 1024;   // upper bound on the persistent Hessian grid (2 CTAs per SM), sizes `partial`
 constexpr int kBlk = 32;             // Cholesky block size
 constexpr int kBlockDoubles = 56;    // per-edge block: M (7x7 row-major) + v (7)
