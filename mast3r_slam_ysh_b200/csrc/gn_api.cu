@@ -84,7 +84,7 @@ GnLayout gn_layout(int num_kf, int num_pts, int num_edges, int num_all_edges) {
   L.off_tstate = take(sizeof(int) * (E * (size_t)L.tiles + 2));
   L.off_sys = take(sizeof(double) * (size_t)L.ld * (size_t)(L.n + 1));
   L.off_lfac = take(sizeof(double) * kBlk * kBlk * (size_t)(L.nblk + 1));
-  L.off_pflag = take(sizeof(int) * (size_t)(L.n / 64 + 4));
+  L.off_pflag = take(sizeof(int) * (size_t)(L.n / 64 + 4) * (size_t)(L.n / 64 + 5));  // pflag + pmask rows
   L.off_xc = take(sizeof(float4) * (size_t)num_kf * (size_t)num_pts);
   L.off_rec = take(sizeof(EdgeRec) * E * (size_t)num_pts);
   L.off_sqv = take(sizeof(float) * E * (size_t)num_pts);

@@ -19,7 +19,8 @@
 namespace m3r {
 
 constexpr int kFusedThreads = 256;
-constexpr int kPanelRows = kFusedThreads;  // rows of the panel solved by one CTA (one row per thread)
+constexpr int kPanW = 64;                  // panel width: two 32-column steps inside one phase
+constexpr int kPanelRows = 192;            // rows of the panel solved by one CTA (six row warps, one row per thread)
 constexpr int kUpdTile = 64;               // trailing-update tile (64x64 outputs per CTA pass)
 
 struct FusedArgs {
@@ -35,6 +36,8 @@ struct FusedArgs {
   double* sys;
   double* lfac;
   int* pflag;
+  int* pmask;   // [panel][64-row group] non-zero flags of the factor (for the back substitution), stride pstride
+  int pstride;
   float* dx;
   int* state;
   int n, ld, nblk, num_kf, n_free, num_edges, hess_grid, phases;
@@ -96,6 +99,12 @@ __device__ __forceinline__ void grid_barrier(int* state, int nb) {
     __threadfence();
   }
   __syncthreads();
+}
+
+// 16-byte global -> shared copy through L2; bytes beyond src_bytes (0..16) are zero-filled
+__device__ __forceinline__ void cp_async16_zfill(void* smem, const void* gmem, int src_bytes) {
+  const unsigned sa = (unsigned)__cvta_generic_to_shared(smem);
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(sa), "l"(gmem), "r"(src_bytes) : "memory");
 }
 
 __device__ __forceinline__ double shfl_d(double v, int src) {
@@ -198,76 +207,187 @@ __device__ __forceinline__ void assemble_items(const FusedArgs& A) {
 }
 
 // ============================================================================================== phase: Cholesky
-// Blocked right-looking LL^T on the lower triangle, block size 32, rows 0..n (row n = rhs).  Per block column kb:
-//   panel : CTA i owns rows [c0+nb + 256 i, +256).  The rows and the 32x32 diagonal block are staged in shared memory
-//           with coalesced loads; warp 0 factors the diagonal block (factor_diag32, gn_small.cuh), redundantly per CTA,
-//           CTA 0 publishes it to lfac[kb]; then every thread solves x L_kk^T = a for its row (trsm_row32) and the
-//           rows go back coalesced.  64-row zero flags let the update skip tiles.
-//   update: C -= X_r X_c^T on 64x64 tiles of the trailing lower triangle, tiles strided over the CTAs.
+// Blocked right-looking LL^T on the lower triangle, rows 0..n (row n = rhs).  The panel is 64 columns wide and is
+// factored as two 32-column steps INSIDE one phase, so the grid pays one panel, one update and two barriers per 64
+// columns (a 32-column panel cost 28 us per block column at n = 1785, most of it fixed latencies: staging, barriers,
+// the update's L2 round trips; r1).  Per panel kp (columns c0 = 64 kp, w <= 64 of them valid):
+//   panel : CTA i owns rows [c0+w + 192 i, +192): six row warps, one row per thread, rows staged in shared memory.
+//           Warp 6 owns the 64x64 diagonal block [[D11, 0], [D21, D22]], redundantly per CTA:
+//             factor D11 | L21 = D21 L11^-T | D22 -= L21 L21^T, factor D22
+//           while the row warps run   X1 = X1 L11^-T | X2 -= X1 L21^T | X2 = X2 L22^-T   with three CTA barriers in
+//           between (factor_diag32 / trsm_row32, gn_small.cuh).  CTA 0 publishes L11, L22 to lfac and L21 to sys for the
+//           back substitution.  64-row zero flags let the update skip tiles.
+//   update: C -= X_r X_c^T (K = 64) on 64x64 tiles of the trailing lower triangle, tiles strided over the CTAs.
 // History: the first version broadcast the pivot column with shuffles (12 us per diagonal block, 37 us per panel); a
 // rolled shared-memory version took 23 us per panel (latency of un-pipelined LDS chains); see tools/micro/chol32.cu.
+constexpr int kDiagWarp = kPanelRows / 32;  // warp 6 (warp 7 only helps staging)
 struct PanelSmem {
-  DiagAux d;                        // diagonal block (staged into d.D2, factored in place), identity-padded beyond nb
-  double X[kPanelRows][kBlk + 2];   // this CTA's panel rows (even stride: 16-byte aligned rows for LDS.128)
+  DiagAux d1, d2;                    // D11 / D22, staged then factored in place, identity-padded
+  double L21[kBlk][kBlk + 2];        // D21 -> L21
+  double X[kPanelRows][kPanW + 2];   // this CTA's panel rows (stride = 16 mod 128 bytes: conflict-free LDS.128 per row)
   int nz[kPanelRows / 64];
 };
 struct UpdateSmem {
-  double R[kUpdTile][kBlk + 1];
-  double C[kUpdTile][kBlk + 1];
+  double R[kUpdTile][kPanW + 1];
+  double C[kUpdTile][kPanW + 1];
 };
 
-__device__ __forceinline__ void panel_phase(const FusedArgs& A, int kb, PanelSmem& sm) {
+// dst[c] -= sum_k a[k] * L[c][k] for c < climit; a = this thread's 32 values (registers), L rows broadcast from shared
+// memory, dst = this thread's row in shared memory
+__device__ __forceinline__ void row_minus_a_Lt(const double (&a)[kBlk], const double (*L)[kBlk + 2], double* dst,
+                                               int climit) {
+#pragma unroll 2
+  for (int c = 0; c < climit; c++) {
+    double s0 = 0.0, s1 = 0.0, s2 = 0.0, s3 = 0.0;
+#pragma unroll
+    for (int k = 0; k < kBlk; k += 4) {
+      const double2 l0 = *reinterpret_cast<const double2*>(&L[c][k]);
+      const double2 l1 = *reinterpret_cast<const double2*>(&L[c][k + 2]);
+      s0 = fma(a[k], l0.x, s0);
+      s1 = fma(a[k + 1], l0.y, s1);
+      s2 = fma(a[k + 2], l1.x, s2);
+      s3 = fma(a[k + 3], l1.y, s3);
+    }
+    dst[c] -= (s0 + s1) + (s2 + s3);
+  }
+}
+
+#ifdef M3R_PANEL_MARKS
+#define PMARK(t) tl_mark(A, (t) + (kp == 3 ? 0 : 50))
+#else
+#define PMARK(t)
+#endif
+__device__ __forceinline__ void panel_phase(const FusedArgs& A, int kp, PanelSmem& sm) {
   const int n = A.n, ld = A.ld;
-  const int c0 = kb * kBlk;
-  const int nb = min(kBlk, n - c0);  // valid columns in this block
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  const int rows_below = n + 1 - (c0 + nb);  // rows c0+nb .. n (row n = rhs), >= 1
+  const int c0 = kp * kPanW;
+  const int w = min(kPanW, n - c0);  // valid columns of this panel
+  const int nb1 = min(kBlk, w), nb2 = w - nb1;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int rows_below = n + 1 - (c0 + w);  // rows c0+w .. n (row n = rhs), >= 1
   const int ptiles = (rows_below + kPanelRows - 1) / kPanelRows;
   if ((int)blockIdx.x >= ptiles) return;
-  const int row0 = c0 + nb + blockIdx.x * kPanelRows;
+  const int row0 = c0 + w + blockIdx.x * kPanelRows;
   __syncthreads();  // previous users of the shared-memory union are done
-  // ---- stage: diagonal block (4 rows per warp) and this CTA's rows (32 per warp), lane = column
-  for (int i = 0; i < kBlk / (kFusedThreads / 32); i++) {
-    const int r = warp * (kBlk / (kFusedThreads / 32)) + i;
-    double v = (r == lane) ? 1.0 : 0.0;
-    if (r < nb && lane <= r) v = __ldcg(A.sys + (size_t)(c0 + r) * ld + c0 + lane);
-    sm.d.D2[r][lane] = v;
-  }
-#pragma unroll 8
-  for (int i = 0; i < 32; i++) {
-    const int lr = warp * 32 + i;
-    const int row = row0 + lr;
-    double v = 0.0;
-    if (row <= n && lane < nb) v = __ldcg(A.sys + (size_t)row * ld + c0 + lane);
-    sm.X[lr][lane] = v;
-  }
-  if (threadIdx.x < kPanelRows / 64) sm.nz[threadIdx.x] = 0;
-  __syncthreads();
-  if (warp == 0) {
-    const bool bad = factor_diag32(&sm.d.D2[lane][0], sm.d, nullptr, nb, lane);
-    if (blockIdx.x == 0 && bad && lane == 0) A.state[kFailNow] = 1;
-  }
-  __syncthreads();
-  if (blockIdx.x == 0) {  // publish L_kk (zero upper part) for the back substitution
-    double* out = A.lfac + (size_t)kb * kBlk * kBlk;
-    for (int l = threadIdx.x; l < kBlk * kBlk; l += kFusedThreads) out[l] = sm.d.D2[l >> 5][l & 31];
-  }
-  // ---- solve x L^T = a for this thread's row; 64-row zero flags: an all-zero tile of the panel stays zero through the
-  //      solve and makes every trailing-update tile that would use it a no-op
-  if (row0 + (int)threadIdx.x <= n) {
-    const int nz = trsm_row32(&sm.X[threadIdx.x][0], sm.d, nb);
-    if (nz) atomicOr(&sm.nz[threadIdx.x >> 6], 1);
-  }
-  __syncthreads();
-  if (sm.nz[warp >> 1]) {
-#pragma unroll 8
+  // ---- stage (lane = column): warps 6, 7 the diagonal block, the row warps their 32 rows each
+  if (warp >= kDiagWarp) {
+    const int half = warp - kDiagWarp;
+#pragma unroll
+    for (int i = 0; i < kBlk / 2; i++) {
+      const int r = half * (kBlk / 2) + i;
+      double v = (r == lane) ? 1.0 : 0.0;
+      if (r < nb1 && lane <= r) v = __ldcg(A.sys + (size_t)(c0 + r) * ld + c0 + lane);
+      sm.d1.D2[r][lane] = v;
+      v = 0.0;
+      if (r < nb2 && lane < nb1) v = __ldcg(A.sys + (size_t)(c0 + kBlk + r) * ld + c0 + lane);
+      sm.L21[r][lane] = v;
+      v = (r == lane) ? 1.0 : 0.0;
+      if (r < nb2 && lane <= r) v = __ldcg(A.sys + (size_t)(c0 + kBlk + r) * ld + c0 + kBlk + lane);
+      sm.d2.D2[r][lane] = v;
+    }
+  } else {
+    // 32 rows x 64 columns per warp, a 16-byte cp.async per lane and row, all in flight at once (staging with
+    // register loads, 16 in flight, took 8.8 us of a 33 us panel at n = 1785; r1).  Bytes beyond the valid columns
+    // / rows are zero-filled by the copy itself.
+#pragma unroll
     for (int i = 0; i < 32; i++) {
       const int lr = warp * 32 + i;
       const int row = row0 + lr;
-      if (row <= n && lane < nb) A.sys[(size_t)row * ld + c0 + lane] = sm.X[lr][lane];
+      const int col = 2 * lane;
+      int bytes = row <= n ? (w - col) * 8 : 0;
+      bytes = bytes < 0 ? 0 : (bytes > 16 ? 16 : bytes);
+      const double* src = bytes > 0 ? A.sys + (size_t)row * ld + c0 + col : A.sys;
+      cp_async16_zfill(&sm.X[lr][col], src, bytes);
+    }
+    asm volatile("cp.async.commit_group;" ::: "memory");
+    asm volatile("cp.async.wait_group 0;" ::: "memory");
+  }
+  if (tid < kPanelRows / 64) sm.nz[tid] = 0;
+  __syncthreads();
+  PMARK(5100);
+  // ---- step 1: L11
+  if (warp == kDiagWarp) {
+    const bool bad = factor_diag32(&sm.d1.D2[lane][0], sm.d1, nullptr, nb1, lane);
+    if (blockIdx.x == 0 && bad && lane == 0) A.state[kFailNow] = 1;
+  }
+  __syncthreads();
+  PMARK(5200);
+  // ---- step 2: L21 = D21 L11^-T (warp 6)  |  X1 = X1 L11^-T (row warps)
+  const bool has_row = warp < kDiagWarp && row0 + tid <= n;
+  int nz1 = 0;
+  if (warp == kDiagWarp) {
+    trsm_row32(&sm.L21[lane][0], sm.d1, nb1);
+  } else if (has_row) {
+    nz1 = trsm_row32(&sm.X[tid][0], sm.d1, nb1);
+  }
+  __syncthreads();
+  PMARK(5300);
+  // ---- step 3: D22 -= L21 L21^T, factor (warp 6)  |  X2 -= X1 L21^T (row warps)
+  if (warp == kDiagWarp) {
+    if (nb2 > 0) {
+      double a[kBlk];
+#pragma unroll
+      for (int k = 0; k < kBlk; k += 2) {
+        const double2 v = *reinterpret_cast<const double2*>(&sm.L21[lane][k]);
+        a[k] = v.x;
+        a[k + 1] = v.y;
+      }
+      row_minus_a_Lt(a, sm.L21, &sm.d2.D2[lane][0], lane < nb2 ? lane + 1 : 0);
+      __syncwarp();
+    }
+    const bool bad = factor_diag32(&sm.d2.D2[lane][0], sm.d2, nullptr, nb2, lane);
+    if (blockIdx.x == 0 && bad && lane == 0) A.state[kFailNow] = 1;
+  } else if (has_row && nz1 && nb2 > 0) {
+    double a[kBlk];
+#pragma unroll
+    for (int k = 0; k < kBlk; k += 2) {
+      const double2 v = *reinterpret_cast<const double2*>(&sm.X[tid][k]);
+      a[k] = v.x;
+      a[k + 1] = v.y;
+    }
+    row_minus_a_Lt(a, sm.L21, &sm.X[tid][kBlk], nb2);
+  }
+  __syncthreads();
+  PMARK(5400);
+  // ---- step 4: X2 = X2 L22^-T; 64-row zero flags: an all-zero tile of the panel stays zero through the solves and
+  //      makes every trailing-update tile that would use it a no-op
+  if (has_row) {
+    int nz = nz1;
+    if (nb2 > 0) nz |= trsm_row32(&sm.X[tid][kBlk], sm.d2, nb2);
+    if (nz) atomicOr(&sm.nz[tid >> 6], 1);
+  }
+  __syncthreads();
+  PMARK(5500);
+  if (warp < kDiagWarp) {
+    if (sm.nz[warp >> 1]) {
+#pragma unroll 8
+      for (int i = 0; i < 32; i++) {
+        const int lr = warp * 32 + i;
+        const int row = row0 + lr;
+        if (row <= n) {
+          if (lane < w) A.sys[(size_t)row * ld + c0 + lane] = sm.X[lr][lane];
+          if (kBlk + lane < w) A.sys[(size_t)row * ld + c0 + kBlk + lane] = sm.X[lr][kBlk + lane];
+        }
+      }
+    }
+  } else if (blockIdx.x == 0) {  // publish L11, L22 (zero upper parts) and L21 for the back substitution
+    const int t = tid - kDiagWarp * 32;  // 0..63
+    double* out1 = A.lfac + (size_t)(2 * kp) * kBlk * kBlk;
+    for (int l = t; l < kBlk * kBlk; l += 64) out1[l] = sm.d1.D2[l >> 5][l & 31];
+    if (nb2 > 0) {
+      double* out2 = A.lfac + (size_t)(2 * kp + 1) * kBlk * kBlk;
+      for (int l = t; l < kBlk * kBlk; l += 64) out2[l] = sm.d2.D2[l >> 5][l & 31];
+      for (int l = t; l < kBlk * kBlk; l += 64) {
+        const int r = l >> 5, k = l & 31;
+        if (r < nb2 && k < nb1) A.sys[(size_t)(c0 + kBlk + r) * ld + c0 + k] = sm.L21[r][k];
+      }
     }
   }
-  if (threadIdx.x < kPanelRows / 64) A.pflag[blockIdx.x * (kPanelRows / 64) + threadIdx.x] = sm.nz[threadIdx.x];
+  if (tid < kPanelRows / 64) {
+    const int g = blockIdx.x * (kPanelRows / 64) + tid;  // 64-row group below the panel
+    A.pflag[g] = sm.nz[tid];
+    // persistent copy for the back substitution: rows of absolute group kp + 1 + g have non-zeros in panel kp
+    if (w == kPanW && kp + 1 + g < A.pstride) A.pmask[(size_t)kp * A.pstride + kp + 1 + g] = sm.nz[tid];
+  }
 }
 
 // C[r][c] -= sum_k X[r][k] X[c][k] on 64x64 tiles (tr, tc), tc <= tr, of the trailing matrix that starts at
@@ -275,8 +395,9 @@ __device__ __forceinline__ void panel_phase(const FusedArgs& A, int kb, PanelSme
 // the NEXT tile and the old C values of the current one are in flight (registers) while the current tile is multiplied
 // out of shared memory, so a tile costs its arithmetic plus one shared-memory round trip instead of three dependent L2
 // round trips (load panels -> compute -> read-modify-write C), which made a tile 6 us for 2 us of DFMAs (r1).
+constexpr int kTileQ = kUpdTile * kPanW / 2 / kFusedThreads;  // double2 loads per thread for one 64 x 64 panel tile
 struct TileRegs {
-  double2 r[4], c[4];
+  double2 r[kTileQ], c[kTileQ];
 };
 
 __device__ __forceinline__ void tile_decode(int t, int& tr, int& tc) {
@@ -287,12 +408,12 @@ __device__ __forceinline__ void tile_decode(int t, int& tr, int& tc) {
 }
 
 __device__ __forceinline__ void tile_load(const FusedArgs& A, int c0, int tr, int tc, TileRegs& g) {
-  const int t0 = c0 + kBlk;
+  const int t0 = c0 + kPanW;
   const int r_base = t0 + tr * kUpdTile, c_base = t0 + tc * kUpdTile;
 #pragma unroll
-  for (int q = 0; q < 4; q++) {
+  for (int q = 0; q < kTileQ; q++) {
     const int l = threadIdx.x + q * kFusedThreads;
-    const int r = l >> 4, k2 = l & 15;
+    const int r = l / (kPanW / 2), k2 = l % (kPanW / 2);
     const int gr = r_base + r, gc = c_base + r;
     g.r[q] = make_double2(0.0, 0.0);
     g.c[q] = make_double2(0.0, 0.0);
@@ -303,9 +424,9 @@ __device__ __forceinline__ void tile_load(const FusedArgs& A, int c0, int tr, in
 
 __device__ __forceinline__ void tile_store(UpdateSmem& sm, const TileRegs& g) {
 #pragma unroll
-  for (int q = 0; q < 4; q++) {
+  for (int q = 0; q < kTileQ; q++) {
     const int l = threadIdx.x + q * kFusedThreads;
-    const int r = l >> 4, k2 = l & 15;
+    const int r = l / (kPanW / 2), k2 = l % (kPanW / 2);
     sm.R[r][2 * k2] = g.r[q].x;
     sm.R[r][2 * k2 + 1] = g.r[q].y;
     sm.C[r][2 * k2] = g.c[q].x;
@@ -313,9 +434,9 @@ __device__ __forceinline__ void tile_store(UpdateSmem& sm, const TileRegs& g) {
   }
 }
 
-__device__ __forceinline__ void update_phase(const FusedArgs& A, int kb, int nfac, UpdateSmem& sm) {
+__device__ __forceinline__ void update_phase(const FusedArgs& A, int kp, int nfac, UpdateSmem& sm) {
   const int n = A.n, ld = A.ld;
-  const int c0 = kb * kBlk, t0 = c0 + kBlk;
+  const int c0 = kp * kPanW, t0 = c0 + kPanW;
   const int rows_below = n + 1 - t0;  // rows t0 .. n
   if (rows_below <= 0) return;
   const int T = (rows_below + kUpdTile - 1) / kUpdTile;
@@ -361,7 +482,7 @@ __device__ __forceinline__ void update_phase(const FusedArgs& A, int kb, int nfa
 #pragma unroll
       for (int j = 0; j < 4; j++) acc[i][j] = 0.0;
 #pragma unroll 8
-    for (int k = 0; k < kBlk; k++) {
+    for (int k = 0; k < kPanW; k++) {
       double a[4], b[4];
 #pragma unroll
       for (int i = 0; i < 4; i++) a[i] = sm.R[ty + 16 * i][k];
@@ -438,46 +559,68 @@ __device__ __forceinline__ void finish_solution(const FusedArgs& A, const double
 // CTA 0 only: y = row n of sys (= L^-1 b after the factorisation); solve L^T x = y block by block from the bottom,
 // dx = -x (gn_kernels.cu:1209), zero on a failed factorisation (:147-150), retraction, ||dx|| < delta test (:1219).
 struct BackSmem {
-  double L[kBlk][kBlk + 1];
-  double dinv[kBlk];
+  double L[2][kBlk][kBlk + 2];  // L_kk, double-buffered: the next block's factor arrives (cp.async) during this block
   double x[kBlk];
   double norm[kFusedThreads / 32];
+  int live[64];                 // column panels with non-zeros in the current block row
   int bad;
 };
 
+__device__ __forceinline__ void back_stage(const FusedArgs& A, BackSmem& sm, int kb) {
+  const double* src = A.lfac + (size_t)kb * kBlk * kBlk;
+  for (int l = threadIdx.x; l < kBlk * kBlk / 2; l += kFusedThreads)
+    cp_async16_zfill(&sm.L[kb & 1][l >> 4][2 * (l & 15)], src + 2 * l, 16);
+  asm volatile("cp.async.commit_group;" ::: "memory");
+}
+
+// History (n = 1785, r1): 405 us with L_kk fetched on the critical path and the y update running 8 loads deep over
+// every column; now the next factor is prefetched, the update has all 32 loads of a column in flight and skips column
+// panels that the factorisation flagged as zero for this block row (pmask).
 __device__ __forceinline__ void backsolve_phase(const FusedArgs& A, BackSmem& sm, double* s_y) {
   const int n = A.n, ld = A.ld, nblk = A.nblk;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   if (tid == 0) sm.bad = __ldcg(A.state + kFailNow);
   for (int c = tid; c < nblk * kBlk; c += kFusedThreads) s_y[c] = (c < n) ? __ldcg(A.sys + (size_t)n * ld + c) : 0.0;
+  back_stage(A, sm, nblk - 1);
   for (int kb = nblk - 1; kb >= 0; kb--) {
     const int c0 = kb * kBlk;
-    __syncthreads();
-    for (int l = tid; l < kBlk * kBlk; l += kFusedThreads) {  // stage L_kk (identity-padded) in shared memory
-      const double v = __ldcg(A.lfac + (size_t)kb * kBlk * kBlk + l);
-      sm.L[l >> 5][l & 31] = v;
-      if ((l >> 5) == (l & 31)) sm.dinv[l & 31] = 1.0 / v;
-    }
-    __syncthreads();
+    asm volatile("cp.async.wait_group 0;" ::: "memory");
+    __syncthreads();  // L_kk landed for everyone; the previous block's y update is complete
+    if (kb > 0) back_stage(A, sm, kb - 1);
+    const double (*L)[kBlk + 2] = sm.L[kb & 1];
     if (warp == 0) {
       double yv = s_y[c0 + lane];
+      const double dinv = 1.0 / L[lane][lane];
 #pragma unroll
       for (int j = kBlk - 1; j >= 0; j--) {
-        const double xj = shfl_d(yv * sm.dinv[j], j);  // lane j holds the finished y_j
+        const double xj = shfl_d(yv * dinv, j);  // lane j holds the finished y_j
         if (lane == j) yv = xj;
-        if (lane < j) yv -= sm.L[j][lane] * xj;
+        if (lane < j) yv -= L[j][lane] * xj;
       }
       sm.x[lane] = yv;
       s_y[c0 + lane] = yv;
+    } else if (warp == 1) {
+      // live column panels of this block row: flagged panels left of the diagonal group, plus the diagonal group's own
+      // first half (L21) when this is the second 32-row block of its panel
+      const int gb = c0 / kPanW;
+      for (int q = lane; q < 64; q += 32) sm.live[q] = (q < gb) ? __ldcg(A.pmask + (size_t)q * A.pstride + gb) : 0;
     }
     __syncthreads();
     const int rows = min(kBlk, n - c0);
     // y[0:c0] -= L[c0:c0+rows, 0:c0]^T x : one column per thread, coalesced along the row
     for (int c = tid; c < c0; c += kFusedThreads) {
-      double acc = 0.0;
-#pragma unroll 8
-      for (int r = 0; r < rows; r++) acc += __ldcg(A.sys + (size_t)(c0 + r) * ld + c) * sm.x[r];
-      s_y[c] -= acc;
+      const int q = c / kPanW;
+      if (q * kPanW + kPanW <= c0 && !sm.live[q & 63]) continue;  // zero panel (the diagonal group is never skipped)
+      double v[kBlk];
+#pragma unroll
+      for (int r = 0; r < kBlk; r++) v[r] = r < rows ? __ldcg(A.sys + (size_t)(c0 + r) * ld + c) : 0.0;
+      double a0 = 0.0, a1 = 0.0;
+#pragma unroll
+      for (int r = 0; r < kBlk; r += 2) {
+        a0 = fma(v[r], sm.x[r], a0);
+        a1 = fma(v[r + 1], sm.x[r + 1], a1);
+      }
+      s_y[c] -= a0 + a1;
     }
   }
   __syncthreads();
@@ -520,20 +663,22 @@ __global__ void __launch_bounds__(kFusedThreads, 1) gn_fused_kernel(const FusedA
     // only the CTAs that can get work in block column kb take part in its two barriers; the trailing matrix shrinks, so
     // the set is non-increasing and a CTA that drops out never comes back
     tl_mark(A, 5);
-    for (int kb = 0; kb < A.nblk; kb++) {
-      const int Tk = (A.n + 1 - (kb + 1) * kBlk + kUpdTile - 1) / kUpdTile;
-      int nfac = Tk > 0 ? Tk * (Tk + 1) / 2 : 1;
+    const int npan = (A.n + kPanW - 1) / kPanW;
+    for (int kp = 0; kp < npan; kp++) {
+      const int below = A.n + 1 - min(A.n, (kp + 1) * kPanW);  // rows under the panel, rhs row included
+      const int Tk = (below + kUpdTile - 1) / kUpdTile;
+      int nfac = Tk * (Tk + 1) / 2;
       if (nfac > (int)gridDim.x) nfac = gridDim.x;
       if ((int)blockIdx.x >= nfac) return;
-      panel_phase(A, kb, sm.panel);
-      tl_mark(A, 1000 + kb);
+      panel_phase(A, kp, sm.panel);
+      tl_mark(A, 1000 + kp);
       grid_barrier(A.state, nfac);
-      tl_mark(A, 2000 + kb);
-      if ((kb + 1) * kBlk < A.n) {
-        update_phase(A, kb, nfac, sm.upd);
-        tl_mark(A, 3000 + kb);
+      tl_mark(A, 2000 + kp);
+      if ((kp + 1) * kPanW < A.n) {
+        update_phase(A, kp, nfac, sm.upd);
+        tl_mark(A, 3000 + kp);
         grid_barrier(A.state, nfac);
-        tl_mark(A, 4000 + kb);
+        tl_mark(A, 4000 + kp);
       }
     }
   }
@@ -612,6 +757,8 @@ int launch_fused(const GnWs& ws, float* Twc, float delta_thresh, int phases, cud
   a.sys = ws.sys();
   a.lfac = ws.lfac();
   a.pflag = ws.pflag();
+  a.pmask = ws.pflag() + (ws.L.n / 64 + 4);
+  a.pstride = ws.L.n / 64 + 4;
   a.dx = ws.dx();
   a.state = ws.state();
   a.n = ws.L.n;

@@ -39,6 +39,13 @@ small = 7 * (nkf - 1) <= 224
 prev = None
 cyc = [(tag - 10000, t) for tag, t in marks if tag >= 10000]
 marks = [m for m in marks if m[0] < 9000]
+if any(5000 <= tag < 6000 for tag, _ in marks):  # -DM3R_PANEL_MARKS: steps inside panel 3 of CTA 0
+    pm = [(tag, t) for tag, t in marks if tag < 5000 or tag in (5100, 5200, 5300, 5400, 5500)]
+    for i, (tag, t) in enumerate(pm):
+        if tag == 5100:
+            seq = pm[i - 1:i + 6]
+            print("panel 3 steps (us): " + ", ".join("%d:%.2f" % (seq[j + 1][0], (seq[j + 1][1] - seq[j][1]) / 1e3) for j in range(len(seq) - 1)))
+    marks = [m for m in marks if not (5000 <= m[0] < 6000)]
 for tag, t in marks:
     if tag == 1: prev = t; continue
     key = names.get(tag) or ({1: "first_factor(kb=0 only)", 2: "trsm", 3: "diagupd+factor_next||update"} if small else {1: "panel", 2: "barrier_after_panel", 3: "update", 4: "barrier_after_update"})[tag // 1000]
