@@ -202,6 +202,12 @@ M3R_API int m3r_track_calib(const float* Xf, const float* meas_k, const float* T
                             double delta_norm, float* T_WCf_out, float* T_CkCf_out, int32_t* info, double* cost_out,
                             void* stream);
 
+/* geometry.constrain_points_to_ray (mast3r_slam/geometry.py:37-42): Xs (num_frames,h,w,3) f32 ->
+ * out = z * [(u-cx)/fx, (v-cy)/fy, 1] with K 3x3 row-major on the device; out may alias Xs.  Bit-identical to the
+ * reference's torch ops (called at global_opt.py:172 and tracker.py:141-142). */
+M3R_API int m3r_constrain_points_to_ray(const float* Xs, const float* K, float* out, long long num_frames, int h, int w,
+                                        void* stream);
+
 /* diagnostics: phase timeline of the fused solver kernel.  dev_buf = 2*cap device uint64; [0] counts the marks that
  * follow as (tag, globaltimer ns) pairs written by CTA 0; pass NULL to switch it off (default).  No reference
  * counterpart (the reference's solve runs on the host, gn_kernels.cu:1199-1222). */
