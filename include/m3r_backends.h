@@ -208,6 +208,13 @@ M3R_API int m3r_track_calib(const float* Xf, const float* meas_k, const float* T
 M3R_API int m3r_constrain_points_to_ray(const float* Xs, const float* K, float* out, long long num_frames, int h, int w,
                                         void* stream);
 
+/* Frame.update_pointmap (mast3r_slam/frame.py:41-105) for the running filters, in place on X_canon (n,3) / C (n):
+ * mode 0 = "weighted_pointmap" (config default, :73-76), mode 1 = "indep_conf" (:68-72).  T = 8 floats [t, q, s] on the
+ * device or NULL: when given, X_new is first moved by that Sim(3) (Xkk = T_CkCf.act(Xkf), tracker.py:96-97).  With
+ * T == NULL the result is bit-identical to the reference's torch ops. */
+M3R_API int m3r_update_pointmap(float* X_canon, float* C, const float* X_new, const float* C_new, const float* T,
+                                long long n, int mode, void* stream);
+
 /* diagnostics: phase timeline of the fused solver kernel.  dev_buf = 2*cap device uint64; [0] counts the marks that
  * follow as (tag, globaltimer ns) pairs written by CTA 0; pass NULL to switch it off (default).  No reference
  * counterpart (the reference's solve runs on the host, gn_kernels.cu:1199-1222). */

@@ -46,6 +46,7 @@ SYMBOLS = {
     "m3r_match": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _f, _f, _f, _i, _i, _vp]),
     "m3r_ray_image": (_i, [_vp, _vp, _i, _i, _i, _vp]),
     "m3r_constrain_points_to_ray": (_i, [_vp, _vp, _vp, _ll, _i, _i, _vp]),
+    "m3r_update_pointmap": (_i, [_vp, _vp, _vp, _vp, _vp, _ll, _i, _vp]),
     "m3r_track_rays": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _ll, _d, _d, _d, _i, _d, _d, _vp, _vp, _vp, _vp, _vp]),
     "m3r_track_calib": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _ll, _i, _i, _d, _d, _d, _d, _d, _i, _d, _d,
                              _vp, _vp, _vp, _vp, _vp]),

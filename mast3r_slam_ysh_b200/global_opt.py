@@ -62,6 +62,12 @@ class KeyframeStore:
         self.X[k] = X_canon.reshape(self.N, 3)
         self.C[k] = C_avg.reshape(self.N, 1)
 
+    def fuse_pointmap(self, k, X_new, C_new, T=None, filtering_mode="weighted_pointmap"):
+        """Frame.update_pointmap (frame.py:41-105) on keyframe k's rows, in place, one kernel; `self.C` holds the
+        accumulated confidence as in the reference (get_average_conf divides by the update count, frame.py:107-108)."""
+        geometry.update_pointmap(self.X[k], self.C[k], X_new.reshape(self.N, 3).contiguous(),
+                                 C_new.reshape(self.N, 1).contiguous(), T, filtering_mode)
+
     def update_T_WCs(self, T_WCs, idx):
         """SharedKeyframes.update_T_WCs (frame.py:258-262): scatter (m,8) poses to keyframes idx."""
         self.T_WC[idx] = T_WCs.reshape(-1, 8)
