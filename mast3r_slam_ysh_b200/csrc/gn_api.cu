@@ -153,7 +153,7 @@ static int gn_begin_impl(GnWs& ws, const m3r_gn_params* p, const float* Xs, cons
     zero_f32_kernel<<<ceil_div(ws.L.n, 256), 256, 0, st>>>(ws.dx(), ws.L.n);
     M3R_LAUNCH_CHECK();
   }
-  if ((rc = launch_pack_points(ws, Xs, Cs, st)) != M3R_OK) return rc;
+  if ((rc = launch_pack_points(ws, Xs, Cs, p->C_thresh, st)) != M3R_OK) return rc;
   if ((rc = launch_pack_edges(ws, *p, Cs, idx, valid, Q, st)) != M3R_OK) return rc;
   return M3R_OK;
 }
@@ -318,7 +318,7 @@ extern "C" int m3r_gn_edge_blocks(const m3r_gn_params* params, const float* Twc,
   if ((rc = launch_direct_edge_index(ws, ii_edge, jj_edge, st)) != M3R_OK) return rc;
   if (params->kind == M3R_GN_CALIB)
     M3R_CUDA(cudaMemcpyAsync(ws.Kdev(), params->K, sizeof(float) * 9, cudaMemcpyDeviceToDevice, st));
-  if ((rc = launch_pack_points(ws, Xs, Cs, st)) != M3R_OK) return rc;
+  if ((rc = launch_pack_points(ws, Xs, Cs, params->C_thresh, st)) != M3R_OK) return rc;
   if ((rc = launch_pack_edges(ws, *params, Cs, idx_ii2jj, valid_match, Q, st)) != M3R_OK) return rc;
   if ((rc = launch_hessian(ws, *params, Twc, st)) != M3R_OK) return rc;
   if ((rc = launch_finalize_edges(ws, Twc, st)) != M3R_OK) return rc;

@@ -16,11 +16,19 @@
 namespace m3r {
 
 // ------------------------------------------------------------------------------------------------ pre-pass
+// Also answers "does any point of any keyframe fail the confidence gate c > C_thresh?" (state[kCFail]); when none does
+// -- the usual case, C_conf = 0 and MASt3R confidences are >= 1 -- pack_edges skips its two confidence gathers per pixel.
 __global__ void __launch_bounds__(256) pack_points_kernel(const float* __restrict__ Xs, const float* __restrict__ Cs,
-                                                          float4* __restrict__ xc, long long total) {
+                                                          float4* __restrict__ xc, long long total, float C_thresh,
+                                                          int* __restrict__ cfail) {
   const long long p = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-  if (p >= total) return;
-  xc[p] = make_float4(__ldg(Xs + 3 * p), __ldg(Xs + 3 * p + 1), __ldg(Xs + 3 * p + 2), __ldg(Cs + p));
+  bool fail = false;
+  if (p < total) {
+    const float c = __ldg(Cs + p);
+    fail = !(c > C_thresh);  // NaN fails, as in the gate itself
+    xc[p] = make_float4(__ldg(Xs + 3 * p), __ldg(Xs + 3 * p + 1), __ldg(Xs + 3 * p + 2), c);
+  }
+  if (__any_sync(0xffffffffu, fail) && (threadIdx.x & 31) == 0) atomicOr(cfail, 1);
 }
 
 // Gate + compact.  One CTA per (edge, 8192-pixel tile); work items are handed out by a ticket so that the owners of
@@ -46,7 +54,8 @@ __global__ void __launch_bounds__(256) pack_edges_kernel(const float* __restrict
                                                          const int* __restrict__ ie, const int* __restrict__ je,
                                                          EdgeRec* __restrict__ rec, float* __restrict__ sqv,
                                                          int* __restrict__ ecount, int* __restrict__ tstate,
-                                                         int num_pts, int tiles, float C_thresh, float Q_thresh) {
+                                                         const int* __restrict__ cfail, int num_pts, int tiles,
+                                                         float C_thresh, float Q_thresh) {
   // Every lane handles 4 consecutive pixels per pass (one LDG.32 of valid, one LDG.128 of Q, two predicated LDG.128 of
   // the 8-byte indices), 8 passes of 1024 pixels per tile: a quarter of the instructions of the one-pixel-per-lane
   // version, which was issue-bound at 52 % with 208 M warp instructions (profiles/r1_pack_v3a_ncu.txt).
@@ -60,6 +69,7 @@ __global__ void __launch_bounds__(256) pack_edges_kernel(const float* __restrict
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int ix = ie[e], jx = je[e];
   const bool edge_ok = ix >= 0 && jx >= 0;
+  const bool cgate = __ldg(cfail) != 0;  // some point fails c > C_thresh: evaluate the confidence gates per pixel
   const size_t eb = (size_t)e * num_pts;
   // vector path: every edge row of Q / idx starts 16-byte aligned and of valid 4-byte aligned
   const bool vec_ok = ((num_pts & 3) == 0) && ((reinterpret_cast<uintptr_t>(Q) & 15) == 0) &&
@@ -108,17 +118,24 @@ __global__ void __launch_bounds__(256) pack_edges_kernel(const float* __restrict
       for (int j = 0; j < 4; j++)
         if (!pass[j] || ind[j] >= num_pts) ind[j] = -1;
     }
-    float ci[4], cj[4];
-#pragma unroll
-    for (int j = 0; j < 4; j++) {
-      ci[j] = ind[j] >= 0 ? __ldg(Ci + ind[j]) : 0.0f;
-      cj[j] = ind[j] >= 0 ? __ldg(Cj + k + j) : 0.0f;
-    }
     int4 id;
-    id.x = (ind[0] >= 0 && ci[0] > C_thresh && cj[0] > C_thresh) ? (int)ind[0] : -1;
-    id.y = (ind[1] >= 0 && ci[1] > C_thresh && cj[1] > C_thresh) ? (int)ind[1] : -1;
-    id.z = (ind[2] >= 0 && ci[2] > C_thresh && cj[2] > C_thresh) ? (int)ind[2] : -1;
-    id.w = (ind[3] >= 0 && ci[3] > C_thresh && cj[3] > C_thresh) ? (int)ind[3] : -1;
+    if (cgate) {
+      float ci[4], cj[4];
+#pragma unroll
+      for (int j = 0; j < 4; j++) {
+        ci[j] = ind[j] >= 0 ? __ldg(Ci + ind[j]) : 0.0f;
+        cj[j] = ind[j] >= 0 ? __ldg(Cj + k + j) : 0.0f;
+      }
+      id.x = (ind[0] >= 0 && ci[0] > C_thresh && cj[0] > C_thresh) ? (int)ind[0] : -1;
+      id.y = (ind[1] >= 0 && ci[1] > C_thresh && cj[1] > C_thresh) ? (int)ind[1] : -1;
+      id.z = (ind[2] >= 0 && ci[2] > C_thresh && cj[2] > C_thresh) ? (int)ind[2] : -1;
+      id.w = (ind[3] >= 0 && ci[3] > C_thresh && cj[3] > C_thresh) ? (int)ind[3] : -1;
+    } else {  // every confidence of every keyframe passes (pack_points checked them all)
+      id.x = (int)ind[0];
+      id.y = (int)ind[1];
+      id.z = (int)ind[2];
+      id.w = (int)ind[3];
+    }
     *reinterpret_cast<int4*>(&s_idx[lk]) = id;
     const int c = (id.x >= 0) + (id.y >= 0) + (id.z >= 0) + (id.w >= 0);
     const int tot = __reduce_add_sync(0xffffffffu, c);
@@ -634,10 +651,11 @@ __global__ void export_blocks_kernel(const double* __restrict__ blocks, float* _
 }
 
 // ------------------------------------------------------------------------------------------------ launchers
-int launch_pack_points(const GnWs& ws, const float* Xs, const float* Cs, cudaStream_t st) {
+int launch_pack_points(const GnWs& ws, const float* Xs, const float* Cs, float C_thresh, cudaStream_t st) {
   const long long total = (long long)ws.L.num_kf * ws.L.num_pts;
   if (total == 0) return M3R_OK;
-  pack_points_kernel<<<(unsigned)ceil_div_ll(total, 256), 256, 0, st>>>(Xs, Cs, ws.xc(), total);
+  pack_points_kernel<<<(unsigned)ceil_div_ll(total, 256), 256, 0, st>>>(Xs, Cs, ws.xc(), total, C_thresh,
+                                                                        ws.state() + kCFail);
   M3R_LAUNCH_CHECK();
   return M3R_OK;
 }
@@ -650,7 +668,8 @@ int launch_pack_edges(const GnWs& ws, const m3r_gn_params& p, const float* Cs, c
     M3R_CUDA(cudaMemsetAsync(ws.tstate(), 0, sizeof(int) * ((size_t)E * tiles + 2), st));
     pack_edges_kernel<<<(unsigned)((long long)E * tiles), 256, 0, st>>>(Cs, idx, valid, Q, ws.ie(), ws.je(), ws.rec(),
                                                                           ws.sqv(), ws.ecount(), ws.tstate(),
-                                                                          ws.L.num_pts, tiles, p.C_thresh, p.Q_thresh);
+                                                                          ws.state() + kCFail, ws.L.num_pts, tiles,
+                                                                          p.C_thresh, p.Q_thresh);
     M3R_LAUNCH_CHECK();
   }
   edge_offsets_kernel<<<1, 1024, 0, st>>>(ws.ecount(), ws.eoff(), E);

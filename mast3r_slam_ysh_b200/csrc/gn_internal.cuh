@@ -18,7 +18,8 @@ constexpr int kBlockDoubles = 56;    // per-edge block: M (7x7 row-major) + v (7
 enum StateSlot {
   kDone = 0, kIters = 1, kFailCount = 2, kFailNow = 3, kBadEdges = 4, kConverged = 5,
   kBarCount = 6, kBarGen = 7,  // grid barrier of the fused solver kernel
-  kStateInts = 8
+  kCFail = 8,                  // some point of some keyframe fails the confidence gate (set by pack_points)
+  kStateInts = 9
 };
 
 // phases of the fused solver kernel (gn_fused.cu)
@@ -66,7 +67,7 @@ struct GnWs {
 };
 
 // gn_hessian.cu
-int launch_pack_points(const GnWs& ws, const float* Xs, const float* Cs, cudaStream_t st);
+int launch_pack_points(const GnWs& ws, const float* Xs, const float* Cs, float C_thresh, cudaStream_t st);
 int launch_pack_edges(const GnWs& ws, const m3r_gn_params& p, const float* Cs, const int64_t* idx, const uint8_t* valid,
                       const float* Q, cudaStream_t st);
 int hessian_grid();

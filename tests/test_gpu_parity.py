@@ -206,6 +206,27 @@ def test_edge_blocks_vs_oracle_fp64(be, orc, kind):
         assert torch.equal(Hs[0], Hs[3]) and torch.equal(Hs[1], -Hs[0]) and torch.equal(gs[0], -gs[1])
 
 
+def test_edge_blocks_confidence_gate_vs_oracle(be, orc):
+    """C_thresh inside the range of the confidences: the per-pixel gates c_i > C_thresh, c_j > C_thresh
+    (gn_kernels.cu:953-957) drop matches; with the default C_conf = 0 the pre-pass skips them altogether."""
+    g = load_golden("gn_rays")
+    uniq, ie, je = orc.index_prep(g["ii"], g["jj"])
+    idx = g["idx"].astype(np.int64)
+    c_mid = float(np.median(g["Cs"]))
+    assert (g["Cs"] > c_mid).mean() < 0.6 and (g["Cs"] > LO["C_conf"]).all()
+    kw = dict(sigma_ray=LO["sigma_ray"], sigma_dist=LO["sigma_dist"])
+    outs = []
+    for c_thresh in (LO["C_conf"], c_mid):
+        Hs_o, gs_o = orc.gn_edge_blocks(orc.KIND_RAYS, g["Twc"], g["Xs"], g["Cs"], ie, je, idx, g["valid"], g["Q"],
+                                        c_thresh, LO["Q_conf"], robust=0, **kw)
+        Hs, gs = be.gn_edge_blocks("rays", t(g["Twc"]), t(g["Xs"]), t(g["Cs"]), t(ie), t(je), t(idx), t(g["valid"]),
+                                   t(g["Q"]), c_thresh, LO["Q_conf"], robust="huber", **kw)
+        assert np.linalg.norm(Hs.cpu().numpy() - Hs_o) / np.linalg.norm(Hs_o) <= 2e-5
+        assert np.linalg.norm(gs.cpu().numpy() - gs_o) / np.linalg.norm(gs_o) <= 2e-5
+        outs.append(np.linalg.norm(Hs_o))
+    assert outs[1] < 0.8 * outs[0]  # the gate really removed matches
+
+
 def test_gn_failure_and_degenerate_inputs(be):
     g = load_golden("gn_rays")
     idx = t(g["idx"].astype(np.int64))
