@@ -240,16 +240,18 @@ __global__ void __launch_bounds__(kPrepThreads) index_prep_kernel(const int64_t*
   }
   __syncthreads();
   if (tid == 0) state[kBadEdges] = s_bad;
-  // incidence lists (see incidence_kernel)
+  // incidence lists (see incidence_kernel): degrees with shared-memory atomics over all edge ends, offsets by one
+  // thread, then one WARP per free keyframe walks the edges 32 at a time and places its entries with ballots, in the
+  // order (edge, i-end before j-end) of the serial version (which spent ~40 us here with 31 active threads; r1)
   const int n_free = num_kf > 0 ? num_kf - 1 : 0;
-  for (int a = tid; a < n_free; a += kPrepThreads) {
-    int d = 0;
-    for (int e = 0; e < num_edges; e++) {
-      const int i = s_ie[e], j = s_je[e];
-      if (i < 0 || j < 0) continue;
-      d += (i - 1 == a) + (j - 1 == a);
-    }
-    s_deg[a] = d;
+  for (int a = tid; a <= n_free; a += kPrepThreads) s_deg[a] = 0;
+  __syncthreads();
+  for (int t = tid; t < 2 * num_edges; t += kPrepThreads) {
+    const int e = t >> 1;
+    const int i = s_ie[e], j = s_je[e];
+    if (i < 0 || j < 0) continue;
+    const int a = ((t & 1) ? j : i) - 1;
+    if (a >= 0) atomicAdd(&s_deg[a], 1);
   }
   __syncthreads();
   if (tid == 0) {
@@ -264,25 +266,66 @@ __global__ void __launch_bounds__(kPrepThreads) index_prep_kernel(const int64_t*
     inc_off[n_free] = run;
   }
   __syncthreads();
-  for (int a = tid; a < n_free; a += kPrepThreads) {
+  const unsigned lt = (1u << lane) - 1u;
+  for (int a = warp; a < n_free; a += kPrepThreads / 32) {
     const int beg = s_deg[a];
     int o = beg;
-    for (int e = 0; e < num_edges; e++) {
-      const int i = s_ie[e], j = s_je[e];
-      if (i < 0 || j < 0) continue;
-      if (i - 1 == a) inc_list[o++] = 2 * e;
-      if (j - 1 == a) inc_list[o++] = 2 * e + 1;
-    }
-    for (int l = beg; l < o; l++) {
-      const int ent = inc_list[l];
-      const int e = ent >> 1;
-      int other = ((ent & 1) ? s_ie[e] : s_je[e]) - 1;
-      if (other >= 0 && other < a) {
-        bool first = true;
-        for (int l2 = beg; l2 < l; l2++) first = first && ((inc_other[l2] & 0x3fffffff) != other || inc_other[l2] < 0);
-        if (first) other |= 1 << 30;
+    for (int e0 = 0; e0 < num_edges; e0 += 32) {
+      const int e = e0 + lane;
+      int i = -1, j = -1;
+      if (e < num_edges) {
+        i = s_ie[e];
+        j = s_je[e];
       }
-      inc_other[l] = other;
+      const bool ok = i >= 0 && j >= 0;
+      const bool mi = ok && (i - 1 == a), mj = ok && (j - 1 == a);
+      const unsigned bi = __ballot_sync(0xffffffffu, mi), bj = __ballot_sync(0xffffffffu, mj);
+      int pos = o + __popc(bi & lt) + __popc(bj & lt);
+      if (mi) inc_list[pos++] = 2 * e;
+      if (mj) inc_list[pos] = 2 * e + 1;
+      o += __popc(bi) + __popc(bj);
+    }
+    __syncwarp();
+    // the other end of every entry; bit 30 marks the first entry of each distinct lower neighbour (the owner of the
+    // off-diagonal block in the assembly)
+    for (int l0 = beg; l0 < o; l0 += 32) {
+      const int l = l0 + lane;
+      if (l < o) {
+        const int ent = inc_list[l];
+        const int e = ent >> 1;
+        inc_other[l] = ((ent & 1) ? s_ie[e] : s_je[e]) - 1;
+      }
+    }
+    __syncwarp();
+    int flag[4] = {0, 0, 0, 0};  // up to 128 entries per keyframe in registers; longer lists fall back to a loop below
+    for (int l0 = beg, q = 0; l0 < o; l0 += 32, q++) {
+      const int l = l0 + lane;
+      bool first = false;
+      if (l < o) {
+        const int other = inc_other[l];
+        if (other >= 0 && other < a) {
+          first = true;
+          for (int l2 = beg; l2 < l; l2++) first = first && (inc_other[l2] != other);
+        }
+      }
+      if (q < 4) flag[q] = first;  // entries beyond 128: see the serial tail
+    }
+    __syncwarp();
+    for (int l0 = beg, q = 0; l0 < o && q < 4; l0 += 32, q++) {
+      const int l = l0 + lane;
+      if (l < o && (flag[q] & 1)) inc_other[l] |= 1 << 30;
+    }
+    if (o - beg > 128) {  // very high degree: finish serially (reads only raw values beyond entry 128)
+      __syncwarp();
+      if (lane == 0)
+        for (int l = beg + 128; l < o; l++) {
+          const int other = inc_other[l];
+          if (other >= 0 && other < a) {
+            bool first = true;
+            for (int l2 = beg; l2 < l; l2++) first = first && ((inc_other[l2] & 0x3fffffff) != other || inc_other[l2] < 0);
+            if (first) inc_other[l] = other | (1 << 30);
+          }
+        }
     }
   }
 }
