@@ -232,12 +232,12 @@ struct UpdateSmem {
   double C[kUpdTile][kPanW + 1];
 };
 
-// dst[c] -= sum_k a[k] * L[c][k] for c < climit; a = this thread's 32 values (registers), L rows broadcast from shared
-// memory, dst = this thread's row in shared memory
+// dst[c] -= sum_k a[k] * L[c][k] for c = cstart, cstart + cstep, ... < climit; a = this thread's 32 values (registers),
+// L rows broadcast from shared memory, dst = this thread's row in shared memory
 __device__ __forceinline__ void row_minus_a_Lt(const double (&a)[kBlk], const double (*L)[kBlk + 2], double* dst,
-                                               int climit) {
+                                               int climit, int cstart = 0, int cstep = 1) {
 #pragma unroll 2
-  for (int c = 0; c < climit; c++) {
+  for (int c = cstart; c < climit; c += cstep) {
     double s0 = 0.0, s1 = 0.0, s2 = 0.0, s3 = 0.0;
 #pragma unroll
     for (int k = 0; k < kBlk; k += 4) {
@@ -322,8 +322,8 @@ __device__ __forceinline__ void panel_phase(const FusedArgs& A, int kp, PanelSme
   __syncthreads();
   PMARK(5300);
   // ---- step 3: D22 -= L21 L21^T, factor (warp 6)  |  X2 -= X1 L21^T (row warps)
-  if (warp == kDiagWarp) {
-    if (nb2 > 0) {
+  if (warp >= kDiagWarp) {
+    if (nb2 > 0) {  // warps 6 and 7 split the columns of the 32x32 update (even / odd), then meet on barrier 1
       double a[kBlk];
 #pragma unroll
       for (int k = 0; k < kBlk; k += 2) {
@@ -331,11 +331,13 @@ __device__ __forceinline__ void panel_phase(const FusedArgs& A, int kp, PanelSme
         a[k] = v.x;
         a[k + 1] = v.y;
       }
-      row_minus_a_Lt(a, sm.L21, &sm.d2.D2[lane][0], lane < nb2 ? lane + 1 : 0);
-      __syncwarp();
+      row_minus_a_Lt(a, sm.L21, &sm.d2.D2[lane][0], lane < nb2 ? lane + 1 : 0, warp - kDiagWarp, 2);
+      asm volatile("bar.sync 1, 64;" ::: "memory");
     }
-    const bool bad = factor_diag32(&sm.d2.D2[lane][0], sm.d2, nullptr, nb2, lane);
-    if (blockIdx.x == 0 && bad && lane == 0) A.state[kFailNow] = 1;
+    if (warp == kDiagWarp) {
+      const bool bad = factor_diag32(&sm.d2.D2[lane][0], sm.d2, nullptr, nb2, lane);
+      if (blockIdx.x == 0 && bad && lane == 0) A.state[kFailNow] = 1;
+    }
   } else if (has_row && nz1 && nb2 > 0) {
     double a[kBlk];
 #pragma unroll
