@@ -139,6 +139,20 @@ M3R_API double* m3r_gn_system_ptr(void* workspace, int num_kf, int num_pts, int 
 M3R_API size_t m3r_gn_system_count(int num_kf);
 M3R_API int m3r_gn_solve_retract(const m3r_gn_params* params, float* Twc, int num_kf, int num_pts, int num_local_edges,
                          void* workspace, void* stream);
+/* Multi-GPU iteration WITHOUT a collective library call: every rank's [H | b] (m3r_gn_system_count(num_kf) doubles,
+ * zero-initialised once) lives in peer-mapped memory (CUDA IPC / fabric handles, e.g. torch symmetric memory), and the
+ * fused solver kernel sums the ranks' buffers itself over NVLink between assembly and factorisation (peer loads, sum in
+ * rank order by the owner of each row, peer stores, two cross-GPU barriers on 8-byte arrival slots).
+ *   peer_sys_ptrs[world]  : addresses, valid on THIS device, of every rank's system buffer (this rank's own included;
+ *                           it replaces the workspace-internal one for the whole launch)
+ *   peer_flag_ptrs[world] : addresses of every rank's `world` uint64 arrival slots, zero before the first call
+ *   epoch                 : > 0, strictly increasing from call to call, identical on all ranks
+ * One call == m3r_gn_accumulate + all-reduce + m3r_gn_solve_retract (Hessian kernel + one cooperative launch).  All
+ * ranks must call it the same number of times; replicas stay bit-identical.  A peer that never arrives is reported by
+ * bit 30 of info[3] at m3r_gn_end after a ~4 s timeout instead of a hang. */
+M3R_API int m3r_gn_iterate_peer(const m3r_gn_params* params, float* Twc, int num_kf, int num_pts, int num_local_edges,
+                                void* workspace, int rank, int world, const uint64_t* peer_sys_ptrs,
+                                const uint64_t* peer_flag_ptrs, uint64_t epoch, void* stream);
 M3R_API int m3r_gn_end(int num_kf, int num_pts, int num_local_edges, float* dx_out, int32_t* info_out, void* workspace,
                void* stream);
 

@@ -54,6 +54,7 @@ SYMBOLS = {
     "m3r_gauss_newton": (_i, [_PP, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _vp, _vp, _vp, _sz, _vp]),
     "m3r_gn_begin": (_i, [_PP, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _vp, _vp, _i, _vp, _sz, _vp]),
     "m3r_gn_accumulate": (_i, [_PP, _vp, _i, _i, _i, _vp, _vp]),
+    "m3r_gn_iterate_peer": (_i, [_PP, _vp, _i, _i, _i, _vp, _i, _i, _vp, _vp, C.c_uint64, _vp]),
     "m3r_gn_hessian_pass": (_i, [_PP, _vp, _i, _i, _i, _vp, _vp]),
     "m3r_gn_system_ptr": (_vp, [_vp, _i, _i, _i]),
     "m3r_gn_system_count": (_sz, [_i]),

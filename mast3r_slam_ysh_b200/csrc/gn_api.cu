@@ -130,7 +130,10 @@ __global__ void finish_kernel(const float* __restrict__ dx, const int* __restric
   const int t = blockIdx.x * blockDim.x + threadIdx.x;
   if (dx_out != nullptr && t < n) dx_out[t] = dx[t];
   if (info_out != nullptr && t < 4) {
-    const int v = t == 0 ? state[kIters] : t == 1 ? state[kConverged] : t == 2 ? state[kFailCount] : state[kBadEdges];
+    const int v = t == 0   ? state[kIters]
+                  : t == 1 ? state[kConverged]
+                  : t == 2 ? state[kFailCount]
+                           : (state[kBadEdges] | (state[kPeerTimeout] ? 0x40000000 : 0));
     info_out[t] = v;
   }
 }
@@ -173,6 +176,13 @@ static int gn_iterate_impl(GnWs& ws, const m3r_gn_params* p, float* Twc, cudaStr
   int rc;
   if ((rc = launch_hessian(ws, *p, Twc, st)) != M3R_OK) return rc;
   return launch_fused(ws, Twc, p->delta_thresh, M3R_PH_ALL, st);
+}
+
+// multi-GPU iteration with the in-kernel peer all-reduce: Hessian kernel + ONE fused launch, as on a single GPU
+static int gn_iterate_peer_impl(GnWs& ws, const m3r_gn_params* p, float* Twc, const PeerInfo& peer, cudaStream_t st) {
+  int rc;
+  if ((rc = launch_hessian(ws, *p, Twc, st)) != M3R_OK) return rc;
+  return launch_fused(ws, Twc, p->delta_thresh, M3R_PH_ALL, st, &peer);
 }
 
 static int gn_end_impl(GnWs& ws, float* dx_out, int32_t* info_out, cudaStream_t st) {
@@ -244,6 +254,33 @@ extern "C" int m3r_gn_hessian_pass(const m3r_gn_params* params, const float* Twc
       M3R_OK)
     return rc;
   return launch_hessian(ws, *params, Twc, (cudaStream_t)stream);
+}
+
+extern "C" int m3r_gn_iterate_peer(const m3r_gn_params* params, float* Twc, int num_kf, int num_pts,
+                                   int num_local_edges, void* workspace, int rank, int world,
+                                   const uint64_t* peer_sys_ptrs, const uint64_t* peer_flag_ptrs, uint64_t epoch,
+                                   void* stream) {
+  int rc;
+  if ((rc = check_params(params)) != M3R_OK) return rc;
+  M3R_REQUIRE(world >= 2 && world <= kMaxPeers && rank >= 0 && rank < world, "gn_iterate_peer: bad rank/world %d/%d",
+              rank, world);
+  M3R_REQUIRE(peer_sys_ptrs && peer_flag_ptrs && epoch > 0, "gn_iterate_peer: null peer table or zero epoch");
+  GnWs ws;
+  if ((rc = bind_ws(&ws, num_kf, num_pts, num_local_edges, max_all_edges(num_local_edges), workspace, (size_t)-1)) !=
+      M3R_OK)
+    return rc;
+  PeerInfo peer = PeerInfo();
+  peer.rank = rank;
+  peer.world = world;
+  peer.epoch = epoch;
+  for (int p = 0; p < world; p++) {
+    M3R_REQUIRE(peer_sys_ptrs[p] != 0 && (peer_sys_ptrs[p] & 15) == 0 && peer_flag_ptrs[p] != 0 &&
+                    (peer_flag_ptrs[p] & 7) == 0,
+                "gn_iterate_peer: peer %d pointers must be non-null and aligned", p);
+    peer.sys[p] = reinterpret_cast<double*>(peer_sys_ptrs[p]);
+    peer.flags[p] = reinterpret_cast<unsigned long long*>(peer_flag_ptrs[p]);
+  }
+  return gn_iterate_peer_impl(ws, params, Twc, peer, (cudaStream_t)stream);
 }
 
 extern "C" double* m3r_gn_system_ptr(void* workspace, int num_kf, int num_pts, int num_local_edges) {

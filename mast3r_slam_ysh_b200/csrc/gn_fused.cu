@@ -45,6 +45,7 @@ struct FusedArgs {
   float delta_thresh;
   unsigned long long* timeline;  // diagnostics (m3r_debug_set_timeline): CTA 0 appends (tag, globaltimer ns) pairs
   int timeline_cap;
+  PeerInfo peer;  // world > 1: sum [H | b] over the ranks inside the kernel (peer_allreduce_phase)
 };
 
 static unsigned long long* g_timeline = nullptr;
@@ -99,6 +100,104 @@ __device__ __forceinline__ void grid_barrier(int* state, int nb) {
     __threadfence();
   }
   __syncthreads();
+}
+
+// ============================================================================================== phase: peer all-reduce
+// Multi-GPU: every rank has assembled the [H | b] of ITS edges into its own buffer in peer-mapped memory.  Between
+// assembly and factorisation the fused kernel sums the buffers itself over NVLink:
+//   barrier (all local CTAs + all ranks: assembly done, visible system-wide)
+//   -> rank r owns every world-th row (small systems: every world-th 256-chunk of the packed triangle); its CTAs read
+//      that slice from all ranks (peer loads), add in rank order and write the sum into ALL ranks' buffers (peer stores)
+//   -> barrier (all sums landed) -> factorisation.
+// Only the lower triangle + rhs row is touched.  Each element is summed by exactly one rank and then replicated, so
+// the replicas stay bit-identical, as with the NCCL all-reduce this replaces (one launch + one collective call less per
+// iteration).  A rank that never arrives (crashed peer) is reported through state[kPeerTimeout] after ~4 s instead of
+// hanging the device.
+__device__ __forceinline__ unsigned long long ld_acquire_sys_u64(const unsigned long long* p) {
+  unsigned long long v;
+  asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_release_sys_u64(unsigned long long* p, unsigned long long v) {
+  asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+
+// grid barrier over all CTAs of this launch whose last local arriver also meets the other ranks at value `v`
+__device__ __forceinline__ void grid_peer_barrier(const FusedArgs& A, unsigned long long v) {
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    int* count = A.state + kBarCount;
+    int* gen = A.state + kBarGen;
+    const int g = ld_relaxed_i(gen);
+    __threadfence_system();
+    if (atomicAdd(count, 1) == (int)gridDim.x - 1) {
+      atomicExch(count, 0);
+      const PeerInfo& P = A.peer;
+      for (int p = 0; p < P.world; p++)
+        if (p != P.rank) st_release_sys_u64(P.flags[p] + P.rank, v);
+      for (int p = 0; p < P.world; p++) {
+        if (p == P.rank) continue;
+        long long spins = 0;
+        while (ld_acquire_sys_u64(P.flags[P.rank] + p) < v) {
+          __nanosleep(64);
+          if (++spins > (1LL << 25)) {  // ~4 s: give up instead of hanging the GPU
+            A.state[kPeerTimeout] = 1;
+            break;
+          }
+        }
+      }
+      __threadfence_system();
+      st_release_i(gen, g + 1);
+    } else {
+      while (ld_relaxed_i(gen) == g) __nanosleep(40);
+    }
+    __threadfence_system();
+  }
+  __syncthreads();
+}
+
+__device__ __forceinline__ void peer_sum_store(const FusedArgs& A, size_t off2) {  // off2: index in double2 units
+  const PeerInfo& P = A.peer;
+  double2 acc = make_double2(0.0, 0.0);
+#pragma unroll
+  for (int p = 0; p < kMaxPeers; p++) {
+    if (p >= P.world) break;
+    double2 v;  // system-scope accesses: peer memory is coherent at the home GPU's L2, never cached locally
+    asm volatile("ld.relaxed.sys.global.v2.f64 {%0, %1}, [%2];"
+                 : "=d"(v.x), "=d"(v.y)
+                 : "l"(reinterpret_cast<const double2*>(P.sys[p]) + off2)
+                 : "memory");
+    acc.x += v.x;
+    acc.y += v.y;
+  }
+#pragma unroll
+  for (int p = 0; p < kMaxPeers; p++) {
+    if (p >= P.world) break;
+    asm volatile("st.relaxed.sys.global.v2.f64 [%0], {%1, %2};" ::"l"(reinterpret_cast<double2*>(P.sys[p]) + off2),
+                 "d"(acc.x), "d"(acc.y)
+                 : "memory");
+  }
+}
+
+template <int THREADS>
+__device__ __forceinline__ void peer_allreduce_phase(const FusedArgs& A) {
+  const PeerInfo& P = A.peer;
+  grid_peer_barrier(A, 2 * P.epoch + 1);
+  if (A.packed) {  // packed lower triangle + rhs row: one linear range of prow(n + 1) doubles (even by construction)
+    const size_t n2 = (size_t)prow(A.n + 1) / 2;
+    const size_t nchunks = (n2 + THREADS - 1) / THREADS;
+    for (size_t c = (size_t)P.rank + (size_t)P.world * blockIdx.x; c < nchunks; c += (size_t)P.world * gridDim.x) {
+      const size_t i = c * THREADS + threadIdx.x;
+      if (i < n2) peer_sum_store(A, i);
+    }
+  } else {  // row-major with leading dimension ld (even): row r holds columns 0..min(r, n-1)
+    for (int r = P.rank + P.world * blockIdx.x; r <= A.n; r += P.world * gridDim.x) {
+      const int len2 = (min(r + 1, A.n) + 1) / 2;
+      const size_t base2 = (size_t)r * A.ld / 2;
+      for (int i = threadIdx.x; i < len2; i += THREADS) peer_sum_store(A, base2 + i);
+    }
+  }
+  grid_peer_barrier(A, 2 * P.epoch + 2);
 }
 
 // 16-byte global -> shared copy through L2; bytes beyond src_bytes (0..16) are zero-filled
@@ -660,8 +759,12 @@ __global__ void __launch_bounds__(kFusedThreads, 1) gn_fused_kernel(const FusedA
     assemble_items(A);
     tl_mark(A, 4);
   }
+  if (A.peer.world > 1) {
+    peer_allreduce_phase<kFusedThreads>(A);  // its barriers also order assembly -> factorisation
+  } else if ((A.phases & M3R_PH_FACTOR) && (A.phases & M3R_PH_ASSEMBLE)) {
+    grid_barrier(A.state, gridDim.x);
+  }
   if (A.phases & M3R_PH_FACTOR) {
-    if (A.phases & M3R_PH_ASSEMBLE) grid_barrier(A.state, gridDim.x);
     // only the CTAs that can get work in block column kb take part in its two barriers; the trailing matrix shrinks, so
     // the set is non-increasing and a CTA that drops out never comes back
     tl_mark(A, 5);
@@ -712,8 +815,12 @@ __global__ void __launch_bounds__(kSmallThreads, 1) gn_small_kernel(const FusedA
     assemble_items(A);
     tl_mark(A, 4);
   }
+  if (A.peer.world > 1) {
+    peer_allreduce_phase<kSmallThreads>(A);  // its barriers also order assembly -> factorisation
+  } else if ((A.phases & M3R_PH_FACTOR) && (A.phases & M3R_PH_ASSEMBLE)) {
+    grid_barrier(A.state, gridDim.x);
+  }
   if (A.phases & M3R_PH_FACTOR) {
-    if (A.phases & M3R_PH_ASSEMBLE) grid_barrier(A.state, gridDim.x);
     if (blockIdx.x != 0) return;
     tl_mark(A, 5);
     double* M = reinterpret_cast<double*>(s_raw);
@@ -744,9 +851,12 @@ int fused_grid(const GnWs& ws) {
   return want < cap ? want : cap;
 }
 
-int launch_fused(const GnWs& ws, float* Twc, float delta_thresh, int phases, cudaStream_t st) {
+int launch_fused(const GnWs& ws, float* Twc, float delta_thresh, int phases, cudaStream_t st, const PeerInfo* peer) {
   if (ws.L.n_free <= 0) return M3R_OK;
   FusedArgs a;
+  a.peer = PeerInfo();
+  a.peer.world = 1;
+  if (peer != nullptr && peer->world > 1) a.peer = *peer;
   a.Twc = Twc;
   a.partial = ws.partial();
   a.eoff = ws.eoff();
@@ -756,7 +866,7 @@ int launch_fused(const GnWs& ws, float* Twc, float delta_thresh, int phases, cud
   a.inc_off = ws.inc_off();
   a.inc_list = ws.inc_list();
   a.inc_other = ws.inc_other();
-  a.sys = ws.sys();
+  a.sys = a.peer.world > 1 ? a.peer.sys[a.peer.rank] : ws.sys();
   a.lfac = ws.lfac();
   a.pflag = ws.pflag();
   a.pmask = ws.pflag() + (ws.L.n / 64 + 4);

@@ -19,11 +19,22 @@ enum StateSlot {
   kDone = 0, kIters = 1, kFailCount = 2, kFailNow = 3, kBadEdges = 4, kConverged = 5,
   kBarCount = 6, kBarGen = 7,  // grid barrier of the fused solver kernel
   kCFail = 8,                  // some point of some keyframe fails the confidence gate (set by pack_points)
-  kStateInts = 9
+  kPeerTimeout = 9,            // a peer rank never arrived at the in-kernel all-reduce (multi-GPU path)
+  kStateInts = 10
 };
 
 // phases of the fused solver kernel (gn_fused.cu)
 enum FusedPhase { M3R_PH_FINALIZE = 1, M3R_PH_ASSEMBLE = 2, M3R_PH_FACTOR = 4, M3R_PH_BACKSOLVE = 8, M3R_PH_ALL = 15 };
+
+// Multi-GPU: the ranks' [H | b] buffers live in peer-mapped (symmetric) memory and the fused solver kernel sums them
+// itself between assembly and factorisation (gn_fused.cu, peer_allreduce_phase) -- no NCCL call in the iteration.
+constexpr int kMaxPeers = 8;
+struct PeerInfo {
+  int rank, world;
+  unsigned long long epoch;              // strictly increasing per launch, the same on every rank
+  double* sys[kMaxPeers];                // every rank's [H | b], addressable from this device
+  unsigned long long* flags[kMaxPeers];  // every rank's arrival slots: flags[p][src] written by rank src
+};
 
 // Edge records produced once per solve by the packing pre-pass (iteration-invariant part of the per-pixel work).
 // Only pixels that pass every pose-independent gate (valid_match & q > Q_thresh & c_i > C_thresh & c_j > C_thresh,
@@ -81,7 +92,8 @@ int launch_index_prep(const GnWs& ws, const int64_t* local_ii, const int64_t* lo
 int launch_direct_edge_index(const GnWs& ws, const int64_t* ii_edge, const int64_t* jj_edge, cudaStream_t st);
 
 // gn_fused.cu
-int launch_fused(const GnWs& ws, float* Twc, float delta_thresh, int phases, cudaStream_t st);
+int launch_fused(const GnWs& ws, float* Twc, float delta_thresh, int phases, cudaStream_t st,
+                 const PeerInfo* peer = nullptr);
 int launch_pose_retr(float* poses, const float* dx, int num_poses, int num_fix, cudaStream_t st);
 
 }  // namespace m3r

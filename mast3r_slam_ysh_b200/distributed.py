@@ -5,12 +5,17 @@ BASELINE.json:north_star defines: "graph edges are split across GPUs and the blo
 keyframe-pair matching ... is split by pair".
 
 GN: every rank holds a replica of Twc/Xs/Cs and a contiguous slice of the directed edges.  Per iteration each rank
-assembles its partial dense [H | b] in fp64 (m3r_gn_accumulate), ONE all-reduce sums it over NVLink, and every rank
-runs the same deterministic fp64 Cholesky + retraction (m3r_gn_solve_retract), so pose replicas stay bit-identical
-without a broadcast.  The convergence flag lives on the device (a pure function of the replicated dx), so no rank ever
-synchronises with its host inside the loop.
+assembles its partial dense [H | b] in fp64, the partial systems are summed over NVLink, and every rank runs the same
+deterministic fp64 Cholesky + retraction, so pose replicas stay bit-identical without a broadcast.  The convergence
+flag lives on the device (a pure function of the replicated dx), so no rank ever synchronises with its host inside the
+loop.  Two exchange paths:
+  * "peer" (default on CUDA when torch symmetric memory is available): the system buffers are peer-mapped and the fused
+    solver kernel sums them itself between assembly and factorisation (m3r_gn_iterate_peer) -- one Hessian kernel and
+    ONE cooperative launch per iteration, exactly as on a single GPU, and no collective library call in the loop;
+  * "nccl": m3r_gn_accumulate, ONE dist.all_reduce of [H | b], m3r_gn_solve_retract.
 """
 import ctypes as C
+import os
 
 import torch
 import torch.distributed as dist
@@ -49,14 +54,63 @@ def allreduce_system(sys_tensor, group=None):
     return sys_tensor
 
 
+# ------------------------------------------------------------------------------------------------ peer-mapped systems
+class _PeerSystem:
+    """One symmetric-memory allocation per (device, group): every rank's [H | b] buffer + arrival slots, mapped into
+    every rank's address space (torch.distributed._symmetric_memory: CUDA IPC / fabric handles).  Allocated and
+    rendezvoused ONCE and reused by every solve (the rendezvous is a collective and costs milliseconds); the epoch
+    counter advances identically on all ranks because they make the same sequence of calls."""
+    _cache = {}
+
+    def __init__(self, count, dev, group):
+        import torch.distributed._symmetric_memory as symm
+        self.count = int(count)
+        self.world = dist.get_world_size(group)
+        self.rank = dist.get_rank(group)
+        self.buf = symm.empty(self.count + 64, dtype=torch.float64, device=dev)  # tail: 64 x 8-byte arrival slots
+        self.buf.zero_()
+        self.handle = symm.rendezvous(self.buf, group if group is not None else dist.group.WORLD)
+        ptrs = [int(p) for p in self.handle.buffer_ptrs]
+        self.sys_ptrs = (C.c_uint64 * self.world)(*ptrs)
+        self.flag_ptrs = (C.c_uint64 * self.world)(*[p + 8 * self.count for p in ptrs])
+        self.epoch = 0
+        torch.cuda.synchronize(dev)
+        dist.barrier(group)  # every rank's buffer is zero before anyone's kernel may write into it
+
+    @classmethod
+    def get(cls, count, dev, group):
+        key = (dev.index, id(group))
+        cur = cls._cache.get(key)
+        if cur is None or cur.count < count:
+            # grow with head-room so that a growing graph does not rendezvous at every solve
+            cur = cls(max(int(count), 2 * cur.count if cur is not None else 0), dev, group)
+            cls._cache[key] = cur
+        return cur
+
+
+def peer_exchange_available():
+    try:
+        import torch.distributed._symmetric_memory  # noqa: F401
+    except Exception:
+        return False
+    return dist.is_available() and dist.is_initialized() and dist.get_backend() == "nccl"
+
+
 # ------------------------------------------------------------------------------------------------ sharded GN (device)
 class ShardedGaussNewton:
-    """Step-wise GN over the C ABI (m3r_gn_begin / accumulate / solve_retract / end)."""
+    """Step-wise GN over the C ABI (m3r_gn_begin / iterate_peer | accumulate + all-reduce + solve_retract / end)."""
 
-    def __init__(self, params, Twc, Xs, Cs, local_ii, local_jj, idx_ii2jj, valid_match, Q, all_ii, all_jj, group=None):
+    def __init__(self, params, Twc, Xs, Cs, local_ii, local_jj, idx_ii2jj, valid_match, Q, all_ii, all_jj, group=None,
+                 exchange="auto"):
         self.lib = _lib.load()
         self.params = params
         self.group = group
+        world = dist.get_world_size(group) if dist.is_available() and dist.is_initialized() else 1
+        if exchange == "auto":
+            exchange = os.environ.get("M3R_EXCHANGE", "auto")  # A/B switch for benchmarking: peer | nccl
+        if exchange == "auto":
+            exchange = "peer" if world > 1 and world <= 8 and peer_exchange_available() else "nccl"
+        self.exchange = exchange if world > 1 else "local"
         self.Twc = Twc
         self.dev = Twc.device
         self.num_kf, self.num_pts = Xs.shape[0], Xs.shape[1]
@@ -77,6 +131,14 @@ class ShardedGaussNewton:
         sys_ptr = self.lib.m3r_gn_system_ptr(C.c_void_p(self.ws_ptr), self.num_kf, self.num_pts, self.E)
         off = sys_ptr - self.ws.data_ptr()
         self.sys = self.ws[off:off + 8 * cnt].view(torch.float64)
+        self.peer = None
+        if self.exchange == "peer":
+            try:
+                self.peer = _PeerSystem.get(cnt, self.dev, group)
+            except Exception as e:  # symmetric memory unavailable on this system: the NCCL path is equivalent
+                import warnings
+                warnings.warn(f"peer-mapped system buffers unavailable ({e!r}); using the NCCL all-reduce")
+                self.exchange = "nccl"
 
     def _stream(self):
         return C.c_void_p(torch.cuda.current_stream(self.dev).cuda_stream)
@@ -88,6 +150,15 @@ class ShardedGaussNewton:
         _lib.check(rc, "gn_hessian_pass")
 
     def iterate(self):
+        if self.peer is not None:
+            pr = self.peer
+            pr.epoch += 1
+            with torch.cuda.device(self.dev):
+                rc = self.lib.m3r_gn_iterate_peer(C.byref(self.params), C.c_void_p(self.Twc.data_ptr()), self.num_kf,
+                                                  self.num_pts, self.E, C.c_void_p(self.ws_ptr), pr.rank, pr.world,
+                                                  pr.sys_ptrs, pr.flag_ptrs, pr.epoch, self._stream())
+            _lib.check(rc, "gn_iterate_peer")
+            return
         with torch.cuda.device(self.dev):
             rc = self.lib.m3r_gn_accumulate(C.byref(self.params), C.c_void_p(self.Twc.data_ptr()), self.num_kf,
                                             self.num_pts, self.E, C.c_void_p(self.ws_ptr), self._stream())
@@ -108,12 +179,13 @@ class ShardedGaussNewton:
 
 
 def gauss_newton_rays_sharded(Twc, Xs, Cs, local_ii, local_jj, idx_ii2jj, valid_match, Q, all_ii, all_jj, sigma_ray,
-                              sigma_dist, C_thresh, Q_thresh, max_iter, delta_thresh, group=None):
+                              sigma_dist, C_thresh, Q_thresh, max_iter, delta_thresh, group=None, exchange="auto"):
     """gauss_newton_rays (gn.cpp:28-52) with the directed edges sharded over the ranks of `group`.
     local_* are this rank's edges, all_ii/all_jj the concatenation over ranks (keyframe numbering must agree)."""
     params = _lib.GnParams(_lib.M3R_GN_RAYS, _lib.M3R_ROBUST_HUBER, float(sigma_ray), float(sigma_dist), float(C_thresh),
                            float(Q_thresh), None, 0, 0, 0, 0.0, int(max_iter), float(delta_thresh))
-    s = ShardedGaussNewton(params, Twc, Xs, Cs, local_ii, local_jj, idx_ii2jj, valid_match, Q, all_ii, all_jj, group)
+    s = ShardedGaussNewton(params, Twc, Xs, Cs, local_ii, local_jj, idx_ii2jj, valid_match, Q, all_ii, all_jj, group,
+                           exchange)
     for _ in range(int(max_iter)):
         s.iterate()
     dx, info = s.finish()
