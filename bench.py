@@ -177,7 +177,10 @@ def workload_config(n):
                          "max_iter 10 (BASELINE.json configs[2]%s)" % (KF_PER_GPU * n, 2 * KF_PER_GPU * SPAN * n,
                                                                       "" if n == 1 else ", weak-scaled at the same 11.25 deg yaw step; N=8 == configs[4] size"),
                 keyframes=KF_PER_GPU * n, directed_edges=2 * KF_PER_GPU * SPAN * n, pixels=N_PIX, gn_iters=GN_ITERS,
-                parallelism="edge-sharded x%d, all-reduce [H|b] fp64, replicated Cholesky" % n,
+                parallelism=("edge-sharded x%d, [H|b] fp64 summed %s, replicated Cholesky"
+                             % (n, "on one GPU" if n == 1 else
+                                ("by NCCL all-reduce" if os.environ.get("M3R_EXCHANGE") == "nccl"
+                                 else "inside the solver kernel over peer-mapped memory (NCCL all-reduce as fallback)"))),
                 l2_policy="inputs (>1.3 GB per GPU) exceed the 126 MB L2; no explicit flush")
 
 
