@@ -87,7 +87,9 @@ M3R_API int m3r_refine_matches_f32(const float* D11, const float* D21, const int
  *   idx_ii2jj (num_edges,num_pts) int64, valid_match (num_edges,num_pts,1) bool(1 byte), Q (num_edges,num_pts,1) f32
  *   dx_out (num_kf-1,7) f32: last update (the reference returns it "for debugging", gn_kernels.cu:1227)
  *   info_out (device, 4 x int32, may be NULL): [0] iterations executed, [1] 1 if stopped on ||dx|| < delta_thresh,
- *            [2] number of iterations whose factorisation failed (dx = 0), [3] reserved
+ *            [2] number of iterations whose factorisation failed (dx = 0), [3] diagnostics: bits 0-23 edges dropped
+ *            because a keyframe rank exceeded num_kf, bits 24-27 lanes of the envelope Cholesky (0: the small or the
+ *            dense solver ran), bit 30 peer time-out (multi-GPU)
  * The whole loop (Hessian assembly, reduction, fp64 Cholesky, retraction, convergence test) runs on the device
  * without a host round trip; the first sorted keyframe is held fixed (num_fix = 1, gn_kernels.cu:1157).
  * ------------------------------------------------------------------------------------------------------- */
@@ -233,6 +235,15 @@ M3R_API int m3r_update_pointmap(float* X_canon, float* C, const float* X_new, co
  * follow as (tag, globaltimer ns) pairs written by CTA 0; pass NULL to switch it off (default).  No reference
  * counterpart (the reference's solve runs on the host, gn_kernels.cu:1199-1222). */
 M3R_API void m3r_debug_set_timeline(unsigned long long* dev_buf, int cap);
+
+/* diagnostics / tests: linear solver of systems with more than 224 unknowns.  0 (default): the single-CTA envelope
+ * Cholesky wherever the keyframe graph's envelope fits (at most 6 active 32-row blocks), else the dense multi-CTA
+ * Cholesky; 1: always the dense multi-CTA Cholesky.  Both replace Eigen::SimplicialLLT (gn_kernels.cu:115-159).
+ * Process-wide; takes effect at the next solve. */
+M3R_API void m3r_debug_set_solver(int mode);
+/* lanes (1..6) of the envelope solver chosen for the solve that last used `workspace`, 0 = dense / small solver ran;
+ * negative = CUDA error.  Synchronises the device. */
+M3R_API int m3r_debug_solver_lanes(const void* workspace);
 
 /* ---------------------------------------------------------------------------------------------------------
  * Host-buffer convenience wrappers (end-to-end path: pageable/pinned HOST pointers in, results back on the host).

@@ -40,6 +40,8 @@ SYMBOLS = {
     "m3r_last_error_string": (C.c_char_p, []),
     "m3r_launch_count": (C.c_uint64, []),
     "m3r_debug_set_timeline": (None, [_vp, _i]),
+    "m3r_debug_set_solver": (None, [_i]),
+    "m3r_debug_solver_lanes": (_i, [_vp]),
     "m3r_iter_proj": (_i, [_vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _f, _f, _vp]),
     "m3r_refine_matches_f16": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _vp]),
     "m3r_refine_matches_f32": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _vp]),

@@ -85,6 +85,7 @@ GnLayout gn_layout(int num_kf, int num_pts, int num_edges, int num_all_edges) {
   L.off_sys = take(sizeof(double) * (size_t)L.ld * (size_t)(L.n + 1));
   L.off_lfac = take(sizeof(double) * kBlk * kBlk * (size_t)(L.nblk + 1));
   L.off_pflag = take(sizeof(int) * (size_t)(L.n / 64 + 4) * (size_t)(L.n / 64 + 5));  // pflag + pmask rows
+  L.off_sky = take(sizeof(int) * (size_t)SkyPlan::total(L.n_free));
   L.off_xc = take(sizeof(float4) * (size_t)num_kf * (size_t)num_pts);
   L.off_rec = take(sizeof(EdgeRec) * E * (size_t)num_pts);
   L.off_sqv = take(sizeof(float) * E * (size_t)num_pts);
@@ -133,7 +134,8 @@ __global__ void finish_kernel(const float* __restrict__ dx, const int* __restric
     const int v = t == 0   ? state[kIters]
                   : t == 1 ? state[kConverged]
                   : t == 2 ? state[kFailCount]
-                           : (state[kBadEdges] | (state[kPeerTimeout] ? 0x40000000 : 0));
+                           : ((state[kBadEdges] & 0xffffff) | ((state[kSkyLanes] & 15) << 24) |
+                              (state[kPeerTimeout] ? 0x40000000 : 0));
     info_out[t] = v;
   }
 }

@@ -38,9 +38,11 @@ struct FusedArgs {
   int* pflag;
   int* pmask;   // [panel][64-row group] non-zero flags of the factor (for the back substitution), stride pstride
   int pstride;
+  const int* sky;  // envelope plan (SkyPlan), nullptr when the envelope solver cannot run (shared memory, debug switch)
   float* dx;
   int* state;
   int n, ld, nblk, num_kf, n_free, num_edges, hess_grid, phases;
+  int launch_id;  // distinct per launch: idle CTAs of a single-CTA phase wait for state[kIdleFlag] == launch_id
   int packed;  // [H ; b] in the packed even-row layout of gn_small.cuh (n <= kSmallMaxN) instead of row-major with ld
   float delta_thresh;
   unsigned long long* timeline;  // diagnostics (m3r_debug_set_timeline): CTA 0 appends (tag, globaltimer ns) pairs
@@ -48,6 +50,7 @@ struct FusedArgs {
   PeerInfo peer;  // world > 1: sum [H | b] over the ranks inside the kernel (peer_allreduce_phase)
 };
 
+extern int g_solver_mode;  // gn_solve.cu
 static unsigned long long* g_timeline = nullptr;
 static int g_timeline_cap = 0;
 
@@ -100,6 +103,24 @@ __device__ __forceinline__ void grid_barrier(int* state, int nb) {
     __threadfence();
   }
   __syncthreads();
+}
+
+// Experiment (M3R_IDLE_SPIN): CTAs without work in a single-CTA phase stay resident (sleeping) until CTA 0 is done
+// instead of exiting, to see whether a lone CTA with a large code body is issue-throttled.
+__device__ __forceinline__ void idle_wait(const FusedArgs& A) {
+#ifdef M3R_IDLE_SPIN
+  if (threadIdx.x == 0) {
+    long long spins = 0;
+    while (ld_relaxed_i(A.state + kIdleFlag) != A.launch_id && ++spins < (1LL << 22)) __nanosleep(M3R_IDLE_SPIN);
+  }
+  __syncthreads();
+#endif
+}
+__device__ __forceinline__ void idle_release(const FusedArgs& A) {
+#ifdef M3R_IDLE_SPIN
+  __syncthreads();
+  if (threadIdx.x == 0) st_release_i(A.state + kIdleFlag, A.launch_id);
+#endif
 }
 
 // ============================================================================================== phase: peer all-reduce
@@ -664,6 +685,7 @@ struct BackSmem {
   double x[kBlk];
   double norm[kFusedThreads / 32];
   int live[64];                 // column panels with non-zeros in the current block row
+  int fb[kSkyMaxBlk];           // envelope solver: first non-zero column block of every row block
   int bad;
 };
 
@@ -677,11 +699,18 @@ __device__ __forceinline__ void back_stage(const FusedArgs& A, BackSmem& sm, int
 // History (n = 1785, r1): 405 us with L_kk fetched on the critical path and the y update running 8 loads deep over
 // every column; now the next factor is prefetched, the update has all 32 loads of a column in flight and skips column
 // panels that the factorisation flagged as zero for this block row (pmask).
+// SKY: the envelope solver ran; s_y already holds L^-1 b, and block row kb of L is non-zero in column blocks
+// [fb[kb], kb) only.
+template <bool SKY>
 __device__ __forceinline__ void backsolve_phase(const FusedArgs& A, BackSmem& sm, double* s_y) {
   const int n = A.n, ld = A.ld, nblk = A.nblk;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   if (tid == 0) sm.bad = __ldcg(A.state + kFailNow);
-  for (int c = tid; c < nblk * kBlk; c += kFusedThreads) s_y[c] = (c < n) ? __ldcg(A.sys + (size_t)n * ld + c) : 0.0;
+  if (SKY) {
+    for (int i = tid; i < nblk; i += kFusedThreads) sm.fb[i] = __ldcg(A.sky + SkyPlan::fb(A.n_free) + i);
+  } else {
+    for (int c = tid; c < nblk * kBlk; c += kFusedThreads) s_y[c] = (c < n) ? __ldcg(A.sys + (size_t)n * ld + c) : 0.0;
+  }
   back_stage(A, sm, nblk - 1);
   for (int kb = nblk - 1; kb >= 0; kb--) {
     const int c0 = kb * kBlk;
@@ -700,7 +729,7 @@ __device__ __forceinline__ void backsolve_phase(const FusedArgs& A, BackSmem& sm
       }
       sm.x[lane] = yv;
       s_y[c0 + lane] = yv;
-    } else if (warp == 1) {
+    } else if (warp == 1 && !SKY) {
       // live column panels of this block row: flagged panels left of the diagonal group, plus the diagonal group's own
       // first half (L21) when this is the second 32-row block of its panel
       const int gb = c0 / kPanW;
@@ -709,9 +738,9 @@ __device__ __forceinline__ void backsolve_phase(const FusedArgs& A, BackSmem& sm
     __syncthreads();
     const int rows = min(kBlk, n - c0);
     // y[0:c0] -= L[c0:c0+rows, 0:c0]^T x : one column per thread, coalesced along the row
-    for (int c = tid; c < c0; c += kFusedThreads) {
+    for (int c = (SKY ? sm.fb[kb] * kBlk : 0) + tid; c < c0; c += kFusedThreads) {
       const int q = c / kPanW;
-      if (q * kPanW + kPanW <= c0 && !sm.live[q & 63]) continue;  // zero panel (the diagonal group is never skipped)
+      if (!SKY && q * kPanW + kPanW <= c0 && !sm.live[q & 63]) continue;  // zero panel (the diagonal group is never skipped)
       double v[kBlk];
 #pragma unroll
       for (int r = 0; r < kBlk; r++) v[r] = r < rows ? __ldcg(A.sys + (size_t)(c0 + r) * ld + c) : 0.0;
@@ -728,12 +757,222 @@ __device__ __forceinline__ void backsolve_phase(const FusedArgs& A, BackSmem& sm
   finish_solution(A, s_y, &sm.bad, sm.norm);
 }
 
+// ============================================================================================== envelope (skyline) solver
+// Keyframe graphs of a SLAM run are chains with a few long-range edges: the assembled H is block-banded plus a few long
+// rows, and a Cholesky factor keeps the row envelope of the matrix it factors.  When at most kSkyMaxLanes 32-row blocks
+// are ever active at once (SkyPlan, gn_solve.cu) ONE CTA factors the whole system out of shared memory: the active tiles
+// (row block x column block, both active) stay resident from the step a row block joins until its column has been
+// eliminated, so each entry of the envelope is read from L2 once and written once; there is no grid barrier, no
+// trailing-matrix round trip through L2 and no work on structural zeros.  The dense multi-CTA solver above spends
+// 27 us per 64-column panel on the diagonal block's serial chain plus two grid barriers whatever the sparsity
+// (1.28 ms at n = 1785); this one spends the chain alone.  The right-hand side travels as a vector in shared memory
+// (forward substitution block by block), not as row n of the matrix, so it does not widen the envelope.
+// Per step kb (column block c0 = 32 kb): join (cp.async the tiles of row blocks that become active) | factor the
+// diagonal tile unless the look-ahead already did | X = X L^-T on the active rows below, y_kb = L^-1 y_kb | publish
+// L_kk, update the next diagonal tile | warp 0 factors the NEXT diagonal tile while warps 1-7 store the finished column
+// to sys, update y and the remaining active tiles.
+constexpr int kSkyTiles = kSkyMaxLanes * (kSkyMaxLanes + 1) / 2;
+constexpr int kSkyPrefetched = 1 << 8;  // schedule word 1: the new members' tiles were fetched during the previous step
+constexpr int kSkyStride = kBlk + 2;  // 272-byte rows: conflict-free LDS.128 for "one row per lane" and "8 rows per quarter warp"
+struct SkySmem {
+  double T[kSkyTiles][kBlk][kSkyStride];
+  DiagAux d;
+  int lane[kSkyMaxBlk];
+  int sched[kSkyMaxBlk][kSkySched];  // the whole plan: no L2 round trip on the per-step critical path
+};
+
+__device__ __forceinline__ double (*sky_tile(SkySmem& sm, int la, int lb))[kSkyStride] {
+  const int p = max(la, lb), q = min(la, lb);
+  return sm.T[p * (p + 1) / 2 + q];
+}
+
+// C[16 half .. +16)[0..32) -= Xi Xj^T (K = 32) by one warp: 4 x 8 threads, 4 x 4 outputs each (rows 16 half + 4 ty + i,
+// columns tx + 8 j: the eight lanes of a quarter warp read eight consecutive rows of Xj, one row of Xi)
+__device__ __noinline__ void sky_update_item(const double (*Xi)[kSkyStride], const double (*Xj)[kSkyStride],
+                                                double (*Cc)[kSkyStride], int half, int lane) {
+  const int ty = lane >> 3, tx = lane & 7;
+  const int r0 = 16 * half + 4 * ty;
+  double acc[4][4];
+#pragma unroll
+  for (int i = 0; i < 4; i++)
+#pragma unroll
+    for (int j = 0; j < 4; j++) acc[i][j] = 0.0;
+#pragma unroll 4
+  for (int k = 0; k < kBlk; k += 2) {
+    double2 a[4], b[4];
+#pragma unroll
+    for (int i = 0; i < 4; i++) a[i] = *reinterpret_cast<const double2*>(&Xi[r0 + i][k]);
+#pragma unroll
+    for (int j = 0; j < 4; j++) b[j] = *reinterpret_cast<const double2*>(&Xj[tx + 8 * j][k]);
+#pragma unroll
+    for (int i = 0; i < 4; i++)
+#pragma unroll
+      for (int j = 0; j < 4; j++) acc[i][j] = fma(a[i].y, b[j].y, fma(a[i].x, b[j].x, acc[i][j]));
+  }
+#pragma unroll
+  for (int i = 0; i < 4; i++)
+#pragma unroll
+    for (int j = 0; j < 4; j++) Cc[r0 + i][tx + 8 * j] -= acc[i][j];
+}
+
+// One warp: right-hand side block of row block rbj, y -= X_j y_kb (one row per lane), and the finished column block of L
+// (rows of block rbj, columns c0 .. c0 + nb) to sys for the back substitution
+__device__ __forceinline__ void sky_rhs_and_store(const FusedArgs& A, SkySmem& sm, double* s_y, int rbj, int al0, int c0,
+                                                  int nb, int lane) {
+  const double (*Xj)[kSkyStride] = sky_tile(sm, sm.lane[rbj], al0);
+  double s0 = 0.0, s1 = 0.0;
+#pragma unroll
+  for (int k = 0; k < kBlk; k += 2) {
+    const double2 a = *reinterpret_cast<const double2*>(&Xj[lane][k]);
+    s0 = fma(a.x, s_y[c0 + k], s0);
+    s1 = fma(a.y, s_y[c0 + k + 1], s1);
+  }
+  s_y[kBlk * rbj + lane] -= s0 + s1;
+#pragma unroll 8
+  for (int r = 0; r < kBlk; r++) {
+    const int row = kBlk * rbj + r;
+    if (row < A.n && lane < nb) A.sys[(size_t)row * A.ld + c0 + lane] = Xj[r][lane];
+  }
+}
+
+// cp.async (no commit) of the tiles that join at step kb, by threads t = 0 .. nthr-1
+__device__ __forceinline__ void sky_join(const FusedArgs& A, SkySmem& sm, int kb, int t0, int nthr) {
+  const int n = A.n, ld = A.ld;
+  const int* sched = sm.sched[kb];
+  const int m = sched[0], mask = sched[1];
+  for (int t = 0, i = 0, j = 0; t < m * (m + 1) / 2; t++, j++) {
+    if (j > i) {
+      i++;
+      j = 0;
+    }
+    if (!(((mask >> i) | (mask >> j)) & 1)) continue;
+    const int rbi = sched[2 + i], rbj = sched[2 + j];
+    double (*Tt)[kSkyStride] = sky_tile(sm, sm.lane[rbi], sm.lane[rbj]);
+    for (int piece = t0; piece < 512; piece += nthr) {  // 512 16-byte pieces per tile
+      const int r = piece >> 4, c2 = (piece & 15) * 2;
+      const int row = kBlk * rbi + r, col = kBlk * rbj + c2;
+      int cnt = (row < n) ? n - col : 0;
+      cnt = cnt < 0 ? 0 : (cnt > 2 ? 2 : cnt);
+      const double* src = cnt > 0 ? A.sys + (size_t)row * ld + col : A.sys;
+      cp_async16_zfill(&Tt[r][c2], src, 8 * cnt);
+    }
+  }
+}
+
+__device__ __forceinline__ void sky_factor(const FusedArgs& A, SkySmem& sm, double* s_y) {
+  const int n = A.n, ld = A.ld, nblk = A.nblk;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  for (int i = tid; i < nblk; i += kFusedThreads) sm.lane[i] = __ldcg(A.sky + SkyPlan::lane(A.n_free) + i);
+  for (int i = tid; i < nblk * kSkySched; i += kFusedThreads)
+    sm.sched[i / kSkySched][i % kSkySched] = __ldcg(A.sky + SkyPlan::sched(A.n_free) + i);
+  for (int c = tid; c < nblk * kBlk; c += kFusedThreads) s_y[c] = (c < n) ? __ldcg(A.sys + (size_t)n * ld + c) : 0.0;
+  bool looked = false;  // the diagonal tile of this step was factored during the previous step (uniform over the CTA)
+  for (int kb = 0; kb < nblk; kb++) {
+    const int c0 = kb * kBlk;
+    const int nb = min(kBlk, n - c0);
+    asm volatile("cp.async.wait_group 0;" ::: "memory");  // tiles prefetched for this step
+    __syncthreads();  // everybody is done with the previous step (the tiles of its column); first step: plan loaded
+#define SKY_MARK(t) if (kb == 20 || kb == 21) tl_mark(A, (t))
+    SKY_MARK(7000);
+    const int* sched = sm.sched[kb];
+    const int m = sched[0], mask = sched[1];
+    const int al0 = sm.lane[kb];
+    // ---- join: tiles (act[i], act[j]), j <= i, with a new member on either side, from the assembled system; when the
+    //      plan says that the lanes of the NEXT step's new members are idle during this step, their tiles are fetched now
+    if (mask & 0xff) {
+      if (!(mask & kSkyPrefetched)) {
+        sky_join(A, sm, kb, tid, kFusedThreads);
+        asm volatile("cp.async.commit_group;" ::: "memory");
+        asm volatile("cp.async.wait_group 0;" ::: "memory");
+        __syncthreads();
+      }
+    }
+    SKY_MARK(7001);
+    double (*Tkk)[kSkyStride] = sky_tile(sm, al0, al0);
+    if (!looked) {
+      if (warp == 0) {
+        const bool bad = factor_diag32(&Tkk[lane][0], sm.d, nullptr, nb, lane);
+        if (bad && lane == 0) A.state[kFailNow] = 1;
+      }
+      __syncthreads();
+    }
+    // ---- rows below: X = X L_kk^-T, one row per thread (warp w: row block act[1 + w]); lane 0 of the first free warp
+    //      forward-substitutes the right-hand side block
+    if (warp < m - 1) {
+      trsm_row32(&sky_tile(sm, sm.lane[sched[3 + warp]], al0)[lane][0], sm.d, nb);
+    } else if (tid == (m - 1) * 32) {
+      trsm_row32(s_y + c0, sm.d, nb);
+    }
+    __syncthreads();
+    SKY_MARK(7003);
+    // ---- update of the next diagonal tile first (look-ahead): thread = (4 rows, 1 column)
+    const bool ahead = m >= 2 && sched[3] == kb + 1;
+    const int al1 = sm.lane[min(kb + 1, nblk - 1)];
+    if (ahead) {
+      const double (*X1)[kSkyStride] = sky_tile(sm, al1, al0);
+      double (*C11)[kSkyStride] = sky_tile(sm, al1, al1);
+      const int r0 = 4 * warp;
+      if (lane <= r0 + 3) {
+        double s[4] = {0.0, 0.0, 0.0, 0.0}, u[4] = {0.0, 0.0, 0.0, 0.0};
+#pragma unroll 4
+        for (int k = 0; k < kBlk; k += 2) {
+          const double2 b = *reinterpret_cast<const double2*>(&X1[lane][k]);
+#pragma unroll
+          for (int i = 0; i < 4; i++) {
+            const double2 a = *reinterpret_cast<const double2*>(&X1[r0 + i][k]);
+            s[i] = fma(a.x, b.x, s[i]);
+            u[i] = fma(a.y, b.y, u[i]);
+          }
+        }
+#pragma unroll
+        for (int i = 0; i < 4; i++) C11[r0 + i][lane] -= s[i] + u[i];
+      }
+      __syncthreads();
+    }
+    SKY_MARK(7004);
+    if (ahead && warp == 0) {
+      const int c1 = c0 + kBlk;
+      const bool bad = factor_diag32(&sky_tile(sm, al1, al1)[lane][0], sm.d, nullptr, min(kBlk, n - c1), lane);
+      if (bad && lane == 0) A.state[kFailNow] = 1;
+      SKY_MARK(7005);
+    } else {
+      // workers: L_kk for the back substitution (zero upper part, identity padding) from the factored diagonal tile, the
+      // right-hand side and the finished column of L, the prefetch of the next step's tiles, then the trailing update
+      const int worker = ahead ? warp - 1 : warp;
+      const int nworkers = ahead ? kFusedThreads / 32 - 1 : kFusedThreads / 32;
+      {
+        double* out = A.lfac + (size_t)kb * kBlk * kBlk;
+        for (int l = worker * 32 + lane; l < kBlk * kBlk; l += nworkers * 32) {
+          const int r = l >> 5, c = l & 31;
+          out[l] = (r < nb && c <= r) ? Tkk[r][c] : (r == c ? 1.0 : 0.0);
+        }
+      }
+      for (int j = 1 + worker; j < m; j += nworkers) sky_rhs_and_store(A, sm, s_y, sched[2 + j], al0, c0, nb, lane);
+      if (kb + 1 < nblk && (sm.sched[kb + 1][1] & kSkyPrefetched)) {
+        sky_join(A, sm, kb + 1, worker * 32 + lane, nworkers * 32);
+        asm volatile("cp.async.commit_group;" ::: "memory");
+      }
+      // trailing tiles (act[i], act[j]) -= X_i X_j^T, 1 <= j <= i < m, two 16-row halves each; (1, 1) is done above
+      const int pairs = m * (m - 1) / 2, skip = ahead ? 1 : 0;
+      for (int item = worker; item < 2 * (pairs - skip); item += nworkers) {
+        int ti, tj;
+        tile_decode((item >> 1) + skip, ti, tj);
+        const int ali = sm.lane[sched[3 + ti]], alj = sm.lane[sched[3 + tj]];
+        sky_update_item(sky_tile(sm, ali, al0), sky_tile(sm, alj, al0), sky_tile(sm, ali, alj), item & 1, lane);
+      }
+    }
+    looked = ahead;
+  }
+  __syncthreads();
+}
+
 // ============================================================================================== the kernel
 union FusedSmem {
   FinalizeScratch fin[kFusedThreads / 32];
   PanelSmem panel;
   UpdateSmem upd;
   BackSmem back;
+  SkySmem sky;
 };
 
 __global__ void __launch_bounds__(kFusedThreads, 1) gn_fused_kernel(const FusedArgs A) {
@@ -764,7 +1003,17 @@ __global__ void __launch_bounds__(kFusedThreads, 1) gn_fused_kernel(const FusedA
   } else if ((A.phases & M3R_PH_FACTOR) && (A.phases & M3R_PH_ASSEMBLE)) {
     grid_barrier(A.state, gridDim.x);
   }
-  if (A.phases & M3R_PH_FACTOR) {
+  // envelope solver: decided once per solve on the device (skyline_plan_kernel), the same for every CTA
+  const int sky = (A.sky != nullptr) ? __ldcg(A.state + kSkyLanes) : 0;
+  if ((A.phases & M3R_PH_FACTOR) && sky > 0) {
+    if (blockIdx.x != 0) {
+      idle_wait(A);
+      return;
+    }
+    tl_mark(A, 5);
+    sky_factor(A, sm.sky, s_y);
+    tl_mark(A, 8);
+  } else if (A.phases & M3R_PH_FACTOR) {
     // only the CTAs that can get work in block column kb take part in its two barriers; the trailing matrix shrinks, so
     // the set is non-increasing and a CTA that drops out never comes back
     tl_mark(A, 5);
@@ -788,8 +1037,12 @@ __global__ void __launch_bounds__(kFusedThreads, 1) gn_fused_kernel(const FusedA
     }
   }
   if ((A.phases & M3R_PH_BACKSOLVE) && blockIdx.x == 0) {
-    backsolve_phase(A, sm.back, s_y);
+    if (sky > 0)
+      backsolve_phase<true>(A, sm.back, s_y);
+    else
+      backsolve_phase<false>(A, sm.back, s_y);
     tl_mark(A, 6);
+    if (sky > 0) idle_release(A);
   }
 }
 
@@ -821,7 +1074,10 @@ __global__ void __launch_bounds__(kSmallThreads, 1) gn_small_kernel(const FusedA
     grid_barrier(A.state, gridDim.x);
   }
   if (A.phases & M3R_PH_FACTOR) {
-    if (blockIdx.x != 0) return;
+    if (blockIdx.x != 0) {
+      idle_wait(A);
+      return;
+    }
     tl_mark(A, 5);
     double* M = reinterpret_cast<double*>(s_raw);
     SmallAux& ax = *reinterpret_cast<SmallAux*>(M + prow(A.n + 1));
@@ -835,6 +1091,7 @@ __global__ void __launch_bounds__(kSmallThreads, 1) gn_small_kernel(const FusedA
     tl_mark(A, 7);
     finish_solution(A, y, &ax.bad, ax.norm);
     tl_mark(A, 6);
+    idle_release(A);
   }
 }
 
@@ -871,6 +1128,7 @@ int launch_fused(const GnWs& ws, float* Twc, float delta_thresh, int phases, cud
   a.pflag = ws.pflag();
   a.pmask = ws.pflag() + (ws.L.n / 64 + 4);
   a.pstride = ws.L.n / 64 + 4;
+  a.sky = nullptr;
   a.dx = ws.dx();
   a.state = ws.state();
   a.n = ws.L.n;
@@ -881,6 +1139,8 @@ int launch_fused(const GnWs& ws, float* Twc, float delta_thresh, int phases, cud
   a.num_edges = ws.L.num_edges;
   a.hess_grid = hessian_grid();
   a.phases = phases;
+  static int launch_seq = 0;
+  a.launch_id = ++launch_seq;
   a.packed = ws.L.n <= kSmallMaxN ? 1 : 0;
   a.delta_thresh = delta_thresh;
   a.timeline = g_timeline;
@@ -914,7 +1174,8 @@ int launch_fused(const GnWs& ws, float* Twc, float delta_thresh, int phases, cud
     return M3R_OK;
   }
   const size_t smem = sizeof(FusedSmem) + sizeof(double) * (size_t)ws.L.nblk * kBlk;
-  if (smem > 200 * 1024) {
+  a.sky = (g_solver_mode != 1 && ws.L.nblk <= kSkyMaxBlk) ? ws.sky() : nullptr;
+  if (smem > 227 * 1024) {
     set_error("gauss_newton: system of dimension %d exceeds the shared-memory back substitution", ws.L.n);
     return M3R_ERR_UNSUPPORTED;
   }
@@ -932,6 +1193,15 @@ int launch_fused(const GnWs& ws, float* Twc, float delta_thresh, int phases, cud
 }  // namespace m3r
 
 // diagnostics hook (tools/fused_timeline.py): device buffer of 2*cap u64; [0] = number of marks, then (tag, ns) pairs
+extern "C" void m3r_debug_set_solver(int mode) { m3r::g_solver_mode = mode; }
+
+extern "C" int m3r_debug_solver_lanes(const void* workspace) {
+  int v = 0;  // the solver state is the first region of the workspace (gn_layout)
+  if (cudaDeviceSynchronize() != cudaSuccess) return -1;
+  if (cudaMemcpy(&v, (const int*)workspace + m3r::kSkyLanes, sizeof(int), cudaMemcpyDeviceToHost) != cudaSuccess) return -1;
+  return v;
+}
+
 extern "C" void m3r_debug_set_timeline(unsigned long long* dev_buf, int cap) {
   m3r::g_timeline = dev_buf;
   m3r::g_timeline_cap = cap;

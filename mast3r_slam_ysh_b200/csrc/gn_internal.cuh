@@ -12,6 +12,7 @@ constexpr int kHessThreads = 256;
 constexpr int kHessChunkAlign = 2 * kHessThreads; // the Hessian kernel's per-CTA range of compacted records is a multiple of this
 constexpr int kMaxHessCtas = 1024;   // upper bound on the persistent Hessian grid (2 CTAs per SM), sizes `partial`
 constexpr int kBlk = 32;             // Cholesky block size
+constexpr int kSmallMaxN = 224;      // largest system of the single-CTA shared-memory solver (gn_small.cuh)
 constexpr int kBlockDoubles = 56;    // per-edge block: M (7x7 row-major) + v (7)
 
 // device-resident solver state (ints)
@@ -20,7 +21,24 @@ enum StateSlot {
   kBarCount = 6, kBarGen = 7,  // grid barrier of the fused solver kernel
   kCFail = 8,                  // some point of some keyframe fails the confidence gate (set by pack_points)
   kPeerTimeout = 9,            // a peer rank never arrived at the in-kernel all-reduce (multi-GPU path)
-  kStateInts = 10
+  kSkyLanes = 10,              // > 0: the envelope (skyline) factorisation applies and needs this many lanes (gn_solve.cu)
+  kIdleFlag = 11,              // experiment M3R_IDLE_SPIN (gn_fused.cu)
+  kStateInts = 12
+};
+
+// Envelope ("skyline") plan of the assembled system, built once per solve by skyline_plan_kernel (gn_solve.cu) from the
+// keyframe graph and consumed by the single-CTA envelope Cholesky in gn_fused.cu.  32-row blocks; fb[rb] = first column
+// block of row block rb with a structural non-zero.  Row block rb is ACTIVE at elimination step kb when fb[rb] <= kb <=
+// rb; an active row block owns a lane (< kSkyMaxLanes) from the step it joins until it has been eliminated itself.
+constexpr int kSkyMaxLanes = 6;      // 21 resident 32x32 tiles of doubles = 183 KB of shared memory
+constexpr int kSkyMaxBlk = 112;      // column blocks (n <= 3584: 512 keyframes, the reference's cap, frame.py:221)
+constexpr int kSkySched = 8;         // ints per step: [m, new-member bitmask, act[0..5]] (act ascending, act[0] = kb)
+struct SkyPlan {                     // int offsets inside the `sky` workspace region
+  static __host__ __device__ int first(int) { return 0; }                          // [n_free] pose level (index prep)
+  static __host__ __device__ int fb(int n_free) { return n_free; }                 // [kSkyMaxBlk]
+  static __host__ __device__ int lane(int n_free) { return n_free + kSkyMaxBlk; }  // [kSkyMaxBlk]
+  static __host__ __device__ int sched(int n_free) { return n_free + 2 * kSkyMaxBlk; }  // [kSkyMaxBlk][kSkySched]
+  static __host__ __device__ int total(int n_free) { return n_free + (2 + kSkySched) * kSkyMaxBlk + 8; }
 };
 
 // phases of the fused solver kernel (gn_fused.cu)
@@ -46,7 +64,7 @@ typedef int2 EdgeRec;
 struct GnLayout {
   int num_kf, num_pts, num_edges, n_free, n, ld, nblk, tiles;
   size_t off_xc, off_rec, off_ie, off_je, off_io, off_jo, off_partial, off_blocks, off_sqv, off_ecount, off_eoff, off_tstate, off_inc_off, off_inc_list, off_inc_other, off_sys,
-      off_lfac, off_pflag, off_dx, off_state, off_uniq_flag, off_all, off_K, total;
+      off_lfac, off_pflag, off_sky, off_dx, off_state, off_uniq_flag, off_all, off_K, total;
 };
 
 GnLayout gn_layout(int num_kf, int num_pts, int num_edges, int num_all_edges);
@@ -70,6 +88,7 @@ struct GnWs {
   double* sys() const { return (double*)(base + L.off_sys); }
   double* lfac() const { return (double*)(base + L.off_lfac); }
   int* pflag() const { return (int*)(base + L.off_pflag); }
+  int* sky() const { return (int*)(base + L.off_sky); }
   float* dx() const { return (float*)(base + L.off_dx); }
   int* state() const { return (int*)(base + L.off_state); }
   int* uniq_flag() const { return (int*)(base + L.off_uniq_flag); }

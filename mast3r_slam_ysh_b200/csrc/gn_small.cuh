@@ -11,7 +11,6 @@
 namespace m3r {
 
 constexpr int kSmallThreads = 256;
-constexpr int kSmallMaxN = 224;
 
 __host__ __device__ __forceinline__ int prow(int r) {
   const int m = r >> 1;

@@ -149,12 +149,14 @@ __global__ void __launch_bounds__(kPrepThreads) index_prep_kernel(const int64_t*
                                                                   int num_kf, int padded, int* __restrict__ ie,
                                                                   int* __restrict__ je, int* __restrict__ inc_off,
                                                                   int* __restrict__ inc_list,
-                                                                  int* __restrict__ inc_other, int* __restrict__ state) {
+                                                                  int* __restrict__ inc_other, int* __restrict__ state,
+                                                                  int* __restrict__ sky_first) {
   extern __shared__ __align__(16) unsigned char s_prep[];
   long long* ids = reinterpret_cast<long long*>(s_prep);                 // [padded]
   int* s_ie = reinterpret_cast<int*>(ids + padded);                       // [num_edges]
   int* s_je = s_ie + num_edges;                                           // [num_edges]
   int* s_deg = s_je + num_edges;                                          // [num_kf + 1]
+  int* s_first = s_deg + num_kf + 1;                                      // [num_kf + 1]
   __shared__ int s_warp[kPrepThreads / 32];
   __shared__ int s_nuniq, s_bad;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -238,7 +240,29 @@ __global__ void __launch_bounds__(kPrepThreads) index_prep_kernel(const int64_t*
       s_ie[e] = r;
     }
   }
+  // envelope of the assembled system over ALL ranks' edges (the all-reduced [H | b] has the pattern of the whole graph):
+  // first[a] = smallest free pose adjacent to free pose a, or a itself; consumed by skyline_plan_kernel
+  const int n_free_env = num_kf > 0 ? num_kf - 1 : 0;
+  for (int a = tid; a < n_free_env; a += kPrepThreads) s_first[a] = a;
   __syncthreads();
+  for (int k = tid; k < num_all; k += kPrepThreads) {
+    int r[2];
+#pragma unroll
+    for (int q = 0; q < 2; q++) {
+      const long long v = q ? (long long)all_jj[k] : (long long)all_ii[k];
+      int lo = 0, hi = nuniq;
+      while (lo < hi) {
+        const int mid = (lo + hi) >> 1;
+        if (ids[mid] < v) lo = mid + 1; else hi = mid;
+      }
+      r[q] = lo;
+    }
+    if (r[0] >= num_kf || r[1] >= num_kf) continue;
+    const int a = max(r[0], r[1]) - 1, o = min(r[0], r[1]) - 1;
+    if (o >= 0) atomicMin(&s_first[a], o);
+  }
+  __syncthreads();
+  for (int a = tid; a < n_free_env; a += kPrepThreads) sky_first[a] = s_first[a];
   if (tid == 0) state[kBadEdges] = s_bad;
   // incidence lists (see incidence_kernel): degrees with shared-memory atomics over all edge ends, offsets by one
   // thread, then one WARP per free keyframe walks the edges 32 at a time and places its entries with ballots, in the
@@ -330,6 +354,76 @@ __global__ void __launch_bounds__(kPrepThreads) index_prep_kernel(const int64_t*
   }
 }
 
+// ---- envelope plan (see SkyPlan, gn_internal.cuh).  One CTA, once per solve.  state[kSkyLanes] = lanes needed, or 0
+//      when more than kSkyMaxLanes row blocks would be active at some step (the dense multi-CTA solver runs then).
+int g_solver_mode = 0;  // 0: envelope solver where it applies, 1: always the dense multi-CTA solver (m3r_debug_set_solver)
+
+__global__ void __launch_bounds__(128) skyline_plan_kernel(int* __restrict__ sky, int n_free, int nblk,
+                                                           int* __restrict__ state) {
+  __shared__ int s_fb[kSkyMaxBlk], s_lane[kSkyMaxBlk], s_over;
+  const int tid = threadIdx.x;
+  const int* first = sky + SkyPlan::first(n_free);
+  if (tid == 0) s_over = 0;
+  for (int rb = tid; rb < nblk; rb += blockDim.x) s_fb[rb] = rb;
+  __syncthreads();
+  for (int a = tid; a < n_free; a += blockDim.x) {
+    const int cb = (kPoseDim * first[a]) / kBlk;  // first column block of the 7 rows of pose a
+    const int r0 = (kPoseDim * a) / kBlk, r1 = (kPoseDim * a + kPoseDim - 1) / kBlk;
+    atomicMin(&s_fb[r0], cb);
+    if (r1 != r0) atomicMin(&s_fb[r1], cb);
+  }
+  __syncthreads();
+  // schedule of step kb: the active row blocks in ascending order, members that join at this step flagged
+  int* sched = sky + SkyPlan::sched(n_free);
+  for (int kb = tid; kb < nblk; kb += blockDim.x) {
+    int m = 0, mask = 0;
+    for (int rb = kb; rb < nblk; rb++) {
+      if (s_fb[rb] > kb) continue;
+      if (m < kSkyMaxLanes) {
+        sched[kb * kSkySched + 2 + m] = rb;
+        if (s_fb[rb] == kb || (rb == kb && kb == 0)) mask |= 1 << m;
+      }
+      m++;
+    }
+    if (m > kSkyMaxLanes) atomicMax(&s_over, m);
+    sched[kb * kSkySched] = m;
+    sched[kb * kSkySched + 1] = mask;
+  }
+  __syncthreads();
+  if (tid == 0) {
+    // lanes: a row block takes the free lane that has been idle longest when it joins (step fb[rb]) and gives it back
+    // after its own elimination.  If every lane taken at step kb was already idle during step kb - 1, the kernel may
+    // fetch the new tiles one step early (bit 8 of the step's mask word).
+    int used = 0, lanes = 0;
+    int freed_at[kSkyMaxLanes];
+    for (int l = 0; l < kSkyMaxLanes; l++) freed_at[l] = -4 - l;  // ties: lowest lane first
+    if (!s_over) {
+      for (int kb = 0; kb < nblk; kb++) {
+        bool early = kb > 0;
+        for (int rb = kb; rb < nblk; rb++) {
+          if (s_fb[rb] != kb) continue;
+          int best = -1;
+          for (int l = 0; l < kSkyMaxLanes; l++)
+            if (!(used & (1 << l)) && (best < 0 || freed_at[l] < freed_at[best])) best = l;
+          used |= 1 << best;
+          s_lane[rb] = best;
+          if (best + 1 > lanes) lanes = best + 1;
+          early = early && freed_at[best] <= kb - 2;
+        }
+        if (early && (sched[kb * kSkySched + 1] & 0xff)) sched[kb * kSkySched + 1] |= 1 << 8;
+        used &= ~(1 << s_lane[kb]);
+        freed_at[s_lane[kb]] = kb;
+      }
+    }
+    state[kSkyLanes] = s_over ? 0 : lanes;
+  }
+  __syncthreads();
+  for (int rb = tid; rb < nblk; rb += blockDim.x) {
+    sky[SkyPlan::fb(n_free) + rb] = s_fb[rb];
+    sky[SkyPlan::lane(n_free) + rb] = s_lane[rb];
+  }
+}
+
 int launch_index_prep(const GnWs& ws, const int64_t* local_ii, const int64_t* local_jj, const int64_t* all_ii,
                       const int64_t* all_jj, int num_all_edges, cudaStream_t st) {
   const int E = ws.L.num_edges;
@@ -337,7 +431,7 @@ int launch_index_prep(const GnWs& ws, const int64_t* local_ii, const int64_t* lo
   if (count <= kPrepMaxCount) {
     int padded = 2;
     while (padded < count) padded <<= 1;
-    const size_t smem = sizeof(long long) * (size_t)padded + sizeof(int) * (size_t)(2 * E + ws.L.num_kf + 2);
+    const size_t smem = sizeof(long long) * (size_t)padded + sizeof(int) * (size_t)(2 * E + 2 * ws.L.num_kf + 4);
     if (smem <= 200 * 1024) {
       static size_t attr = 0;
       if (smem > 48 * 1024 && smem > attr) {
@@ -346,8 +440,12 @@ int launch_index_prep(const GnWs& ws, const int64_t* local_ii, const int64_t* lo
       }
       index_prep_kernel<<<1, kPrepThreads, smem, st>>>(all_ii, all_jj, num_all_edges, local_ii, local_jj, E,
                                                          ws.L.num_kf, padded, ws.ie(), ws.je(), ws.inc_off(),
-                                                         ws.inc_list(), ws.inc_other(), ws.state());
+                                                         ws.inc_list(), ws.inc_other(), ws.state(), ws.sky());
       M3R_LAUNCH_CHECK();
+      if (g_solver_mode != 1 && ws.L.n > kSmallMaxN && ws.L.nblk <= kSkyMaxBlk) {
+        skyline_plan_kernel<<<1, 128, 0, st>>>(ws.sky(), ws.L.n_free, ws.L.nblk, ws.state());
+        M3R_LAUNCH_CHECK();
+      }
       return M3R_OK;
     }
   }
