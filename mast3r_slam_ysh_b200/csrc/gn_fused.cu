@@ -42,7 +42,6 @@ struct FusedArgs {
   float* dx;
   int* state;
   int n, ld, nblk, num_kf, n_free, num_edges, hess_grid, phases;
-  int launch_id;  // distinct per launch: idle CTAs of a single-CTA phase wait for state[kIdleFlag] == launch_id
   int packed;  // [H ; b] in the packed even-row layout of gn_small.cuh (n <= kSmallMaxN) instead of row-major with ld
   float delta_thresh;
   unsigned long long* timeline;  // diagnostics (m3r_debug_set_timeline): CTA 0 appends (tag, globaltimer ns) pairs
@@ -103,24 +102,6 @@ __device__ __forceinline__ void grid_barrier(int* state, int nb) {
     __threadfence();
   }
   __syncthreads();
-}
-
-// Experiment (M3R_IDLE_SPIN): CTAs without work in a single-CTA phase stay resident (sleeping) until CTA 0 is done
-// instead of exiting, to see whether a lone CTA with a large code body is issue-throttled.
-__device__ __forceinline__ void idle_wait(const FusedArgs& A) {
-#ifdef M3R_IDLE_SPIN
-  if (threadIdx.x == 0) {
-    long long spins = 0;
-    while (ld_relaxed_i(A.state + kIdleFlag) != A.launch_id && ++spins < (1LL << 22)) __nanosleep(M3R_IDLE_SPIN);
-  }
-  __syncthreads();
-#endif
-}
-__device__ __forceinline__ void idle_release(const FusedArgs& A) {
-#ifdef M3R_IDLE_SPIN
-  __syncthreads();
-  if (threadIdx.x == 0) st_release_i(A.state + kIdleFlag, A.launch_id);
-#endif
 }
 
 // ============================================================================================== phase: peer all-reduce
@@ -200,8 +181,10 @@ __device__ __forceinline__ void peer_sum_store(const FusedArgs& A, size_t off2) 
   }
 }
 
+__device__ __forceinline__ int row_first_col(const FusedArgs& A, int sky, int r);
+
 template <int THREADS>
-__device__ __forceinline__ void peer_allreduce_phase(const FusedArgs& A) {
+__device__ __forceinline__ void peer_allreduce_phase(const FusedArgs& A, int sky) {
   const PeerInfo& P = A.peer;
   grid_peer_barrier(A, 2 * P.epoch + 1);
   if (A.packed) {  // packed lower triangle + rhs row: one linear range of prow(n + 1) doubles (even by construction)
@@ -215,7 +198,7 @@ __device__ __forceinline__ void peer_allreduce_phase(const FusedArgs& A) {
     for (int r = P.rank + P.world * blockIdx.x; r <= A.n; r += P.world * gridDim.x) {
       const int len2 = (min(r + 1, A.n) + 1) / 2;
       const size_t base2 = (size_t)r * A.ld / 2;
-      for (int i = threadIdx.x; i < len2; i += THREADS) peer_sum_store(A, base2 + i);
+      for (int i = row_first_col(A, sky, r) / 2 + threadIdx.x; i < len2; i += THREADS) peer_sum_store(A, base2 + i);
     }
   }
   grid_peer_barrier(A, 2 * P.epoch + 2);
@@ -257,7 +240,14 @@ __device__ __forceinline__ size_t sys_at(const FusedArgs& A, int r, int c) {
   return A.packed ? (size_t)(prow(r) + c) : (size_t)r * A.ld + c;
 }
 
-__device__ __forceinline__ void assemble_zero(const FusedArgs& A) {
+// First column of row r that the solver will ever read: with the envelope solver nothing left of the row block's
+// envelope is touched (not by the assembly, the joins or the back substitution), so it is neither zeroed nor summed
+// over the ranks (12.7 MB -> 1.8 MB per iteration at n = 1785 with a window of 8).
+__device__ __forceinline__ int row_first_col(const FusedArgs& A, int sky, int r) {
+  return (sky > 0 && r < A.n) ? kBlk * __ldg(A.sky + SkyPlan::fb(A.n_free) + r / kBlk) : 0;
+}
+
+__device__ __forceinline__ void assemble_zero(const FusedArgs& A, int sky) {
   if (A.packed) {
     const int total2 = prow(A.n + 1) >> 1;
     double2* p = reinterpret_cast<double2*>(A.sys);
@@ -271,7 +261,7 @@ __device__ __forceinline__ void assemble_zero(const FusedArgs& A) {
   for (int r = gwarp; r <= A.n; r += nwarp) {
     const int width = (r == A.n) ? A.n : 7 * (r / 7) + 7;
     double* row = A.sys + (size_t)r * A.ld;
-    for (int c = lane; c < width; c += 32) row[c] = 0.0;
+    for (int c = row_first_col(A, sky, r) + lane; c < width; c += 32) row[c] = 0.0;
   }
 }
 
@@ -982,6 +972,8 @@ __global__ void __launch_bounds__(kFusedThreads, 1) gn_fused_kernel(const FusedA
   // kDone is only written by the last phase of an earlier launch on the same stream: uniform over the grid
   if (__ldcg(A.state + kDone)) return;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  // envelope solver: decided once per solve on the device (skyline_plan_kernel), the same for every CTA
+  const int sky = (A.sky != nullptr) ? __ldcg(A.state + kSkyLanes) : 0;
   tl_mark(A, 1);
 
   if (A.phases & M3R_PH_FINALIZE) {
@@ -991,7 +983,7 @@ __global__ void __launch_bounds__(kFusedThreads, 1) gn_fused_kernel(const FusedA
   }
   if (A.phases & M3R_PH_ASSEMBLE) {
     if (blockIdx.x == 0 && threadIdx.x == 0) A.state[kFailNow] = 0;
-    assemble_zero(A);
+    assemble_zero(A, sky);
     tl_mark(A, 2);
     grid_barrier(A.state, gridDim.x);  // also orders finalize -> assemble
     tl_mark(A, 3);
@@ -999,17 +991,12 @@ __global__ void __launch_bounds__(kFusedThreads, 1) gn_fused_kernel(const FusedA
     tl_mark(A, 4);
   }
   if (A.peer.world > 1) {
-    peer_allreduce_phase<kFusedThreads>(A);  // its barriers also order assembly -> factorisation
+    peer_allreduce_phase<kFusedThreads>(A, sky);  // its barriers also order assembly -> factorisation
   } else if ((A.phases & M3R_PH_FACTOR) && (A.phases & M3R_PH_ASSEMBLE)) {
     grid_barrier(A.state, gridDim.x);
   }
-  // envelope solver: decided once per solve on the device (skyline_plan_kernel), the same for every CTA
-  const int sky = (A.sky != nullptr) ? __ldcg(A.state + kSkyLanes) : 0;
   if ((A.phases & M3R_PH_FACTOR) && sky > 0) {
-    if (blockIdx.x != 0) {
-      idle_wait(A);
-      return;
-    }
+    if (blockIdx.x != 0) return;
     tl_mark(A, 5);
     sky_factor(A, sm.sky, s_y);
     tl_mark(A, 8);
@@ -1042,7 +1029,6 @@ __global__ void __launch_bounds__(kFusedThreads, 1) gn_fused_kernel(const FusedA
     else
       backsolve_phase<false>(A, sm.back, s_y);
     tl_mark(A, 6);
-    if (sky > 0) idle_release(A);
   }
 }
 
@@ -1061,7 +1047,7 @@ __global__ void __launch_bounds__(kSmallThreads, 1) gn_small_kernel(const FusedA
   }
   if (A.phases & M3R_PH_ASSEMBLE) {
     if (blockIdx.x == 0 && threadIdx.x == 0) A.state[kFailNow] = 0;
-    assemble_zero(A);
+    assemble_zero(A, 0);
     tl_mark(A, 2);
     grid_barrier(A.state, gridDim.x);
     tl_mark(A, 3);
@@ -1069,15 +1055,12 @@ __global__ void __launch_bounds__(kSmallThreads, 1) gn_small_kernel(const FusedA
     tl_mark(A, 4);
   }
   if (A.peer.world > 1) {
-    peer_allreduce_phase<kSmallThreads>(A);  // its barriers also order assembly -> factorisation
+    peer_allreduce_phase<kSmallThreads>(A, 0);  // its barriers also order assembly -> factorisation
   } else if ((A.phases & M3R_PH_FACTOR) && (A.phases & M3R_PH_ASSEMBLE)) {
     grid_barrier(A.state, gridDim.x);
   }
   if (A.phases & M3R_PH_FACTOR) {
-    if (blockIdx.x != 0) {
-      idle_wait(A);
-      return;
-    }
+    if (blockIdx.x != 0) return;
     tl_mark(A, 5);
     double* M = reinterpret_cast<double*>(s_raw);
     SmallAux& ax = *reinterpret_cast<SmallAux*>(M + prow(A.n + 1));
@@ -1091,7 +1074,6 @@ __global__ void __launch_bounds__(kSmallThreads, 1) gn_small_kernel(const FusedA
     tl_mark(A, 7);
     finish_solution(A, y, &ax.bad, ax.norm);
     tl_mark(A, 6);
-    idle_release(A);
   }
 }
 
@@ -1139,8 +1121,6 @@ int launch_fused(const GnWs& ws, float* Twc, float delta_thresh, int phases, cud
   a.num_edges = ws.L.num_edges;
   a.hess_grid = hessian_grid();
   a.phases = phases;
-  static int launch_seq = 0;
-  a.launch_id = ++launch_seq;
   a.packed = ws.L.n <= kSmallMaxN ? 1 : 0;
   a.delta_thresh = delta_thresh;
   a.timeline = g_timeline;

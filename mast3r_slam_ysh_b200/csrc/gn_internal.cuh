@@ -22,8 +22,7 @@ enum StateSlot {
   kCFail = 8,                  // some point of some keyframe fails the confidence gate (set by pack_points)
   kPeerTimeout = 9,            // a peer rank never arrived at the in-kernel all-reduce (multi-GPU path)
   kSkyLanes = 10,              // > 0: the envelope (skyline) factorisation applies and needs this many lanes (gn_solve.cu)
-  kIdleFlag = 11,              // experiment M3R_IDLE_SPIN (gn_fused.cu)
-  kStateInts = 12
+  kStateInts = 11
 };
 
 // Envelope ("skyline") plan of the assembled system, built once per solve by skyline_plan_kernel (gn_solve.cu) from the

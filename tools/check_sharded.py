@@ -10,9 +10,10 @@ dist.init_process_group("nccl", device_id=dev)
 lo = syn.LOCAL_OPT
 out = {"world": world}
 ok = True
-# (keyframes, h, w): n = 77 (single-CTA solver, packed system) and n = 273 (multi-CTA solver, row-major system)
-for nkf, h, w in ((12, 96, 128), (40, 48, 64)):
-    edges = syn.ring_edges(nkf, 3)
+# (keyframes, h, w, graph): n = 77 (small single-CTA solver, packed system), n = 273 and n = 553 (envelope solver, row-major
+# system; the plan is built from ALL ranks' edges), n = 413 with loop closures everywhere (dense multi-CTA solver)
+for nkf, h, w, span in ((12, 96, 128, 3), (40, 48, 64, 3), (80, 24, 32, 8), (60, 24, 32, 0)):
+    edges = syn.ring_edges(nkf, span) if span > 0 else syn.loop_closure_edges(nkf, n_loop=3, seed=2)
     ng = len(edges[0])
     g = syn.make_gn_problem(nkf, h, w, edges, seed=31, device=dev, yaw_step_deg=8.0)
     P = (lo["sigma_ray"], lo["sigma_dist"], lo["C_conf"], lo["Q_conf"], 6, lo["delta_norm"])
@@ -33,7 +34,7 @@ for nkf, h, w in ((12, 96, 128), (40, 48, 64)):
         same = all(torch.equal(gath[0], x) for x in gath)
         res[mode] = {"pose_rel_vs_single_gpu": rel, "replicas_bit_identical": same, "info": info.tolist(),
                      "gt_err": float((T2 - g["Twc_gt"]).abs().max())}
-        ok = ok and rel < 1e-5 and same and (info.tolist()[3] & ~(15 << 24)) == 0
+        ok = ok and rel < (1e-5 if span == 3 else 1e-4) and same and (info.tolist()[3] & ~(15 << 24)) == 0
         res[mode + "_T"] = T2
     res["peer_equals_nccl_bits"] = bool(torch.equal(res.pop("peer_T"), res.pop("nccl_T")))
     out[f"nkf{nkf}"] = res

@@ -89,10 +89,64 @@ __device__ void v4(double (*D)[B + 1], double* col, int lane) {
 #pragma unroll
   for (int c = 0; c < B; c++) D[lane][c] = (c <= lane) ? a[c] : 0.0;
 }
+// 1/x: fp32 reciprocal seed + two Newton steps in fp64 (two dependent FMAs each)
+__device__ __forceinline__ double fast_rcp(double x) {
+  double y = (double)__frcp_rn((float)x);
+  double t = fma(-x, y, 1.0); y = fma(y, t, y);
+  t = fma(-x, y, 1.0); y = fma(y, t, y);
+  return y;
+}
+// V5: square-root-free pivot chain.  The rank-1 update uses the UNSCALED column (stored to shared memory before the
+// reciprocal is known, so the broadcast overlaps the reciprocal) and m = a_j / d_jj; the rsqrt scaling of L is applied
+// once at the end, off the chain.  Column buffer double-buffered: one __syncwarp per step.
+__device__ void v5(double (*D)[B + 1], double (*col)[B], double* inv, int lane) {
+  double a[B];
+#pragma unroll
+  for (int c = 0; c < B; c++) a[c] = D[lane][c];
+#pragma unroll
+  for (int j = 0; j < B; j++) {
+    col[j & 1][lane] = a[j];
+    const double djj = shfl_d(a[j], j);
+    const double m = a[j] * fast_rcp(djj);
+    __syncwarp();
+#pragma unroll
+    for (int c = j + 1; c < B; c++) a[c] = fma(-m, col[j & 1][c], a[c]);
+  }
+  double d = 0.0;
+#pragma unroll
+  for (int c = 0; c < B; c++) d = (c == lane) ? a[c] : d;
+  inv[lane] = fast_rsqrt(d);
+  __syncwarp();
+#pragma unroll
+  for (int c = 0; c < B; c++) D[lane][c] = (c <= lane) ? a[c] * inv[c] : 0.0;
+}
+// V6: as V5, the pivot broadcast through shared memory as well (no shuffles): every lane reads d_jj = col[j]
+__device__ void v6(double (*D)[B + 1], double (*col)[B], double* inv, int lane) {
+  double a[B];
+#pragma unroll
+  for (int c = 0; c < B; c++) a[c] = D[lane][c];
+#pragma unroll
+  for (int j = 0; j < B; j++) {
+    col[j & 1][lane] = a[j];
+    __syncwarp();
+    const double m = a[j] * fast_rcp(col[j & 1][j]);
+#pragma unroll
+    for (int c = j + 1; c < B; c++) a[c] = fma(-m, col[j & 1][c], a[c]);
+  }
+  double d = 0.0;
+#pragma unroll
+  for (int c = 0; c < B; c++) d = (c == lane) ? a[c] : d;
+  inv[lane] = fast_rsqrt(d);
+  __syncwarp();
+#pragma unroll
+  for (int c = 0; c < B; c++) D[lane][c] = (c <= lane) ? a[c] * inv[c] : 0.0;
+}
 template <int V>
 __global__ void bench(const double* in, double* out, long long* cycles, int reps) {
   __shared__ double D[B][B + 1];
   __shared__ double col[B];
+  __shared__ double col2[2][B];
+  __shared__ double inv[B];
   const int lane = threadIdx.x;
   long long tot = 0;
   for (int r = 0; r < reps; r++) {
@@ -103,6 +157,8 @@ __global__ void bench(const double* in, double* out, long long* cycles, int reps
     if (V == 2) v2(D, lane);
     if (V == 3) v3(D, col, lane);
     if (V == 4) v4(D, col, lane);
+    if (V == 5) v5(D, col2, inv, lane);
+    if (V == 6) v6(D, col2, inv, lane);
     __syncwarp();
     tot += clock64() - t0;
   }
@@ -120,12 +176,13 @@ int main() {
     for (int pass = 0; pass < 2; pass++) {
       if (v == 1) bench<1><<<1, 32>>>(din, dout, dc, 20); if (v == 2) bench<2><<<1, 32>>>(din, dout, dc, 20);
       if (v == 3) bench<3><<<1, 32>>>(din, dout, dc, 20); if (v == 4) bench<4><<<1, 32>>>(din, dout, dc, 20);
+      if (v == 5) bench<5><<<1, 32>>>(din, dout, dc, 20); if (v == 6) bench<6><<<1, 32>>>(din, dout, dc, 20);
       cudaDeviceSynchronize();
     }
     std::vector<double> R(B * B); long long c; cudaMemcpy(R.data(), dout, B * B * 8, cudaMemcpyDeviceToHost); cudaMemcpy(&c, dc, 8, cudaMemcpyDeviceToHost);
     double err = 0; for (int i = 0; i < B * B; i++) err = std::fmax(err, std::fabs(R[i] - L[i]));
     printf("V%d: %lld cycles per 32x32 factorisation (%.2f us @1.965GHz), max |L - L_ref| = %.2e  (%s)\n", v, c, c / 1965.0, err, cudaGetErrorString(cudaGetLastError()));
   };
-  for (int v = 1; v <= 4; v++) run(v);
+  for (int v = 1; v <= 6; v++) run(v);
   return 0;
 }
