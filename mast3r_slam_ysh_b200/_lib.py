@@ -89,6 +89,8 @@ def load():
         fn.argtypes = args
     if lib.m3r_abi_version() != 1:
         raise ImportError("libm3r_backends_b200.so: ABI version mismatch")
+    if os.environ.get("M3R_SOLVER") == "dense":  # A/B switch for benchmarking: envelope Cholesky off
+        lib.m3r_debug_set_solver(1)
     _lib = lib
     return lib
 
