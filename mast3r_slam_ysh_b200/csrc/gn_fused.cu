@@ -57,11 +57,23 @@ __device__ __forceinline__ void tl_mark(const FusedArgs& A, int tag) {
   if (A.timeline != nullptr && blockIdx.x == 0 && threadIdx.x == 0) {
     unsigned long long t;
     asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
-    const unsigned long long k = A.timeline[0];
+    const unsigned long long k = atomicAdd(A.timeline, 1ULL);
     if ((int)k + 1 < A.timeline_cap) {
       A.timeline[2 * (k + 1)] = (unsigned long long)tag;
       A.timeline[2 * (k + 1) + 1] = t;
-      A.timeline[0] = k + 1;
+    }
+  }
+}
+
+// same, from any one thread of CTA 0 (slots claimed atomically: marks of different warps may interleave)
+__device__ __forceinline__ void tl_mark_any(const FusedArgs& A, int tag) {
+  if (A.timeline != nullptr && blockIdx.x == 0) {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+    const unsigned long long k = atomicAdd(A.timeline, 1ULL);
+    if ((int)k + 1 < A.timeline_cap) {
+      A.timeline[2 * (k + 1)] = (unsigned long long)tag;
+      A.timeline[2 * (k + 1) + 1] = t;
     }
   }
 }
@@ -937,11 +949,14 @@ __device__ __forceinline__ void sky_factor(const FusedArgs& A, SkySmem& sm, doub
           out[l] = (r < nb && c <= r) ? Tkk[r][c] : (r == c ? 1.0 : 0.0);
         }
       }
+      if (kb == 20 && tid == 32) tl_mark_any(A, 7101);
       for (int j = 1 + worker; j < m; j += nworkers) sky_rhs_and_store(A, sm, s_y, sched[2 + j], al0, c0, nb, lane);
+      if (kb == 20 && tid == 32) tl_mark_any(A, 7102);
       if (kb + 1 < nblk && (sm.sched[kb + 1][1] & kSkyPrefetched)) {
         sky_join(A, sm, kb + 1, worker * 32 + lane, nworkers * 32);
         asm volatile("cp.async.commit_group;" ::: "memory");
       }
+      if (kb == 20 && tid == 32) tl_mark_any(A, 7103);
       // trailing tiles (act[i], act[j]) -= X_i X_j^T, 1 <= j <= i < m, two 16-row halves each; (1, 1) is done above
       const int pairs = m * (m - 1) / 2, skip = ahead ? 1 : 0;
       for (int item = worker; item < 2 * (pairs - skip); item += nworkers) {
@@ -949,6 +964,7 @@ __device__ __forceinline__ void sky_factor(const FusedArgs& A, SkySmem& sm, doub
         tile_decode((item >> 1) + skip, ti, tj);
         const int ali = sm.lane[sched[3 + ti]], alj = sm.lane[sched[3 + tj]];
         sky_update_item(sky_tile(sm, ali, al0), sky_tile(sm, alj, al0), sky_tile(sm, ali, alj), item & 1, lane);
+        if (kb == 20 && tid == 32) tl_mark_any(A, 7110 + item);
       }
     }
     looked = ahead;

@@ -77,10 +77,10 @@ __device__ __noinline__ bool factor_diag32(double* myrow, DiagAux& d, double* di
     const double l = (lane == j) ? djj * inv : a[j] * inv;
     a[j] = l;
     d.col[lane] = l;
-    if (lane == 0) {
-      d.inv[j] = inv;
-      if (dinv != nullptr) dinv[j] = inv;
-    }
+    // every lane stores the same value: a lane-0-only store is a divergent region per pivot (BSSY / BRA / BSYNC in the
+    // middle of the serial chain), which cost ~100 cycles per pivot (r1)
+    d.inv[j] = inv;
+    if (dinv != nullptr) dinv[j] = inv;
     __syncwarp();
 #pragma unroll
     for (int c = j + 1; c < kBlk; c++) a[c] = fma(-l, d.col[c], a[c]);  // rows above the diagonal: garbage, never read

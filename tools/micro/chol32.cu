@@ -141,16 +141,57 @@ __device__ void v6(double (*D)[B + 1], double (*col)[B], double* inv, int lane) 
 #pragma unroll
   for (int c = 0; c < B; c++) D[lane][c] = (c <= lane) ? a[c] * inv[c] : 0.0;
 }
+// V7: V3 folded: ONE unrolled 16-pivot body over 32 register columns, run twice (the second time on the columns 16..31
+// moved down to registers 0..15, the upper 16 registers then hold don't-care values): 15 KB of code instead of 40 KB,
+// 752 instead of 496 FMAs per lane.  col needs 48 entries (reads up to base + 31).
+__device__ void v7(double (*D)[B + 1], double* col, int lane) {
+  double a[B];
+#pragma unroll
+  for (int c = 0; c < B; c++) a[c] = D[lane][c];
+#pragma unroll 1
+  for (int base = 0; base < B; base += 16) {
+#pragma unroll
+    for (int j = 0; j < 16; j++) {
+      const double djj = shfl_d(a[j], base + j);
+      const double inv = fast_rsqrt(djj);
+      const double l = (lane == base + j) ? djj * inv : a[j] * inv;
+      a[j] = l;
+      col[lane] = l;
+      __syncwarp();
+#pragma unroll
+      for (int c = j + 1; c < B; c++) a[c] = fma(-l, col[base + c], a[c]);
+      __syncwarp();
+    }
+#pragma unroll
+    for (int c = 0; c < 16; c++) {
+      D[lane][base + c] = (base + c <= lane) ? a[c] : 0.0;
+      a[c] = a[c + 16];
+    }
+  }
+}
 template <int V>
 __global__ void bench(const double* in, double* out, long long* cycles, int reps) {
   __shared__ double D[B][B + 1];
-  __shared__ double col[B];
+  __shared__ double col[B + 16];
   __shared__ double col2[2][B];
+  __shared__ double Dx[B][B + 1];
   __shared__ double inv[B];
   const int lane = threadIdx.x;
   long long tot = 0;
   for (int r = 0; r < reps; r++) {
     for (int c = 0; c < B; c++) D[lane][c] = in[lane * B + c];
+    if (V >= 10) {  // cold instruction cache: ~100 KB of other straight-line code between the timed calls
+      for (int c = 0; c < B; c++) Dx[lane][c] = in[lane * B + c];
+      __syncwarp();
+      v1(Dx, lane);
+      for (int c = 0; c < B; c++) Dx[lane][c] = in[lane * B + c];
+      __syncwarp();
+      v5(Dx, col2, inv, lane);
+      for (int c = 0; c < B; c++) Dx[lane][c] = in[lane * B + c];
+      __syncwarp();
+      v4(Dx, col, lane);
+      if (Dx[lane][0] == 123.456) D[lane][0] = 0.0;
+    }
     __syncwarp();
     const long long t0 = clock64();
     if (V == 1) v1(D, lane);
@@ -159,11 +200,35 @@ __global__ void bench(const double* in, double* out, long long* cycles, int reps
     if (V == 4) v4(D, col, lane);
     if (V == 5) v5(D, col2, inv, lane);
     if (V == 6) v6(D, col2, inv, lane);
+    if (V == 7) v7(D, col, lane);
+    if (V == 13) v3(D, col, lane);
+    if (V == 17) v7(D, col, lane);
     __syncwarp();
     tot += clock64() - t0;
   }
   for (int c = 0; c < B; c++) out[lane * B + c] = (c <= lane) ? D[lane][c] : 0.0;
   if (lane == 0) *cycles = tot / reps;
+}
+// V3 inside a 256-thread CTA with 200 KB of dynamic shared memory (the solver kernel's configuration): warp 0 factors,
+// the other warps wait on the CTA barrier
+__global__ void bench_cta(const double* in, double* out, long long* cycles, int reps) {
+  extern __shared__ __align__(16) unsigned char dyn[];
+  double (*D)[B + 1] = reinterpret_cast<double (*)[B + 1]>(dyn + 150 * 1024);
+  double* col = reinterpret_cast<double*>(dyn + 190 * 1024);
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  long long tot = 0;
+  for (int r = 0; r < reps; r++) {
+    if (warp == 0) for (int c = 0; c < B; c++) D[lane][c] = in[lane * B + c];
+    __syncthreads();
+    const long long t0 = clock64();
+    if (warp == 0) v3(D, col, lane);
+    __syncthreads();
+    tot += clock64() - t0;
+  }
+  if (warp == 0) {
+    for (int c = 0; c < B; c++) out[lane * B + c] = (c <= lane) ? D[lane][c] : 0.0;
+    if (lane == 0) *cycles = tot / reps;
+  }
 }
 int main() {
   std::vector<double> A(B * B), L(B * B, 0.0);
@@ -177,12 +242,25 @@ int main() {
       if (v == 1) bench<1><<<1, 32>>>(din, dout, dc, 20); if (v == 2) bench<2><<<1, 32>>>(din, dout, dc, 20);
       if (v == 3) bench<3><<<1, 32>>>(din, dout, dc, 20); if (v == 4) bench<4><<<1, 32>>>(din, dout, dc, 20);
       if (v == 5) bench<5><<<1, 32>>>(din, dout, dc, 20); if (v == 6) bench<6><<<1, 32>>>(din, dout, dc, 20);
+      if (v == 7) bench<7><<<1, 32>>>(din, dout, dc, 20);
+      if (v == 13) bench<13><<<1, 32>>>(din, dout, dc, 20); if (v == 17) bench<17><<<1, 32>>>(din, dout, dc, 20);
       cudaDeviceSynchronize();
     }
     std::vector<double> R(B * B); long long c; cudaMemcpy(R.data(), dout, B * B * 8, cudaMemcpyDeviceToHost); cudaMemcpy(&c, dc, 8, cudaMemcpyDeviceToHost);
     double err = 0; for (int i = 0; i < B * B; i++) err = std::fmax(err, std::fabs(R[i] - L[i]));
     printf("V%d: %lld cycles per 32x32 factorisation (%.2f us @1.965GHz), max |L - L_ref| = %.2e  (%s)\n", v, c, c / 1965.0, err, cudaGetErrorString(cudaGetLastError()));
   };
-  for (int v = 1; v <= 6; v++) run(v);
+  for (int v = 1; v <= 7; v++) run(v);
+  {
+    cudaFuncSetAttribute(bench_cta, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+    for (int pass = 0; pass < 2; pass++) { bench_cta<<<1, 256, 200 * 1024>>>(din, dout, dc, 20); cudaDeviceSynchronize(); }
+    long long c; cudaMemcpy(&c, dc, 8, cudaMemcpyDeviceToHost);
+    printf("V3 in a 256-thread CTA with 200 KB dynamic smem: %lld cycles (%.2f us) (%s)\n", c, c / 1965.0, cudaGetErrorString(cudaGetLastError()));
+    for (int pass = 0; pass < 2; pass++) { bench_cta<<<148, 256, 200 * 1024>>>(din, dout, dc, 20); cudaDeviceSynchronize(); }
+    cudaMemcpy(&c, dc, 8, cudaMemcpyDeviceToHost);
+    printf("same, grid 148: %lld cycles (%.2f us) (%s)\n", c, c / 1965.0, cudaGetErrorString(cudaGetLastError()));
+  }
+  printf("cold instruction cache (V13 = V3, V17 = V7):\n");
+  run(13); run(17);
   return 0;
 }

@@ -56,6 +56,7 @@ for mode in (1, 0):
         lib.m3r_debug_set_timeline(None, 0)
         bb = buf.cpu().tolist(); k = bb[0]
         marks = [(bb[2 * (i + 1)], bb[2 * (i + 1) + 1]) for i in range(k)]
+        marks.sort(key=lambda x: x[1])
         res["timeline_us"] = [[marks[i][0], round((marks[i][1] - marks[i - 1][1]) / 1e3, 2)] for i in range(1, len(marks))]
     del s
 d = (out[0] - out[1]).double()
