@@ -773,13 +773,45 @@ __device__ __forceinline__ void backsolve_phase(const FusedArgs& A, BackSmem& sm
 // diagonal tile unless the look-ahead already did | X = X L^-T on the active rows below, y_kb = L^-1 y_kb | publish
 // L_kk, update the next diagonal tile | warp 0 factors the NEXT diagonal tile while warps 1-7 store the finished column
 // to sys, update y and the remaining active tiles.
+// ---- TMA bulk copies (cp.async.bulk, 1-D) + mbarrier: a 32 x 32 fp64 tile moves as 32 rows of 256 bytes, one
+//      instruction per lane, instead of 16 cp.async / 32 STG per lane with their address arithmetic (the update warps
+//      spent 2.8 us per step issuing the prefetch and 1.9 us storing the finished column of L that way; r1)
+__device__ __forceinline__ unsigned smem_u32(const void* p) { return (unsigned)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(unsigned long long* b, int count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(b)), "r"(count) : "memory");
+  asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+__device__ __forceinline__ void mbar_arrive_expect_tx(unsigned long long* b, unsigned bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(b)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ bool mbar_try_wait(unsigned long long* b, unsigned parity) {
+  unsigned ok;
+  asm volatile(
+      "{ .reg .pred p; mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2; selp.u32 %0, 1, 0, p; }"
+      : "=r"(ok)
+      : "r"(smem_u32(b)), "r"(parity)
+      : "memory");
+  return ok != 0;
+}
+__device__ __forceinline__ void bulk_g2s(void* dst, const void* src, unsigned bytes, unsigned long long* b) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(smem_u32(dst)),
+               "l"(src), "r"(bytes), "r"(smem_u32(b))
+               : "memory");
+}
+__device__ __forceinline__ void bulk_s2g(void* dst, const void* src, unsigned bytes) {
+  asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(dst), "r"(smem_u32(src)), "r"(bytes)
+               : "memory");
+}
+
 constexpr int kSkyTiles = kSkyMaxLanes * (kSkyMaxLanes + 1) / 2;
 constexpr int kSkyPrefetched = 1 << 8;  // schedule word 1: the new members' tiles were fetched during the previous step
 constexpr int kSkyStride = kBlk + 2;  // 272-byte rows: conflict-free LDS.128 for "one row per lane" and "8 rows per quarter warp"
 struct SkySmem {
   double T[kSkyTiles][kBlk][kSkyStride];
   DiagAux d;
+  unsigned long long mbar;  // completion of the tile loads of one join (one arrival carrying the byte count)
   int lane[kSkyMaxBlk];
+  int adj[kSkyMaxBlk][4];  // bit cb of row rb: tile (rb, cb) of the ASSEMBLED matrix has a structural non-zero
   int sched[kSkyMaxBlk][kSkySched];  // the whole plan: no L2 round trip on the per-step critical path
 };
 
@@ -830,35 +862,82 @@ __device__ __forceinline__ void sky_rhs_and_store(const FusedArgs& A, SkySmem& s
     s1 = fma(a.y, s_y[c0 + k + 1], s1);
   }
   s_y[kBlk * rbj + lane] -= s0 + s1;
-#pragma unroll 8
-  for (int r = 0; r < kBlk; r++) {
-    const int row = kBlk * rbj + r;
-    if (row < A.n && lane < nb) A.sys[(size_t)row * A.ld + c0 + lane] = Xj[r][lane];
+  const int row = kBlk * rbj + lane;
+  if (nb == kBlk) {  // always, when there are rows below: one 256-byte bulk store per row
+    if (row < A.n) bulk_s2g(A.sys + (size_t)row * A.ld + c0, &Xj[lane][0], kBlk * sizeof(double));
+    asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+  } else {
+    for (int r = 0; r < kBlk; r++) {
+      const int rr = kBlk * rbj + r;
+      if (rr < A.n && lane < nb) A.sys[(size_t)rr * A.ld + c0 + lane] = Xj[r][lane];
+    }
   }
 }
 
-// cp.async (no commit) of the tiles that join at step kb, by threads t = 0 .. nthr-1
+// Threads t0, t0 + 1, ... < nthr (whole warps): the tiles that join at step kb.  Full tiles: one 256-byte bulk copy per tile
+// row, the (tile, row) pairs dealt out over the threads, completing on sm.mbar (thread 0 of the group posts the byte
+// count and is the one arrival); rows beyond the matrix are zeroed with plain stores; the one tile with a partial
+// column block (the last diagonal tile) uses zero-filling cp.async.  Ends with a cp.async commit.
 __device__ __forceinline__ void sky_join(const FusedArgs& A, SkySmem& sm, int kb, int t0, int nthr) {
   const int n = A.n, ld = A.ld;
   const int* sched = sm.sched[kb];
   const int m = sched[0], mask = sched[1];
-  for (int t = 0, i = 0, j = 0; t < m * (m + 1) / 2; t++, j++) {
-    if (j > i) {
-      i++;
-      j = 0;
-    }
-    if (!(((mask >> i) | (mask >> j)) & 1)) continue;
-    const int rbi = sched[2 + i], rbj = sched[2 + j];
-    double (*Tt)[kSkyStride] = sky_tile(sm, sm.lane[rbi], sm.lane[rbj]);
-    for (int piece = t0; piece < 512; piece += nthr) {  // 512 16-byte pieces per tile
-      const int r = piece >> 4, c2 = (piece & 15) * 2;
-      const int row = kBlk * rbi + r, col = kBlk * rbj + c2;
-      int cnt = (row < n) ? n - col : 0;
-      cnt = cnt < 0 ? 0 : (cnt > 2 ? 2 : cnt);
-      const double* src = cnt > 0 ? A.sys + (size_t)row * ld + col : A.sys;
-      cp_async16_zfill(&Tt[r][c2], src, 8 * cnt);
+  unsigned bytes = 0;
+  int q = 0;  // running (tile, row) index over the full tiles
+  // pairs (new member p, any member o); a pair of two new members is taken once (by the larger index)
+  for (int p = 0; p < m; p++) {
+    if (!((mask >> p) & 1)) continue;
+    for (int o = 0; o < m; o++) {
+      if (o < p && ((mask >> o) & 1)) continue;
+      const int i = max(p, o), j = min(p, o);
+      const int rbi = sched[2 + i], rbj = sched[2 + j];
+      double (*Tt)[kSkyStride] = sky_tile(sm, sm.lane[rbi], sm.lane[rbj]);
+      if (!((sm.adj[rbi][rbj >> 5] >> (rbj & 31)) & 1)) {
+        // a tile inside the envelope that is structurally zero in the assembled matrix (it only receives fill): no copy
+        for (int piece = t0; piece < 512; piece += nthr)
+          *reinterpret_cast<double2*>(&Tt[piece >> 4][(piece & 15) * 2]) = make_double2(0.0, 0.0);
+      } else if (kBlk * rbj + kBlk <= n) {
+        const int rows = min(kBlk, n - kBlk * rbi);
+        bytes += rows * (unsigned)(kBlk * sizeof(double));
+        // this thread's row of this tile, if any: pair index q + r with (q + r) % nthr == t0
+        int r = (t0 - q % nthr + nthr) % nthr;
+        for (; r < kBlk; r += nthr) {
+          if (r < rows) {
+            bulk_g2s(&Tt[r][0], A.sys + (size_t)(kBlk * rbi + r) * ld + kBlk * rbj, kBlk * sizeof(double), &sm.mbar);
+          } else {
+  #pragma unroll
+            for (int c = 0; c < kBlk; c += 2) *reinterpret_cast<double2*>(&Tt[r][c]) = make_double2(0.0, 0.0);
+          }
+        }
+        q += kBlk;
+      } else {
+        for (int piece = t0; piece < 512; piece += nthr) {  // 512 16-byte pieces
+          const int r = piece >> 4, c2 = (piece & 15) * 2;
+          const int row = kBlk * rbi + r, col = kBlk * rbj + c2;
+          int cnt = (row < n) ? n - col : 0;
+          cnt = cnt < 0 ? 0 : (cnt > 2 ? 2 : cnt);
+          const double* src = cnt > 0 ? A.sys + (size_t)row * ld + col : A.sys;
+          cp_async16_zfill(&Tt[r][c2], src, 8 * cnt);
+        }
+      }
     }
   }
+  if (t0 == 0) mbar_arrive_expect_tx(&sm.mbar, bytes);
+  asm volatile("cp.async.commit_group;" ::: "memory");
+}
+
+// all threads: the tiles of the pending join have landed (then a CTA barrier makes them visible to everybody)
+__device__ __forceinline__ void sky_join_wait(const FusedArgs& A, SkySmem& sm, unsigned& parity) {
+  asm volatile("cp.async.wait_group 0;" ::: "memory");
+  int spins = 0;
+  while (!mbar_try_wait(&sm.mbar, parity)) {
+    if (++spins > (1 << 24)) {  // never in a correct run: report a failed factorisation instead of hanging the device
+      A.state[kFailNow] = 1;
+      break;
+    }
+  }
+  parity ^= 1u;
+  __syncthreads();
 }
 
 __device__ __forceinline__ void sky_factor(const FusedArgs& A, SkySmem& sm, double* s_y) {
@@ -867,12 +946,16 @@ __device__ __forceinline__ void sky_factor(const FusedArgs& A, SkySmem& sm, doub
   for (int i = tid; i < nblk; i += kFusedThreads) sm.lane[i] = __ldcg(A.sky + SkyPlan::lane(A.n_free) + i);
   for (int i = tid; i < nblk * kSkySched; i += kFusedThreads)
     sm.sched[i / kSkySched][i % kSkySched] = __ldcg(A.sky + SkyPlan::sched(A.n_free) + i);
+  for (int i = tid; i < nblk * 4; i += kFusedThreads) sm.adj[i >> 2][i & 3] = __ldcg(A.sky + SkyPlan::adj(A.n_free) + i);
   for (int c = tid; c < nblk * kBlk; c += kFusedThreads) s_y[c] = (c < n) ? __ldcg(A.sys + (size_t)n * ld + c) : 0.0;
-  bool looked = false;  // the diagonal tile of this step was factored during the previous step (uniform over the CTA)
+  if (tid == 0) mbar_init(&sm.mbar, 1);
+  asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+  unsigned jparity = 0;  // phase of sm.mbar the next join completes (uniform over the CTA)
+  bool looked = false;   // the diagonal tile of this step was factored during the previous step (uniform over the CTA)
   for (int kb = 0; kb < nblk; kb++) {
     const int c0 = kb * kBlk;
     const int nb = min(kBlk, n - c0);
-    asm volatile("cp.async.wait_group 0;" ::: "memory");  // tiles prefetched for this step
+    asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");  // my bulk stores of the last column have read their tiles
     __syncthreads();  // everybody is done with the previous step (the tiles of its column); first step: plan loaded
 #define SKY_MARK(t) if (kb == 20 || kb == 21) tl_mark(A, (t))
     SKY_MARK(7000);
@@ -882,12 +965,8 @@ __device__ __forceinline__ void sky_factor(const FusedArgs& A, SkySmem& sm, doub
     // ---- join: tiles (act[i], act[j]), j <= i, with a new member on either side, from the assembled system; when the
     //      plan says that the lanes of the NEXT step's new members are idle during this step, their tiles are fetched now
     if (mask & 0xff) {
-      if (!(mask & kSkyPrefetched)) {
-        sky_join(A, sm, kb, tid, kFusedThreads);
-        asm volatile("cp.async.commit_group;" ::: "memory");
-        asm volatile("cp.async.wait_group 0;" ::: "memory");
-        __syncthreads();
-      }
+      if (!(mask & kSkyPrefetched)) sky_join(A, sm, kb, tid, kFusedThreads);
+      sky_join_wait(A, sm, jparity);
     }
     SKY_MARK(7001);
     double (*Tkk)[kSkyStride] = sky_tile(sm, al0, al0);
@@ -905,10 +984,14 @@ __device__ __forceinline__ void sky_factor(const FusedArgs& A, SkySmem& sm, doub
     } else if (tid == (m - 1) * 32) {
       trsm_row32(s_y + c0, sm.d, nb);
     }
+    // the bulk stores of this column (async proxy) read what was just written: writer-side proxy fence, then a CTA barrier,
+    // then the stores.  With the look-ahead the fence waits until after the diagonal update (0.4 us on the critical path
+    // right here, nothing there: the writes have long drained)
+    const bool ahead = m >= 2 && sched[3] == kb + 1;
+    if (!ahead) asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
     __syncthreads();
     SKY_MARK(7003);
     // ---- update of the next diagonal tile first (look-ahead): thread = (4 rows, 1 column)
-    const bool ahead = m >= 2 && sched[3] == kb + 1;
     const int al1 = sm.lane[min(kb + 1, nblk - 1)];
     if (ahead) {
       const double (*X1)[kSkyStride] = sky_tile(sm, al1, al0);
@@ -929,6 +1012,7 @@ __device__ __forceinline__ void sky_factor(const FusedArgs& A, SkySmem& sm, doub
 #pragma unroll
         for (int i = 0; i < 4; i++) C11[r0 + i][lane] -= s[i] + u[i];
       }
+      asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
       __syncthreads();
     }
     SKY_MARK(7004);
@@ -949,14 +1033,11 @@ __device__ __forceinline__ void sky_factor(const FusedArgs& A, SkySmem& sm, doub
           out[l] = (r < nb && c <= r) ? Tkk[r][c] : (r == c ? 1.0 : 0.0);
         }
       }
-      if (kb == 20 && tid == 32) tl_mark_any(A, 7101);
+      if (kb == 20 && tid == 224) tl_mark_any(A, 7101);
       for (int j = 1 + worker; j < m; j += nworkers) sky_rhs_and_store(A, sm, s_y, sched[2 + j], al0, c0, nb, lane);
-      if (kb == 20 && tid == 32) tl_mark_any(A, 7102);
-      if (kb + 1 < nblk && (sm.sched[kb + 1][1] & kSkyPrefetched)) {
-        sky_join(A, sm, kb + 1, worker * 32 + lane, nworkers * 32);
-        asm volatile("cp.async.commit_group;" ::: "memory");
-      }
-      if (kb == 20 && tid == 32) tl_mark_any(A, 7103);
+      if (kb == 20 && tid == 224) tl_mark_any(A, 7102);
+      if (kb + 1 < nblk && (sm.sched[kb + 1][1] & kSkyPrefetched)) sky_join(A, sm, kb + 1, worker * 32 + lane, nworkers * 32);
+      if (kb == 20 && tid == 224) tl_mark_any(A, 7103);
       // trailing tiles (act[i], act[j]) -= X_i X_j^T, 1 <= j <= i < m, two 16-row halves each; (1, 1) is done above
       const int pairs = m * (m - 1) / 2, skip = ahead ? 1 : 0;
       for (int item = worker; item < 2 * (pairs - skip); item += nworkers) {
@@ -964,11 +1045,12 @@ __device__ __forceinline__ void sky_factor(const FusedArgs& A, SkySmem& sm, doub
         tile_decode((item >> 1) + skip, ti, tj);
         const int ali = sm.lane[sched[3 + ti]], alj = sm.lane[sched[3 + tj]];
         sky_update_item(sky_tile(sm, ali, al0), sky_tile(sm, alj, al0), sky_tile(sm, ali, alj), item & 1, lane);
-        if (kb == 20 && tid == 32) tl_mark_any(A, 7110 + item);
+        if (kb == 20 && tid == 224) tl_mark_any(A, 7110 + item);
       }
     }
     looked = ahead;
   }
+  asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");  // every column of L has reached global memory
   __syncthreads();
 }
 

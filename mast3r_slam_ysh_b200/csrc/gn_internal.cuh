@@ -37,7 +37,9 @@ struct SkyPlan {                     // int offsets inside the `sky` workspace r
   static __host__ __device__ int fb(int n_free) { return n_free; }                 // [kSkyMaxBlk]
   static __host__ __device__ int lane(int n_free) { return n_free + kSkyMaxBlk; }  // [kSkyMaxBlk]
   static __host__ __device__ int sched(int n_free) { return n_free + 2 * kSkyMaxBlk; }  // [kSkyMaxBlk][kSkySched]
-  static __host__ __device__ int total(int n_free) { return n_free + (2 + kSkySched) * kSkyMaxBlk + 8; }
+  static __host__ __device__ int adj(int n_free) { return n_free + (2 + kSkySched) * kSkyMaxBlk; }  // [kSkyMaxBlk][4] bit cb of row rb:
+                                                                     // tile (rb, cb), cb <= rb, has a structural non-zero
+  static __host__ __device__ int total(int n_free) { return n_free + (6 + kSkySched) * kSkyMaxBlk + 8; }
 };
 
 // phases of the fused solver kernel (gn_fused.cu)

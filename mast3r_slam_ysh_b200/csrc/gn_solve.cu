@@ -157,6 +157,7 @@ __global__ void __launch_bounds__(kPrepThreads) index_prep_kernel(const int64_t*
   int* s_je = s_ie + num_edges;                                           // [num_edges]
   int* s_deg = s_je + num_edges;                                          // [num_kf + 1]
   int* s_first = s_deg + num_kf + 1;                                      // [num_kf + 1]
+  int* s_adj = s_first + num_kf + 1;                                      // [4 * nblk] tile adjacency bits (SkyPlan::adj)
   __shared__ int s_warp[kPrepThreads / 32];
   __shared__ int s_nuniq, s_bad;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -243,8 +244,23 @@ __global__ void __launch_bounds__(kPrepThreads) index_prep_kernel(const int64_t*
   // envelope of the assembled system over ALL ranks' edges (the all-reduced [H | b] has the pattern of the whole graph):
   // first[a] = smallest free pose adjacent to free pose a, or a itself; consumed by skyline_plan_kernel
   const int n_free_env = num_kf > 0 ? num_kf - 1 : 0;
+  const int nblk_env = (kPoseDim * n_free_env + kBlk - 1) / kBlk;
+  const bool adj_on = nblk_env <= kSkyMaxBlk;
   for (int a = tid; a < n_free_env; a += kPrepThreads) s_first[a] = a;
+  if (adj_on)
+    for (int i = tid; i < 4 * nblk_env; i += kPrepThreads) s_adj[i] = 0;
   __syncthreads();
+  auto mark_tile = [&](int ra, int rc) {
+    const int hi = max(ra, rc), lo = min(ra, rc);
+    atomicOr(&s_adj[4 * hi + (lo >> 5)], 1 << (lo & 31));
+  };
+  if (adj_on)
+    for (int a = tid; a < n_free_env; a += kPrepThreads) {  // a pose's own 7 x 7 block (may straddle two row blocks)
+      const int r0 = (kPoseDim * a) / kBlk, r1 = (kPoseDim * a + kPoseDim - 1) / kBlk;
+      mark_tile(r0, r0);
+      mark_tile(r1, r0);
+      mark_tile(r1, r1);
+    }
   for (int k = tid; k < num_all; k += kPrepThreads) {
     int r[2];
 #pragma unroll
@@ -259,10 +275,22 @@ __global__ void __launch_bounds__(kPrepThreads) index_prep_kernel(const int64_t*
     }
     if (r[0] >= num_kf || r[1] >= num_kf) continue;
     const int a = max(r[0], r[1]) - 1, o = min(r[0], r[1]) - 1;
-    if (o >= 0) atomicMin(&s_first[a], o);
+    if (o >= 0) {
+      atomicMin(&s_first[a], o);
+      if (adj_on) {
+        const int a0 = (kPoseDim * a) / kBlk, a1 = (kPoseDim * a + kPoseDim - 1) / kBlk;
+        const int o0 = (kPoseDim * o) / kBlk, o1 = (kPoseDim * o + kPoseDim - 1) / kBlk;
+        mark_tile(a0, o0);
+        mark_tile(a0, o1);
+        mark_tile(a1, o0);
+        mark_tile(a1, o1);
+      }
+    }
   }
   __syncthreads();
   for (int a = tid; a < n_free_env; a += kPrepThreads) sky_first[a] = s_first[a];
+  if (adj_on)
+    for (int i = tid; i < 4 * nblk_env; i += kPrepThreads) sky_first[SkyPlan::adj(n_free_env) + i] = s_adj[i];
   if (tid == 0) state[kBadEdges] = s_bad;
   // incidence lists (see incidence_kernel): degrees with shared-memory atomics over all edge ends, offsets by one
   // thread, then one WARP per free keyframe walks the edges 32 at a time and places its entries with ballots, in the
@@ -431,7 +459,8 @@ int launch_index_prep(const GnWs& ws, const int64_t* local_ii, const int64_t* lo
   if (count <= kPrepMaxCount) {
     int padded = 2;
     while (padded < count) padded <<= 1;
-    const size_t smem = sizeof(long long) * (size_t)padded + sizeof(int) * (size_t)(2 * E + 2 * ws.L.num_kf + 4);
+    const size_t smem = sizeof(long long) * (size_t)padded +
+                        sizeof(int) * (size_t)(2 * E + 2 * ws.L.num_kf + 4 + 4 * (ws.L.nblk <= kSkyMaxBlk ? ws.L.nblk : 0));
     if (smem <= 200 * 1024) {
       static size_t attr = 0;
       if (smem > 48 * 1024 && smem > attr) {
