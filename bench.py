@@ -354,6 +354,11 @@ def run_ours(args):
         extra["hessian_kernel_ms"] = hess_ms
         extra["solve_other_ms_per_iter"] = value - hess_ms
         extra["iterations_executed"] = iters
+        lanes = (int(info_keep["info"].cpu()[3]) >> 24) & 15
+        n_sys = 7 * (nkf - 1)
+        extra["linear_solver"] = ("single-CTA shared-memory Cholesky (n = %d)" % n_sys if n_sys <= 224 else
+                                  "single-CTA envelope Cholesky, %d lanes (n = %d)" % (lanes, n_sys) if lanes > 0 else
+                                  "dense multi-CTA Cholesky (n = %d)" % n_sys)
         cpu_base = cpu_gn_sample(device=dev)[0] if world == 1 else None
         line = dict(metric="gn_solve_ms_per_iter", value=value, unit="ms/iter", n_gpus=world, steps=args.steps,
                     warmup=args.warmup, ms_per_step=ms_per_step, higher_is_better=False, scaling="weak", vs_baseline=None,

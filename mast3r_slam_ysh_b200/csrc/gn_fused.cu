@@ -1026,21 +1026,28 @@ __device__ __forceinline__ void sky_factor(const FusedArgs& A, SkySmem& sm, doub
       // right-hand side and the finished column of L, the prefetch of the next step's tiles, then the trailing update
       const int worker = ahead ? warp - 1 : warp;
       const int nworkers = ahead ? kFusedThreads / 32 - 1 : kFusedThreads / 32;
-      {
+      const int pairs = m * (m - 1) / 2, skip = ahead ? 1 : 0;
+      const int nitems = 2 * (pairs - skip);
+      // the first nitems % nworkers warps get one update item more than the others; the others ("light" warps) take
+      // the remaining duties, so that no update warp outlasts the factoring warp (the 3-item warps also stored, solved
+      // the right-hand side and issued loads before: 8.3 us against 6.0 us for the factorisation; r1)
+      const int w0 = nitems % nworkers;
+      const int nlight = nworkers - w0;
+      if (worker >= w0) {
+        const int lw = worker - w0;
         double* out = A.lfac + (size_t)kb * kBlk * kBlk;
-        for (int l = worker * 32 + lane; l < kBlk * kBlk; l += nworkers * 32) {
+        for (int l = lw * 32 + lane; l < kBlk * kBlk; l += nlight * 32) {
           const int r = l >> 5, c = l & 31;
           out[l] = (r < nb && c <= r) ? Tkk[r][c] : (r == c ? 1.0 : 0.0);
         }
+        if (kb == 20 && tid == 224) tl_mark_any(A, 7101);
+        for (int j = 1 + lw; j < m; j += nlight) sky_rhs_and_store(A, sm, s_y, sched[2 + j], al0, c0, nb, lane);
+        if (kb == 20 && tid == 224) tl_mark_any(A, 7102);
+        if (kb + 1 < nblk && (sm.sched[kb + 1][1] & kSkyPrefetched)) sky_join(A, sm, kb + 1, lw * 32 + lane, nlight * 32);
+        if (kb == 20 && tid == 224) tl_mark_any(A, 7103);
       }
-      if (kb == 20 && tid == 224) tl_mark_any(A, 7101);
-      for (int j = 1 + worker; j < m; j += nworkers) sky_rhs_and_store(A, sm, s_y, sched[2 + j], al0, c0, nb, lane);
-      if (kb == 20 && tid == 224) tl_mark_any(A, 7102);
-      if (kb + 1 < nblk && (sm.sched[kb + 1][1] & kSkyPrefetched)) sky_join(A, sm, kb + 1, worker * 32 + lane, nworkers * 32);
-      if (kb == 20 && tid == 224) tl_mark_any(A, 7103);
       // trailing tiles (act[i], act[j]) -= X_i X_j^T, 1 <= j <= i < m, two 16-row halves each; (1, 1) is done above
-      const int pairs = m * (m - 1) / 2, skip = ahead ? 1 : 0;
-      for (int item = worker; item < 2 * (pairs - skip); item += nworkers) {
+      for (int item = worker; item < nitems; item += nworkers) {
         int ti, tj;
         tile_decode((item >> 1) + skip, ti, tj);
         const int ali = sm.lane[sched[3 + ti]], alj = sm.lane[sched[3 + tj]];
