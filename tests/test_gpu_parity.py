@@ -306,6 +306,12 @@ def _long_graph(kind, nkf):
     if kind == "chain2+loops":   # chain + two long-range loop closures: long rows in the middle of the band
         ii, jj = syn.ring_edges(nkf, 2, wrap=False)
         return ii + [nkf - 3, nkf // 2], jj + [2, 5]
+    if kind == "chain2":         # open chain, 2 neighbours (with 65 keyframes n = 448 = 14 full column blocks)
+        return syn.ring_edges(nkf, 2, wrap=False)
+    if kind == "zigzag":         # chain through 0, h, 1, h+1, 2, ...: the first row blocks are mutually uncoupled, so the next
+        h = nkf // 2             # diagonal block is NOT active in the early steps (the path without look-ahead, m >= 2)
+        order = [v for k in range(h) for v in (k, h + k)]
+        return order[:-1], order[1:]
     if kind == "closures":       # loop closures everywhere: envelope too wide, the dense solver has to run
         return syn.loop_closure_edges(nkf, n_loop=3, seed=1)
     raise KeyError(kind)
@@ -316,7 +322,8 @@ def _long_graph(kind, nkf):
     # long open chains with two neighbours are weakly constrained: the fp32 rounding of the Hessian blocks (ours and the
     # oracle's accumulate in different orders) is amplified by the conditioning for EITHER solver (the dense one alone
     # runs the last case), so the oracle bar is looser there; solver-vs-solver below stays at 1e-6
-    ("chain2+loops", 90, True, 2e-3), ("closures", 120, False, 2e-3)])
+    ("chain2+loops", 90, True, 2e-3), ("closures", 120, False, 2e-3), ("chain2", 65, True, 2e-3),
+    ("zigzag", 40, True, 2e-3)])
 def test_gn_envelope_solver_vs_dense_solver_and_oracle(be, orc, kind, nkf, expect_envelope, oracle_tol):
     """Systems with more than 224 unknowns: the single-CTA envelope Cholesky (row-block envelope of the keyframe graph
     resident in shared memory) must reproduce the dense multi-CTA Cholesky to rounding, be chosen exactly when at most
@@ -324,7 +331,8 @@ def test_gn_envelope_solver_vs_dense_solver_and_oracle(be, orc, kind, nkf, expec
     gn_kernels.cu:115-159).  n is not a multiple of 32 in any case, so the last column block is partial."""
     from mast3r_slam_ysh_b200 import synthetic as syn
     h, w = 24, 32
-    g = syn.make_gn_problem(nkf, h, w, _long_graph(kind, nkf), seed=21, yaw_step_deg=5.0)
+    # zigzag links keyframes half the sequence apart: a small yaw step keeps those views overlapping
+    g = syn.make_gn_problem(nkf, h, w, _long_graph(kind, nkf), seed=21, yaw_step_deg=1.0 if kind == "zigzag" else 5.0)
     args = [g[k] for k in ("Xs", "Cs", "ii", "jj", "idx_ii2jj", "valid_match", "Q")]
     P = (LO["sigma_ray"], LO["sigma_dist"], LO["C_conf"], LO["Q_conf"])
     T_o = g["Twc"].numpy().copy()
