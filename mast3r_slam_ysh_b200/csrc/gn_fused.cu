@@ -720,6 +720,15 @@ __device__ __forceinline__ void backsolve_phase(const FusedArgs& A, BackSmem& sm
     __syncthreads();  // L_kk landed for everyone; the previous block's y update is complete
     if (kb > 0) back_stage(A, sm, kb - 1);
     const double (*L)[kBlk + 2] = sm.L[kb & 1];
+    const int rows = min(kBlk, n - c0);
+    // envelope solver: a block row has few columns (one per thread or less, except the long rows), and they do not
+    // depend on x -- fetch this thread's first column now, so that its L2 round trip overlaps the triangular solve
+    const int cfirst = (SKY ? sm.fb[kb] * kBlk : 0) + tid;
+    double vp[kBlk];
+    if (SKY && cfirst < c0) {
+#pragma unroll
+      for (int r = 0; r < kBlk; r++) vp[r] = r < rows ? __ldcg(A.sys + (size_t)(c0 + r) * ld + cfirst) : 0.0;
+    }
     if (warp == 0) {
       double yv = s_y[c0 + lane];
       const double dinv = 1.0 / L[lane][lane];
@@ -738,9 +747,17 @@ __device__ __forceinline__ void backsolve_phase(const FusedArgs& A, BackSmem& sm
       for (int q = lane; q < 64; q += 32) sm.live[q] = (q < gb) ? __ldcg(A.pmask + (size_t)q * A.pstride + gb) : 0;
     }
     __syncthreads();
-    const int rows = min(kBlk, n - c0);
     // y[0:c0] -= L[c0:c0+rows, 0:c0]^T x : one column per thread, coalesced along the row
-    for (int c = (SKY ? sm.fb[kb] * kBlk : 0) + tid; c < c0; c += kFusedThreads) {
+    if (SKY && cfirst < c0) {
+      double a0 = 0.0, a1 = 0.0;
+#pragma unroll
+      for (int r = 0; r < kBlk; r += 2) {
+        a0 = fma(vp[r], sm.x[r], a0);
+        a1 = fma(vp[r + 1], sm.x[r + 1], a1);
+      }
+      s_y[cfirst] -= a0 + a1;
+    }
+    for (int c = cfirst + (SKY ? kFusedThreads : 0); c < c0; c += kFusedThreads) {
       const int q = c / kPanW;
       if (!SKY && q * kPanW + kPanW <= c0 && !sm.live[q & 63]) continue;  // zero panel (the diagonal group is never skipped)
       double v[kBlk];
