@@ -39,6 +39,7 @@ struct FusedArgs {
   int* pmask;   // [panel][64-row group] non-zero flags of the factor (for the back substitution), stride pstride
   int pstride;
   const int* sky;  // envelope plan (SkyPlan), nullptr when the envelope solver cannot run (shared memory, debug switch)
+  int sy_off;      // gn_fused_kernel: byte offset of the solution vector behind the phase union in dynamic shared memory
   float* dx;
   int* state;
   int n, ld, nblk, num_kf, n_free, num_edges, hess_grid, phases;
@@ -1090,7 +1091,7 @@ union FusedSmem {
 __global__ void __launch_bounds__(kFusedThreads, 1) gn_fused_kernel(const FusedArgs A) {
   extern __shared__ __align__(16) unsigned char s_raw[];
   FusedSmem& sm = *reinterpret_cast<FusedSmem*>(s_raw);
-  double* s_y = reinterpret_cast<double*>(s_raw + sizeof(FusedSmem));
+  double* s_y = reinterpret_cast<double*>(s_raw + A.sy_off);
   // kDone is only written by the last phase of an earlier launch on the same stream: uniform over the grid
   if (__ldcg(A.state + kDone)) return;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -1233,6 +1234,7 @@ int launch_fused(const GnWs& ws, float* Twc, float delta_thresh, int phases, cud
   a.pmask = ws.pflag() + (ws.L.n / 64 + 4);
   a.pstride = ws.L.n / 64 + 4;
   a.sky = nullptr;
+  a.sy_off = 0;
   a.dx = ws.dx();
   a.state = ws.state();
   a.n = ws.L.n;
@@ -1275,8 +1277,17 @@ int launch_fused(const GnWs& ws, float* Twc, float delta_thresh, int phases, cud
     count_launch();
     return M3R_OK;
   }
-  const size_t smem = sizeof(FusedSmem) + sizeof(double) * (size_t)ws.L.nblk * kBlk;
+  // the envelope solver's tile store (183 KB) is only reserved when that solver can run; systems beyond its range keep
+  // the dense solver's footprint (101 KB + the solution vector)
   a.sky = (g_solver_mode != 1 && ws.L.nblk <= kSkyMaxBlk) ? ws.sky() : nullptr;
+  size_t phase_smem = sizeof(PanelSmem);
+  if (sizeof(UpdateSmem) > phase_smem) phase_smem = sizeof(UpdateSmem);
+  if (sizeof(BackSmem) > phase_smem) phase_smem = sizeof(BackSmem);
+  if (sizeof(FinalizeScratch) * (kFusedThreads / 32) > phase_smem) phase_smem = sizeof(FinalizeScratch) * (kFusedThreads / 32);
+  if (a.sky != nullptr) phase_smem = sizeof(FusedSmem);
+  phase_smem = (phase_smem + 15) & ~(size_t)15;
+  a.sy_off = (int)phase_smem;
+  const size_t smem = phase_smem + sizeof(double) * (size_t)ws.L.nblk * kBlk;
   if (smem > 227 * 1024) {
     set_error("gauss_newton: system of dimension %d exceeds the shared-memory back substitution", ws.L.n);
     return M3R_ERR_UNSUPPORTED;
