@@ -1042,7 +1042,9 @@ __device__ __forceinline__ void sky_factor(const FusedArgs& A, SkySmem& sm, doub
     } else {
       // workers: L_kk for the back substitution (zero upper part, identity padding) from the factored diagonal tile, the
       // right-hand side and the finished column of L, the prefetch of the next step's tiles, then the trailing update
-      const int worker = ahead ? warp - 1 : warp;
+      // with the look-ahead warp 4 is numbered last: it shares its scheduler with the factoring warp 0 and so gets the
+      // fewest update items
+      const int worker = ahead ? (warp < 4 ? warp - 1 : (warp == 4 ? kFusedThreads / 32 - 2 : warp - 2)) : warp;
       const int nworkers = ahead ? kFusedThreads / 32 - 1 : kFusedThreads / 32;
       const int pairs = m * (m - 1) / 2, skip = ahead ? 1 : 0;
       const int nitems = 2 * (pairs - skip);
