@@ -174,6 +174,12 @@ M3R_API int m3r_gn_edge_blocks(const m3r_gn_params* params, const float* Twc, co
 M3R_API int m3r_gn_hessian_pass(const m3r_gn_params* params, const float* Twc, int num_kf, int num_pts, int num_local_edges,
                         void* workspace, void* stream);
 
+/* Measurement hook: number of (pixel, directed edge) records that survived the pose-independent gates of the packing
+ * pre-pass of the solve that last used `workspace` (valid_match & q > Q_thresh & c_i, c_j > C_thresh, gn_kernels.cu:
+ * 953-957) -- the units the Hessian kernel streams per iteration (bench.py roofline).  Synchronises the device;
+ * negative on error. */
+M3R_API long long m3r_gn_record_count(const void* workspace, int num_kf, int num_pts, int num_local_edges);
+
 /* pose_retr_kernel (gn_kernels.cu:415-453): poses (num_poses,8) in place, dx (num_poses-num_fix,7) */
 M3R_API int m3r_pose_retr(float* poses, const float* dx, int num_poses, int num_fix, void* stream);
 

@@ -60,6 +60,7 @@ SYMBOLS = {
     "m3r_gn_hessian_pass": (_i, [_PP, _vp, _i, _i, _i, _vp, _vp]),
     "m3r_gn_system_ptr": (_vp, [_vp, _i, _i, _i]),
     "m3r_gn_system_count": (_sz, [_i]),
+    "m3r_gn_record_count": (_ll, [_vp, _i, _i, _i]),
     "m3r_gn_solve_retract": (_i, [_PP, _vp, _i, _i, _i, _vp, _vp]),
     "m3r_gn_end": (_i, [_i, _i, _i, _vp, _vp, _vp, _vp]),
     "m3r_gn_edge_blocks": (_i, [_PP, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _vp, _vp, _vp, _sz, _vp]),

@@ -22,14 +22,24 @@ void set_error(const char* fmt, ...) {
 }
 void count_launch(int n) { g_launches.fetch_add((uint64_t)n, std::memory_order_relaxed); }
 
+int current_device_slot() {
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0) dev = 0;
+  return dev < kMaxDevices ? dev : kMaxDevices - 1;
+}
+
 int sm_count() {
-  static int cached = 0;
-  if (cached == 0) {
-    int dev = 0, n = 148;
+  static std::atomic<int> cached[kMaxDevices];
+  const int d = current_device_slot();
+  int n = cached[d].load(std::memory_order_relaxed);
+  if (n == 0) {
+    int dev = 0;
+    n = 148;
     if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev);
-    cached = n > 0 ? n : 148;
+    if (n <= 0) n = 148;
+    cached[d].store(n, std::memory_order_relaxed);
   }
-  return cached;
+  return n;
 }
 
 int keep_async_pool() {
@@ -294,6 +304,17 @@ extern "C" double* m3r_gn_system_ptr(void* workspace, int num_kf, int num_pts, i
 extern "C" size_t m3r_gn_system_count(int num_kf) {
   GnLayout L = gn_layout(num_kf, 0, 0, 0);
   return (size_t)L.ld * (size_t)(L.n + 1);
+}
+
+extern "C" long long m3r_gn_record_count(const void* workspace, int num_kf, int num_pts, int num_local_edges) {
+  if (!workspace) return -1;
+  GnLayout L = gn_layout(num_kf, num_pts, num_local_edges, max_all_edges(num_local_edges));
+  long long v = 0;
+  if (cudaDeviceSynchronize() != cudaSuccess) return -1;
+  if (cudaMemcpy(&v, (const char*)workspace + L.off_eoff + sizeof(long long) * (size_t)num_local_edges, sizeof(long long),
+                 cudaMemcpyDeviceToHost) != cudaSuccess)
+    return -1;
+  return v;
 }
 
 extern "C" int m3r_gn_solve_retract(const m3r_gn_params* params, float* Twc, int num_kf, int num_pts,

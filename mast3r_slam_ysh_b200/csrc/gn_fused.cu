@@ -217,6 +217,21 @@ __device__ __forceinline__ void peer_allreduce_phase(const FusedArgs& A, int sky
   grid_peer_barrier(A, 2 * P.epoch + 2);
 }
 
+// A peer never arrived: this rank holds a PARTIAL sum.  Nothing may be factored or retracted from it -- the solve stops
+// here (kDone, dx = 0, poses untouched) and m3r_gn_end reports bit 30 of info[3], which the host side turns into an
+// error.  The flag is written before the barrier releases, so every CTA of the launch reads the same value.
+__device__ __forceinline__ bool peer_timed_out(const FusedArgs& A) {
+  if (__ldcg(A.state + kPeerTimeout) == 0) return false;
+  if (blockIdx.x == 0) {
+    for (int i = threadIdx.x; i < A.n; i += blockDim.x) A.dx[i] = 0.0f;
+    if (threadIdx.x == 0) {
+      A.state[kFailCount] += 1;
+      A.state[kDone] = 1;
+    }
+  }
+  return true;
+}
+
 // 16-byte global -> shared copy through L2; bytes beyond src_bytes (0..16) are zero-filled
 __device__ __forceinline__ void cp_async16_zfill(void* smem, const void* gmem, int src_bytes) {
   const unsigned sa = (unsigned)__cvta_generic_to_shared(smem);
@@ -1117,6 +1132,7 @@ __global__ void __launch_bounds__(kFusedThreads, 1) gn_fused_kernel(const FusedA
   }
   if (A.peer.world > 1) {
     peer_allreduce_phase<kFusedThreads>(A, sky);  // its barriers also order assembly -> factorisation
+    if (peer_timed_out(A)) return;
   } else if ((A.phases & M3R_PH_FACTOR) && (A.phases & M3R_PH_ASSEMBLE)) {
     grid_barrier(A.state, gridDim.x);
   }
@@ -1181,6 +1197,7 @@ __global__ void __launch_bounds__(kSmallThreads, 1) gn_small_kernel(const FusedA
   }
   if (A.peer.world > 1) {
     peer_allreduce_phase<kSmallThreads>(A, 0);  // its barriers also order assembly -> factorisation
+    if (peer_timed_out(A)) return;
   } else if ((A.phases & M3R_PH_FACTOR) && (A.phases & M3R_PH_ASSEMBLE)) {
     grid_barrier(A.state, gridDim.x);
   }
@@ -1256,10 +1273,10 @@ int launch_fused(const GnWs& ws, float* Twc, float delta_thresh, int phases, cud
     size_t smem = small_smem_bytes(ws.L.n) + 2 * sizeof(double) * (size_t)ws.L.nblk * kBlk;
     const size_t fin = sizeof(FinalizeScratch) * (kSmallThreads / 32);
     if (smem < fin) smem = fin;
-    static size_t attr_small = 0;
-    if (smem > 48 * 1024 && smem > attr_small) {
-      M3R_CUDA(cudaFuncSetAttribute(gn_small_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-      attr_small = smem;
+    static DynSmemOptIn attr_small;
+    {
+      const int rc = ensure_dyn_smem(gn_small_kernel, smem, attr_small);
+      if (rc != M3R_OK) return rc;
     }
     int grid = 1;
     if (phases & (M3R_PH_FINALIZE | M3R_PH_ASSEMBLE)) {
@@ -1294,10 +1311,10 @@ int launch_fused(const GnWs& ws, float* Twc, float delta_thresh, int phases, cud
     set_error("gauss_newton: system of dimension %d exceeds the shared-memory back substitution", ws.L.n);
     return M3R_ERR_UNSUPPORTED;
   }
-  static size_t attr_smem = 0;
-  if (smem > 48 * 1024 && smem > attr_smem) {
-    M3R_CUDA(cudaFuncSetAttribute(gn_fused_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    attr_smem = smem;
+  static DynSmemOptIn attr_smem;
+  {
+    const int rc = ensure_dyn_smem(gn_fused_kernel, smem, attr_smem);
+    if (rc != M3R_OK) return rc;
   }
   M3R_CUDA(cudaLaunchCooperativeKernel((const void*)gn_fused_kernel, dim3((unsigned)fused_grid(ws)),
                                        dim3(kFusedThreads), args, smem, st));

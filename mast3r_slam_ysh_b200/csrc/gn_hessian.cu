@@ -9,8 +9,10 @@
 //     g_j = v, g_i = -v.
 //   * Pose-independent work is hoisted into a packing pre-pass that runs once per solve: points and confidences
 //     become one float4 record (one LDG.128 per gather), and idx/valid/Q/C-gates become one 8-byte edge record.
-//   * 2-D decomposition: grid = edges x pixel tiles (the reference runs one 256-thread block per edge), fp32
-//     warp-shuffle + shared-memory tree per tile, deterministic fp64 second stage across tiles (no atomics).
+//   * Persistent stream-K decomposition over the flat list of compacted records (the reference runs one 256-thread
+//     block per edge), two records per thread in packed f32x2 arithmetic, fp32 warp-shuffle + shared-memory tree per
+//     segment, deterministic fp64 second stage across segments (no atomics).
+#include "f32x2.cuh"
 #include "gn_finalize.cuh"
 
 namespace m3r {
@@ -26,7 +28,10 @@ __global__ void __launch_bounds__(256) pack_points_kernel(const float* __restric
   if (p < total) {
     const float c = __ldg(Cs + p);
     fail = !(c > C_thresh);  // NaN fails, as in the gate itself
-    xc[p] = make_float4(__ldg(Xs + 3 * p), __ldg(Xs + 3 * p + 1), __ldg(Xs + 3 * p + 2), c);
+    const float x = __ldg(Xs + 3 * p), y = __ldg(Xs + 3 * p + 1), z = __ldg(Xs + 3 * p + 2);
+    // .w = -1/|X|: the Hessian kernel gets r_i = X_i/|X_i| and |X_i| without a rsqrt chain per record and iteration
+    // (the confidence is only needed by the gates, which read Cs directly)
+    xc[p] = make_float4(x, y, z, -1.0f / sqrtf(fmaf(x, x, fmaf(y, y, z * z))));
   }
   if (__any_sync(0xffffffffu, fail) && (threadIdx.x & 31) == 0) atomicOr(cfail, 1);
 }
@@ -116,7 +121,7 @@ __global__ void __launch_bounds__(256) pack_edges_kernel(const float* __restrict
       }
 #pragma unroll
       for (int j = 0; j < 4; j++)
-        if (!pass[j] || ind[j] >= num_pts) ind[j] = -1;
+        if (!pass[j] || ind[j] < 0 || ind[j] >= num_pts) ind[j] = -1;  // corrupt indices never reach the gather
     }
     int4 id;
     if (cgate) {
@@ -227,36 +232,43 @@ __global__ void __launch_bounds__(1024) edge_offsets_kernel(const int* __restric
 }
 
 // ------------------------------------------------------------------------------------------------ robust weights
+// All per-record arithmetic below runs on PAIRS of records (V2, f32x2.cuh): one thread carries record A in the low and
+// record B in the high half of every register pair, so each FADD2/FMUL2/FFMA2 serves two records.
+//
+// Huber (gn_kernels.cu:172-175): w = |r| < k ? 1 : k/|r|  ==  min(1, k * rcp(|r|)), branch-free; r = 0 gives
+// min(1, inf) = 1.  The reference compares against the double literal 1.345 and divides in double; rcp.approx is within
+// 1 ulp of that quotient and the two forms agree except within 1 ulp of the switch point, where both give w = 1 - O(ulp)
+// (documented deviation).  Tukey (nonlinear_optimizer.py:36-42): (1 - (r/t)^2)^2 inside |r| < t, else 0
+// == max(1 - (r/t)^2, 0)^2.
 template <int ROBUST>
-__device__ __forceinline__ float robust_weight(float r) {
-  const float a = fabsf(r);
-  if (ROBUST == M3R_ROBUST_HUBER) {  // gn_kernels.cu:172-175
-    return a < 1.345f ? 1.0f : __fdividef(1.345f, a);
-  } else {  // Tukey biweight, nonlinear_optimizer.py:36-42
-    const float t = a * (1.0f / 4.6851f);
-    const float m = 1.0f - t * t;
-    return a < 4.6851f ? m * m : 0.0f;
+__device__ __forceinline__ V2 robust_weight2(V2 r) {
+  if (ROBUST == M3R_ROBUST_HUBER) {
+    return min2(mul2(rcp_abs2(r), bc(1.345f)), 1.0f);
+  } else {
+    const V2 t = mul2(r, bc(1.0f / 4.6851f));
+    const V2 m = max2(fma2(mul2(t, bc(-1.0f)), t, bc(1.0f)), 0.0f);
+    return mul2(m, m);
   }
 }
 
 // acc[0..27]: lower triangle of S (row a, col b<=a at a(a+1)/2+b); acc[28..34]: g.
 // MASK: bit a set <=> J[a] may be non-zero for this residual row (compile-time sparsity of the local Jacobian).
 template <int MASK>
-__device__ __forceinline__ void accum_row(float (&acc)[kAcc], const float (&J)[7], float w, float e) {
-  float wJ[7];
+__device__ __forceinline__ void accum_row(V2 (&acc)[kAcc], const V2 (&J)[7], V2 w, V2 e) {
+  V2 wJ[7];
 #pragma unroll
   for (int a = 0; a < 7; a++)
-    if ((MASK >> a) & 1) wJ[a] = w * J[a];
-  const float we = w * e;
+    if ((MASK >> a) & 1) wJ[a] = mul2(w, J[a]);
+  const V2 we = mul2(w, e);
 #pragma unroll
   for (int a = 0; a < 7; a++) {
     if (!((MASK >> a) & 1)) continue;
 #pragma unroll
     for (int b = 0; b <= a; b++) {
       if (!((MASK >> b) & 1)) continue;
-      acc[a * (a + 1) / 2 + b] = fmaf(wJ[a], J[b], acc[a * (a + 1) / 2 + b]);
+      fma2_acc(acc[a * (a + 1) / 2 + b], wJ[a], J[b]);
     }
-    acc[28 + a] = fmaf(we, J[a], acc[28 + a]);
+    fma2_acc(acc[28 + a], we, J[a]);
   }
 }
 
@@ -321,98 +333,116 @@ struct PixParams {
   float z_eps;
 };
 
-// One pixel of one edge: residuals, weights, local Jacobian rows, accumulation.
+__device__ __forceinline__ float act_row(const float* R, float t, const float4& x) {
+  return fmaf(R[0], x.x, fmaf(R[1], x.y, fmaf(R[2], x.z, t)));
+}
+
+// Two records of one edge: residuals, weights, local Jacobian rows, accumulation.  Record B may be a padding lane
+// (sq.hi == 0, inputs copied from A): every weight is then exactly zero and every term finite.
+// xi.w = -1/|X_i| (pack_points_kernel): r_i and |X_i| cost no rsqrt chain here.
 template <int KIND, int ROBUST>
-__device__ __forceinline__ void pixel_accumulate(float (&acc)[kAcc], const EdgeConst& c, const PixParams& pp,
-                                                 const float4 xi, const float4 xj, int ind, float sq) {
-  const float Px = fmaf(c.R[0], xj.x, fmaf(c.R[1], xj.y, fmaf(c.R[2], xj.z, c.t[0])));
-  const float Py = fmaf(c.R[3], xj.x, fmaf(c.R[4], xj.y, fmaf(c.R[5], xj.z, c.t[1])));
-  const float Pz = fmaf(c.R[6], xj.x, fmaf(c.R[7], xj.y, fmaf(c.R[8], xj.z, c.t[2])));
-  float J[7];
+__device__ __forceinline__ void pair_accumulate(V2 (&acc)[kAcc], const EdgeConst& c, const PixParams& pp,
+                                                const float4 xiA, const float4 xiB, const float4 xjA,
+                                                const float4 xjB, int indA, int indB, V2 sq) {
+  // P = s_ij R_ij X_j + t_ij: the edge constants are scalars, one FFMA per record and term
+  const V2 Px = pk(act_row(c.R + 0, c.t[0], xjA), act_row(c.R + 0, c.t[0], xjB));
+  const V2 Py = pk(act_row(c.R + 3, c.t[1], xjA), act_row(c.R + 3, c.t[1], xjB));
+  V2 Pz = pk(act_row(c.R + 6, c.t[2], xjA), act_row(c.R + 6, c.t[2], xjB));
+  V2 J[7];
   if (KIND == M3R_GN_RAYS) {
-    const float n2j = fmaf(Px, Px, fmaf(Py, Py, Pz * Pz));
-    const float invj = rsqrtf(n2j);
-    const float n1j = n2j * invj;
-    const float rx = Px * invj, ry = Py * invj, rz = Pz * invj;
-    const float n2i = fmaf(xi.x, xi.x, fmaf(xi.y, xi.y, xi.z * xi.z));
-    const float invi = rsqrtf(n2i);
-    const float n1i = n2i * invi;
-    const float e0 = rx - xi.x * invi, e1 = ry - xi.y * invi, e2 = rz - xi.z * invi, e3 = n1j - n1i;
-    const float sw_ray = pp.sa_inv * sq, sw_dist = pp.sb_inv * sq;
-    const float wc_ray = sw_ray * sw_ray, wc_dist = sw_dist * sw_dist;
-    const float w0 = robust_weight<ROBUST>(sw_ray * e0) * wc_ray;
-    const float w1 = robust_weight<ROBUST>(sw_ray * e1) * wc_ray;
-    const float w2 = robust_weight<ROBUST>(sw_ray * e2) * wc_ray;
-    const float w3 = robust_weight<ROBUST>(sw_dist * e3) * wc_dist;
-    // d r / d P = (I - r r^T) / |P|   (gn_kernels.cu:982-988)
-    const float dxx = invj * (1.0f - rx * rx), dyy = invj * (1.0f - ry * ry), dzz = invj * (1.0f - rz * rz);
-    const float dxy = -invj * rx * ry, dxz = -invj * rx * rz, dyz = -invj * ry * rz;
-    J[0] = dxx; J[1] = dxy; J[2] = dxz; J[3] = 0.0f; J[4] = rz; J[5] = -ry; J[6] = 0.0f;
+    const V2 n2j = fma2(Px, Px, fma2(Py, Py, mul2(Pz, Pz)));
+    const V2 invj = rsqrt2(n2j);
+    const V2 n1j = mul2(n2j, invj);
+    const V2 rx = mul2(Px, invj), ry = mul2(Py, invj), rz = mul2(Pz, invj);
+    const V2 wi = pk(xiA.w, xiB.w);  // -1/|X_i|
+    const V2 e0 = fma2(pk(xiA.x, xiB.x), wi, rx), e1 = fma2(pk(xiA.y, xiB.y), wi, ry),
+             e2 = fma2(pk(xiA.z, xiB.z), wi, rz);
+    const V2 e3 = add2(n1j, rcp2(wi));  // |P| - |X_i|
+    const V2 sw_ray = mul2(sq, bc(pp.sa_inv)), sw_dist = mul2(sq, bc(pp.sb_inv));
+    const V2 wc_ray = mul2(sw_ray, sw_ray), wc_dist = mul2(sw_dist, sw_dist);
+    const V2 w0 = mul2(robust_weight2<ROBUST>(mul2(sw_ray, e0)), wc_ray);
+    const V2 w1 = mul2(robust_weight2<ROBUST>(mul2(sw_ray, e1)), wc_ray);
+    const V2 w2 = mul2(robust_weight2<ROBUST>(mul2(sw_ray, e2)), wc_ray);
+    const V2 w3 = mul2(robust_weight2<ROBUST>(mul2(sw_dist, e3)), wc_dist);
+    // d r / d P = (I - r r^T) / |P|   (gn_kernels.cu:982-988), with s = r/|P| and the negated ray n = -r
+    const V2 neg1 = bc(-1.0f);
+    const V2 nx = mul2(rx, neg1), ny = mul2(ry, neg1), nz = mul2(rz, neg1);
+    const V2 sx = mul2(rx, invj), sy = mul2(ry, invj), sz = mul2(rz, invj);
+    const V2 dxx = fma2(sx, nx, invj), dyy = fma2(sy, ny, invj), dzz = fma2(sz, nz, invj);
+    const V2 dxy = mul2(sx, ny), dxz = mul2(sx, nz), dyz = mul2(sy, nz);
+    J[0] = dxx; J[1] = dxy; J[2] = dxz; J[3] = dxx; J[4] = rz; J[5] = ny; J[6] = dxx;
     accum_row<0b0110111>(acc, J, w0, e0);
-    J[0] = dxy; J[1] = dyy; J[2] = dyz; J[3] = -rz; J[4] = 0.0f; J[5] = rx; J[6] = 0.0f;
+    J[0] = dxy; J[1] = dyy; J[2] = dyz; J[3] = nz; J[5] = rx;
     accum_row<0b0101111>(acc, J, w1, e1);
-    J[0] = dxz; J[1] = dyz; J[2] = dzz; J[3] = ry; J[4] = -rx; J[5] = 0.0f; J[6] = 0.0f;
+    J[0] = dxz; J[1] = dyz; J[2] = dzz; J[3] = ry; J[4] = nx;
     accum_row<0b0011111>(acc, J, w2, e2);
-    J[0] = rx; J[1] = ry; J[2] = rz; J[3] = 0.0f; J[4] = 0.0f; J[5] = 0.0f; J[6] = n1j;
+    J[0] = rx; J[1] = ry; J[2] = rz; J[6] = n1j;
     accum_row<0b1000111>(acc, J, w3, e3);
   } else if (KIND == M3R_GN_POINTS) {
-    const float e0 = Px - xi.x, e1 = Py - xi.y, e2 = Pz - xi.z;
-    const float sw = pp.sa_inv * sq;
-    const float wc = sw * sw;
-    const float w0 = robust_weight<ROBUST>(sw * e0) * wc;
-    const float w1 = robust_weight<ROBUST>(sw * e1) * wc;
-    const float w2 = robust_weight<ROBUST>(sw * e2) * wc;
-    J[0] = 1.0f; J[1] = 0.0f; J[2] = 0.0f; J[3] = 0.0f; J[4] = Pz; J[5] = -Py; J[6] = Px;
+    const V2 e0 = sub2(Px, pk(xiA.x, xiB.x)), e1 = sub2(Py, pk(xiA.y, xiB.y)), e2 = sub2(Pz, pk(xiA.z, xiB.z));
+    const V2 sw = mul2(sq, bc(pp.sa_inv));
+    const V2 wc = mul2(sw, sw);
+    const V2 w0 = mul2(robust_weight2<ROBUST>(mul2(sw, e0)), wc);
+    const V2 w1 = mul2(robust_weight2<ROBUST>(mul2(sw, e1)), wc);
+    const V2 w2 = mul2(robust_weight2<ROBUST>(mul2(sw, e2)), wc);
+    const V2 one = bc(1.0f), neg1 = bc(-1.0f);
+    const V2 nPx = mul2(Px, neg1), nPy = mul2(Py, neg1), nPz = mul2(Pz, neg1);
+    J[0] = one; J[1] = one; J[2] = one; J[3] = one; J[4] = Pz; J[5] = nPy; J[6] = Px;
     accum_row<0b1110001>(acc, J, w0, e0);
-    J[0] = 0.0f; J[1] = 1.0f; J[2] = 0.0f; J[3] = -Pz; J[4] = 0.0f; J[5] = Px; J[6] = Py;
+    J[3] = nPz; J[5] = Px; J[6] = Py;
     accum_row<0b1101010>(acc, J, w1, e1);
-    J[0] = 0.0f; J[1] = 0.0f; J[2] = 1.0f; J[3] = Py; J[4] = -Px; J[5] = 0.0f; J[6] = Pz;
+    J[3] = Py; J[4] = nPx; J[6] = Pz;
     accum_row<0b1011100>(acc, J, w2, e2);
   } else {  // M3R_GN_CALIB, gn_kernels.cu:1360-1479
-    const bool valid_z = (Pz > pp.z_eps) && (xi.z > pp.z_eps);
-    if (!valid_z) return;  // zero weight in the reference
-    const float zj_inv = 1.0f / Pz;
-    const float x = Px * zj_inv, y = Py * zj_inv;
-    const float u = fmaf(c.fx, x, c.cx), v = fmaf(c.fy, y, c.cy);
-    const bool valid_u = (u > (float)pp.pixel_border) && (u < (float)(pp.width - 1 - pp.pixel_border));
-    const bool valid_v = (v > (float)pp.pixel_border) && (v < (float)(pp.height - 1 - pp.pixel_border));
-    if (!(valid_u && valid_v)) return;
-    const int v_t = ind / pp.width;
-    const int u_t = ind - v_t * pp.width;
-    const float e0 = u - (float)u_t, e1 = v - (float)v_t, e2 = logf(Pz) - logf(xi.z);
-    const float sw_pix = pp.sa_inv * sq, sw_dep = pp.sb_inv * sq;
-    const float wc_pix = sw_pix * sw_pix, wc_dep = sw_dep * sw_dep;
-    const float w0 = robust_weight<ROBUST>(sw_pix * e0) * wc_pix;
-    const float w1 = robust_weight<ROBUST>(sw_pix * e1) * wc_pix;
-    const float w2 = robust_weight<ROBUST>(sw_dep * e2) * wc_dep;
-    J[0] = c.fx * zj_inv; J[1] = 0.0f; J[2] = -c.fx * x * zj_inv; J[3] = -c.fx * x * y;
-    J[4] = c.fx * (1.0f + x * x); J[5] = -c.fx * y; J[6] = 0.0f;
+    // per-record validity (z > eps on both sides, projection inside the bordered image): an invalid record keeps finite
+    // stand-in values and gets sq = 0, i.e. weight exactly zero as in the reference (:1399-1404)
+    const bool zA = lo(Pz) > pp.z_eps && xiA.z > pp.z_eps, zB = hi(Pz) > pp.z_eps && xiB.z > pp.z_eps;
+    Pz = pk(zA ? lo(Pz) : 1.0f, zB ? hi(Pz) : 1.0f);
+    const float ziA = zA ? xiA.z : 1.0f, ziB = zB ? xiB.z : 1.0f;
+    const V2 zj_inv = pk(1.0f / lo(Pz), 1.0f / hi(Pz));
+    const V2 x = mul2(Px, zj_inv), y = mul2(Py, zj_inv);
+    const V2 fx = bc(c.fx), fy = bc(c.fy);
+    const V2 u = fma2(fx, x, bc(c.cx)), v = fma2(fy, y, bc(c.cy));
+    const float ulo = (float)pp.pixel_border, uhi = (float)(pp.width - 1 - pp.pixel_border),
+                vhi = (float)(pp.height - 1 - pp.pixel_border);
+    const bool okA = zA && lo(u) > ulo && lo(u) < uhi && lo(v) > ulo && lo(v) < vhi;
+    const bool okB = zB && hi(u) > ulo && hi(u) < uhi && hi(v) > ulo && hi(v) < vhi;
+    sq = pk(okA ? lo(sq) : 0.0f, okB ? hi(sq) : 0.0f);
+    const int vtA = indA / pp.width, vtB = indB / pp.width;
+    const int utA = indA - vtA * pp.width, utB = indB - vtB * pp.width;
+    const V2 e0 = sub2(u, pk((float)utA, (float)utB)), e1 = sub2(v, pk((float)vtA, (float)vtB));
+    const V2 e2 = pk(logf(lo(Pz)) - logf(ziA), logf(hi(Pz)) - logf(ziB));
+    const V2 sw_pix = mul2(sq, bc(pp.sa_inv)), sw_dep = mul2(sq, bc(pp.sb_inv));
+    const V2 wc_pix = mul2(sw_pix, sw_pix), wc_dep = mul2(sw_dep, sw_dep);
+    const V2 w0 = mul2(robust_weight2<ROBUST>(mul2(sw_pix, e0)), wc_pix);
+    const V2 w1 = mul2(robust_weight2<ROBUST>(mul2(sw_pix, e1)), wc_pix);
+    const V2 w2 = mul2(robust_weight2<ROBUST>(mul2(sw_dep, e2)), wc_dep);
+    const V2 one = bc(1.0f), neg1 = bc(-1.0f);
+    const V2 fxz = mul2(fx, zj_inv), fyz = mul2(fy, zj_inv);
+    const V2 nx = mul2(x, neg1), ny = mul2(y, neg1);
+    J[0] = fxz; J[1] = one; J[2] = mul2(fxz, nx); J[3] = mul2(mul2(fx, nx), y); J[4] = mul2(fx, fma2(x, x, one));
+    J[5] = mul2(fx, ny); J[6] = one;
     accum_row<0b0111101>(acc, J, w0, e0);
-    J[0] = 0.0f; J[1] = c.fy * zj_inv; J[2] = -c.fy * y * zj_inv; J[3] = -c.fy * (1.0f + y * y);
-    J[4] = c.fy * x * y; J[5] = c.fy * x; J[6] = 0.0f;
+    J[1] = fyz; J[2] = mul2(fyz, ny); J[3] = mul2(fy, fma2(ny, y, neg1)); J[4] = mul2(mul2(fy, x), y);
+    J[5] = mul2(fy, x);
     accum_row<0b0111110>(acc, J, w1, e1);
-    J[0] = 0.0f; J[1] = 0.0f; J[2] = zj_inv; J[3] = y; J[4] = -x; J[5] = 0.0f; J[6] = 1.0f;
+    J[2] = zj_inv; J[3] = y; J[4] = nx; J[6] = one;
     accum_row<0b1011100>(acc, J, w2, e2);
   }
 }
 
 // ------------------------------------------------------------------------------------------------ Hessian kernel
-// Persistent, stream-K style: the V = sum_e ecount[e] compacted records of all edges form one flat list; CTA c of a
-// grid of 2 CTAs per SM owns the records [c*chunk, (c+1)*chunk), chunk = V/grid rounded up to 512.  A CTA walks the
-// (at most a few) edge segments inside its range; per segment it builds the edge constants once, streams the records
-// through a two-stage software pipeline (records two batches ahead, the gathered points one batch ahead of the
-// arithmetic), and reduces its 35 accumulators once: transposing butterfly across lanes (31 shuffles for 32 values),
-// shared memory across the 8 warps.  The partial sums of segment (e, c) go to slot e + c, which is unique because
-// consecutive segments advance e, c or both; finalize_edges_kernel sums an edge's slots in fixed order (no atomics).
+// Persistent, stream-K style: the V = sum_e ecount[e] compacted records of all edges form one flat list; CTA c of the
+// grid (kHessCtasPerSm CTAs per SM) owns the records [c*chunk, (c+1)*chunk).  A CTA walks the (at most a few) edge
+// segments inside its range; per segment it builds the edge constants once, streams the records through a software
+// pipeline (records two batches ahead in registers, the gathered points one batch ahead in a cp.async shared-memory
+// ring), and reduces its 35 accumulators once: transposing butterfly across lanes (31 shuffles for 32 values), shared
+// memory across the warps.  The partial sums of segment (e, c) go to slot e + c, which is unique because consecutive
+// segments advance e, c or both; finalize_edge sums an edge's slots in fixed order (no atomics).
 // History (profiles/): v1 one CTA per 2048-px tile, latency-bound at 25 % occupancy; v2 8192-px tiles + pipelined
-// loads; v3 (this) drops gated-out pixels in the pre-pass (40-50 % of the lanes idled in v2) and amortises the serial
-// edge set-up, pipeline prologue and block reduction over ~1e5 records per CTA instead of 8192 pixels.
-struct PixBatch {
-  float4 xj[2], xi[2];
-  int idx[2];
-  float sq[2];
-};
-
+// loads; v3 drops gated-out pixels in the pre-pass and amortises the serial edge set-up over ~1e5 records per CTA; v4
+// cp.async ring; v6 (this): two records per thread in packed f32x2 arithmetic, MUFU-only reciprocals, branch-free
+// Huber, pre-normalised X_i -- ~236 -> ~105 issue slots per record.
 struct RecBatch {
   int2 r[2];
   float sq[2];
@@ -432,25 +462,10 @@ __device__ __forceinline__ void load_recs(const EdgeRec* __restrict__ er, const 
   }
 }
 
-__device__ __forceinline__ void load_points(const float4* __restrict__ xci, const float4* __restrict__ xcj,
-                                            const RecBatch& rb, PixBatch& pb) {
-#pragma unroll
-  for (int u = 0; u < 2; u++) {
-    pb.idx[u] = rb.r[u].x;
-    pb.sq[u] = rb.sq[u];
-    if (rb.r[u].x >= 0) {
-      pb.xj[u] = __ldg(xcj + rb.r[u].y);
-      pb.xi[u] = __ldg(xci + rb.r[u].x);
-    }
-  }
-}
-
-// ---- v4 load path: the gathered points go global -> shared memory with cp.async (LDGSTS), kRingDepth batches ahead of
-// the arithmetic, into a ring of kRingSlots per-thread slots.  No registers are held by loads in flight, so the depth
-// is not limited by the register file as it was in v3 (points one batch ahead; ncu: 2.6 warps stalled on the long
-// scoreboard per issue at 3.7 warps per scheduler -> 0.74 with the ring, issue-active 59 % -> 67 %).  A thread only ever touches its own slots: no barrier in the loop.
-constexpr int kRingDepth = 1;               // batches in flight (r1, us at 32 kf: depth 1 99.4, 2 101.3, 3 103.0, 4 105.1)
-constexpr int kRingSlots = kRingDepth + 1;  // the slot being computed from is never a copy destination
+// The gathered points go global -> shared memory with cp.async (LDGSTS), one batch ahead of the arithmetic, into a
+// two-slot per-thread ring: no registers are held by loads in flight.  A thread only ever touches its own slots, so
+// there is no barrier in the loop.  (r1: ring depth 1 / 2 / 3 / 4 = 99.4 / 101.3 / 103.0 / 105.1 us at 32 kf.)
+constexpr int kRingSlots = 2;
 struct HessRing {
   float4 xi[kRingSlots][2][kHessThreads];
   float4 xj[kRingSlots][2][kHessThreads];
@@ -482,10 +497,6 @@ __device__ __forceinline__ void ring_issue(HessRing& ring, int slot, const float
   cp_async_commit();
 }
 
-// 2 CTAs x 256 threads per SM at ~120 registers.  Tried on B200 (r1, us at 32 kf / 256 kf; this shape 99.7 / 1307):
-// 2 x 320 threads 111 / 1394, 3 x 192 109 / 1432, 5 x 128 110 / 1442, 3 x 256 108 / 1405 (all spill or lose ILP to
-// the tighter register cap), 1 x 512 99.3 / 1299 (same occupancy).
-constexpr int kHessCtasPerSm = 2;
 template <int KIND, int ROBUST>
 __global__ void __launch_bounds__(kHessThreads, kHessCtasPerSm) hessian_kernel(const float* __restrict__ Twc,
                                                                   const float* __restrict__ K,
@@ -516,12 +527,12 @@ __global__ void __launch_bounds__(kHessThreads, kHessCtasPerSm) hessian_kernel(c
     if (threadIdx.x == 0) {
       int en;
       if (e < 0) {
-        int lo = 0, hi = num_edges - 1;  // last edge with eoff[edge] <= p
-        while (lo < hi) {
-          const int mid = (lo + hi + 1) >> 1;
-          if (eoff[mid] <= p) lo = mid; else hi = mid - 1;
+        int lo_e = 0, hi_e = num_edges - 1;  // last edge with eoff[edge] <= p
+        while (lo_e < hi_e) {
+          const int mid = (lo_e + hi_e + 1) >> 1;
+          if (eoff[mid] <= p) lo_e = mid; else hi_e = mid - 1;
         }
-        en = lo;
+        en = lo_e;
       } else {
         en = e + 1;
       }
@@ -540,51 +551,54 @@ __global__ void __launch_bounds__(kHessThreads, kHessCtasPerSm) hessian_kernel(c
     const EdgeRec* __restrict__ er = rec + (size_t)e * num_pts;
     const float* __restrict__ es = sqv + (size_t)e * num_pts;
 
-    float acc[kAcc];
+    V2 acc2[kAcc];
 #pragma unroll
-    for (int i = 0; i < kAcc; i++) acc[i] = 0.0f;
+    for (int i = 0; i < kAcc; i++) acc2[i] = bc(0.0f);
     {
       constexpr int kStep = 2 * kHessThreads;
       int kb = (int)(p - e0) + threadIdx.x;
-      // prologue: gathers of batches 0 .. kRingDepth-1 in flight, records of the next two batches in registers
-#pragma unroll
-      for (int d = 0; d < kRingDepth; d++) {
+      {  // prologue: gathers of batch 0 in flight, records of the next two batches in registers
         RecBatch r0;
-        load_recs(er, es, kb + d * kStep, k1, r0);
-        ring_issue(ring, d, xci, xcj, r0);
+        load_recs(er, es, kb, k1, r0);
+        ring_issue(ring, 0, xci, xcj, r0);
       }
       RecBatch ra, rb;
-      load_recs(er, es, kb + kRingDepth * kStep, k1, ra);
-      load_recs(er, es, kb + (kRingDepth + 1) * kStep, k1, rb);
+      load_recs(er, es, kb + kStep, k1, ra);
+      load_recs(er, es, kb + 2 * kStep, k1, rb);
       int slot = 0;
+#pragma unroll 2
       for (; kb < k1; kb += kStep) {
         RecBatch rc;
-        load_recs(er, es, kb + (kRingDepth + 2) * kStep, k1, rc);
-        cp_async_wait<kRingDepth - 1>();  // this batch has landed
-        float4 xi[2], xj[2];
-        float2 meta[2];
-#pragma unroll
-        for (int u = 0; u < 2; u++) {
-          meta[u] = ring.meta[slot][u][threadIdx.x];
-          xi[u] = ring.xi[slot][u][threadIdx.x];
-          xj[u] = ring.xj[slot][u][threadIdx.x];
+        load_recs(er, es, kb + 3 * kStep, k1, rc);
+        cp_async_wait<0>();  // this batch has landed
+        const float2 mA = ring.meta[slot][0][threadIdx.x], mB = ring.meta[slot][1][threadIdx.x];
+        const float4 xiA = ring.xi[slot][0][threadIdx.x], xjA = ring.xj[slot][0][threadIdx.x];
+        float4 xiB = ring.xi[slot][1][threadIdx.x], xjB = ring.xj[slot][1][threadIdx.x];
+        ring_issue(ring, slot ^ 1, xci, xcj, ra);
+        // kb < k1 inside the loop, so record A always exists; records are dense, so B = A + kHessThreads can only be
+        // missing at the end of the segment: it becomes a padding lane, a copy of A with weight zero (no branch around
+        // the arithmetic: the 70 accumulator registers would have to be merged behind it)
+        const int idxA = __float_as_int(mA.x);
+        int idxB = __float_as_int(mB.x);
+        float sqB = mB.y;
+        if (idxB < 0) {
+          xiB = xiA;
+          xjB = xjA;
+          idxB = idxA;
+          sqB = 0.0f;
         }
-        int nslot = slot + kRingDepth;
-        if (nslot >= kRingSlots) nslot -= kRingSlots;
-        ring_issue(ring, nslot, xci, xcj, ra);
-#pragma unroll
-        for (int u = 0; u < 2; u++) {
-          const int idx = __float_as_int(meta[u].x);
-          if (idx >= 0) pixel_accumulate<KIND, ROBUST>(acc, c, pp, xi[u], xj[u], idx, meta[u].y);
-        }
+        pair_accumulate<KIND, ROBUST>(acc2, c, pp, xiA, xiB, xjA, xjB, idxA, idxB, pk(mA.y, sqB));
         ra = rb;
         rb = rc;
-        slot = slot + 1 == kRingSlots ? 0 : slot + 1;
+        slot ^= 1;
       }
       cp_async_wait<0>();  // drain before the next segment reuses the ring
     }
+    float acc[kAcc];
+#pragma unroll
+    for (int i = 0; i < kAcc; i++) acc[i] = lo(acc2[i]) + hi(acc2[i]);
     // ---- block reduction: transposing butterfly for acc[0..31] (lane l ends up with the warp total of acc[l]),
-    //      plain xor-tree for the remaining kAcc-32 values, then 8 warps through shared memory
+    //      plain xor-tree for the remaining kAcc-32 values, then the warps through shared memory
 #pragma unroll
     for (int s = 16; s >= 1; s >>= 1) {
       const bool upper = (lane & s) != 0;
@@ -693,13 +707,11 @@ static int launch_hessian_kind(const GnWs& ws, const m3r_gn_params& p, const flo
   pp.z_eps = p.z_eps;
   if (ws.L.num_edges == 0 || ws.L.num_pts == 0) return M3R_OK;
   const unsigned grid = (unsigned)hessian_grid();
-  static bool attr_done = false;  // per instantiation (function-local static of a template)
-  if (!attr_done) {
-    M3R_CUDA(cudaFuncSetAttribute(hessian_kernel<KIND, M3R_ROBUST_TUKEY>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                  (int)sizeof(HessRing)));
-    M3R_CUDA(cudaFuncSetAttribute(hessian_kernel<KIND, M3R_ROBUST_HUBER>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                  (int)sizeof(HessRing)));
-    attr_done = true;
+  static DynSmemOptIn attr_t, attr_h;  // per instantiation (function-local statics of a template), per device
+  {
+    int rc = ensure_dyn_smem(hessian_kernel<KIND, M3R_ROBUST_TUKEY>, sizeof(HessRing), attr_t);
+    if (rc == M3R_OK) rc = ensure_dyn_smem(hessian_kernel<KIND, M3R_ROBUST_HUBER>, sizeof(HessRing), attr_h);
+    if (rc != M3R_OK) return rc;
   }
   if (p.robust == M3R_ROBUST_TUKEY)
     hessian_kernel<KIND, M3R_ROBUST_TUKEY><<<grid, kHessThreads, sizeof(HessRing), st>>>(

@@ -8,7 +8,16 @@ constexpr int kPoseDim = 7;          // sim(3) tangent (tau, omega, sigma)
 constexpr int kAcc = 35;             // 28 lower-triangle entries of S = sum w J J^T  +  7 entries of g = sum w e J
 constexpr int kAccStride = 36;       // padded stride of one tile's partial sums
 constexpr int kTilePix = 8192;       // pixels of one edge compacted by one CTA of the packing pre-pass (32 per thread)
-constexpr int kHessThreads = 256;
+// Hessian kernel shape: two records per thread in packed arithmetic need ~70 accumulator registers, so the CTA is small
+// and three of them share an SM (168 registers per thread); -DM3R_HESS_THREADS / -DM3R_HESS_CTAS time other shapes.
+#ifndef M3R_HESS_THREADS
+#define M3R_HESS_THREADS 128
+#endif
+#ifndef M3R_HESS_CTAS
+#define M3R_HESS_CTAS 3
+#endif
+constexpr int kHessThreads = M3R_HESS_THREADS;
+constexpr int kHessCtasPerSm = M3R_HESS_CTAS;
 constexpr int kHessChunkAlign = 2 * kHessThreads; // the Hessian kernel's per-CTA range of compacted records is a multiple of this
 constexpr int kMaxHessCtas = 1024;   // upper bound on the persistent Hessian grid (2 CTAs per SM), sizes `partial`
 constexpr int kBlk = 32;             // Cholesky block size

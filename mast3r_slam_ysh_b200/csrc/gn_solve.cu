@@ -462,10 +462,10 @@ int launch_index_prep(const GnWs& ws, const int64_t* local_ii, const int64_t* lo
     const size_t smem = sizeof(long long) * (size_t)padded +
                         sizeof(int) * (size_t)(2 * E + 2 * ws.L.num_kf + 4 + 4 * (ws.L.nblk <= kSkyMaxBlk ? ws.L.nblk : 0));
     if (smem <= 200 * 1024) {
-      static size_t attr = 0;
-      if (smem > 48 * 1024 && smem > attr) {
-        M3R_CUDA(cudaFuncSetAttribute(index_prep_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        attr = smem;
+      static DynSmemOptIn attr;
+      {
+        const int rc = ensure_dyn_smem(index_prep_kernel, smem, attr);
+        if (rc != M3R_OK) return rc;
       }
       index_prep_kernel<<<1, kPrepThreads, smem, st>>>(all_ii, all_jj, num_all_edges, local_ii, local_jj, E,
                                                          ws.L.num_kf, padded, ws.ie(), ws.je(), ws.inc_off(),

@@ -43,7 +43,25 @@ static inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; 
 static inline int ceil_div(int a, int b) { return (a + b - 1) / b; }
 static inline long long ceil_div_ll(long long a, long long b) { return (a + b - 1) / b; }
 
-int sm_count();
+int sm_count();  // of the CURRENT device (cached per device)
+
+// cudaFuncSetAttribute applies to the current device only, so the "already opted in" value is remembered PER DEVICE
+// (a process that runs on cuda:0 and then on cuda:1 must opt in on both).
+constexpr int kMaxDevices = 64;
+struct DynSmemOptIn {
+  size_t set[kMaxDevices] = {};
+};
+int current_device_slot();  // cudaGetDevice(), clamped to [0, kMaxDevices)
+template <typename K>
+static inline int ensure_dyn_smem(K kernel, size_t bytes, DynSmemOptIn& cache) {
+  if (bytes <= 48 * 1024) return M3R_OK;
+  const int d = current_device_slot();
+  if (bytes > cache.set[d]) {
+    M3R_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
+    cache.set[d] = bytes;
+  }
+  return M3R_OK;
+}
 // keep stream-ordered scratch cached in the default pool across synchronisations (the default threshold returns it to the OS)
 int keep_async_pool();
 

@@ -501,7 +501,8 @@ static int track_launch(int kind, TrackArgs A, cudaStream_t st) {
   const long long rounds = ntiles > 0 ? ceil_div_ll(ntiles, (long long)G * kTrkTilesPerRound) : 1;
   const long long cap = rounds * kTrkThreads;
   const size_t smem = (size_t)cap * 2 * sizeof(float4);
-  static int smem_max = 0;
+  static int smem_max_dev[kMaxDevices] = {};  // per device: the opt-in applies to the current device only
+  int& smem_max = smem_max_dev[current_device_slot()];
   if (smem_max == 0) {
     int dev = 0, v = 0;
     M3R_CUDA(cudaGetDevice(&dev));

@@ -175,6 +175,12 @@ class ShardedGaussNewton:
             rc = self.lib.m3r_gn_end(self.num_kf, self.num_pts, self.E, C.c_void_p(dx.data_ptr()) if dx.numel() else None,
                                      C.c_void_p(info.data_ptr()), C.c_void_p(self.ws_ptr), self._stream())
         _lib.check(rc, "gn_end")
+        if self.peer is not None and (int(info[3].item()) & 0x40000000):
+            # a peer rank never reached the in-kernel exchange (~4 s): the device stopped the solve with dx = 0 and the
+            # poses of the last completed iteration; replicas may have diverged, so this must not pass silently
+            raise RuntimeError("sharded Gauss-Newton: a peer rank never arrived at the in-kernel all-reduce "
+                               "(timeout); poses were left at the last completed iteration. Re-run with "
+                               "exchange='nccl' or check the other ranks.")
         return dx, info
 
 

@@ -7,7 +7,8 @@ The reference ships only sm_60..sm_86 gencodes and uses two torch C++ APIs that 
   2. applies the 4-line API patch (`D11.type()` -> `D11.scalar_type()`, matching_kernels.cu:103;
      `torch::linalg::linalg_norm` -> `at::linalg_norm`, gn_kernels.cu:802,1219,1629),
   3. compiles it for sm_100a with nvcc/g++ directly (not the reference's setup.py),
-  4. writes ONLY `oracle/_ref/mast3r_slam_backends_ref*.so` (git-ignored; it travels to the GPU box).
+  4. writes ONLY into `oracle/_ref/` (git-ignored; it travels to the GPU box): `mast3r_slam_backends_ref*.so` and
+     `pyref/` = unchanged copies of the reference's pure-Python callers of the path (see stage_python).
 
 The resulting module is the GPU oracle for `tests/ -m gpu` and the "reference CUDA on the same B200" timing arm
 in bench.py.  Nothing in the product package imports it.  It cannot run in a GPU-less container.
@@ -30,12 +31,31 @@ def patch(text, old, new, count):
     return text.replace(old, new)
 
 
+PY_STAGE = ("mast3r_slam/__init__.py", "mast3r_slam/matching.py", "mast3r_slam/image.py", "mast3r_slam/config.py",
+            "mast3r_slam/nonlinear_optimizer.py", "config/base.yaml")
+
+
+def stage_python():
+    """The reference's pure-Python callers of the path (matching.py and what it imports, nonlinear_optimizer.py,
+    config/base.yaml) are staged UNCHANGED under oracle/_ref/pyref/ (git-ignored like the .so, travels to the GPU box)
+    so that tests can run them over the drop-in shim where /root/reference does not exist."""
+    dst_root = os.path.join(OUT, "pyref")
+    for rel in PY_STAGE:
+        src = os.path.join(REF, rel)
+        dst = os.path.join(dst_root, rel)
+        os.makedirs(os.path.dirname(dst), exist_ok=True)
+        if not os.path.exists(dst) or os.path.getmtime(dst) < os.path.getmtime(src):
+            shutil.copyfile(src, dst)
+    print(f"[build_ref] staged {len(PY_STAGE)} reference Python files under {dst_root}")
+
+
 def main():
     src = os.path.join(REF, "mast3r_slam", "backend")
     if not os.path.isdir(src):
         print(f"[build_ref] {src} not present; skipping (prebuilt oracle/_ref is used if it exists)")
         return 0
     os.makedirs(OUT, exist_ok=True)
+    stage_python()
     so = os.path.join(OUT, NAME + sysconfig.get_config_var("EXT_SUFFIX"))
     newest_src = max(
         os.path.getmtime(os.path.join(src, "src", f)) for f in ("gn.cpp", "gn_kernels.cu", "matching_kernels.cu")

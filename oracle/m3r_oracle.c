@@ -474,6 +474,12 @@ static inline float orc_tukey(float r) {
 }
 static inline float orc_robust(float r, int robust) { return robust ? orc_tukey(r) : orc_huber(r); }
 
+/* the IRLS weight functions alone, for pinning against nonlinear_optimizer.py:28-42 (tests/golden/robust.npz) */
+ORC_API int orc_robust_weights(const float* r, int64_t n, int robust, float* w) {
+  for (int64_t i = 0; i < n; i++) w[i] = orc_robust(r[i], robust);
+  return 0;
+}
+
 typedef struct {
   int nres;
   float err[4];

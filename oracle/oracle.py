@@ -65,6 +65,15 @@ def f16_bits_to_f32(x):
     return out
 
 
+def robust_weights(r, robust=ROBUST_HUBER):
+    """IRLS weight of the GN kernels: Huber k=1.345 (gn_kernels.cu:172-175) or Tukey t=4.6851
+    (nonlinear_optimizer.py:36-42)."""
+    r = _c(r, np.float32)
+    out = np.empty(r.shape, np.float32)
+    lib().orc_robust_weights(_p(r), C.c_int64(r.size), C.c_int(int(robust)), _p(out))
+    return out
+
+
 def iter_proj(rays_img_with_grad, pts_3d_norm, p_init, max_iter, lambda_init, cost_thresh):
     """reference: iter_proj (gn.cpp:84-99) -> [p_new (b,n,2) f32, converged (b,n) bool]"""
     rays = _c(rays_img_with_grad, np.float32)

@@ -116,6 +116,15 @@ def huber(r, k=1.345):  # nonlinear_optimizer.py:28-33
     return torch.where(r_abs < k, unit, k / r_abs)
 
 
+def check_convergence(rel_error_threshold, delta_norm_threshold, old_cost, new_cost, delta):
+    """nonlinear_optimizer.py:5-25 (without the print).  On the first iteration old_cost is inf (tracker.py:183):
+    (inf - c) / inf is NaN and NaN < threshold is False, so only the step norm can stop the loop there."""
+    cost_diff = old_cost - new_cost
+    rel_dec = math.fabs(cost_diff / old_cost)
+    delta_norm = torch.linalg.norm(delta)
+    return bool(rel_dec < rel_error_threshold or delta_norm < delta_norm_threshold)
+
+
 def solve(sqrt_info, r, J, cfg):  # tracker.py:156-171
     whitened_r = sqrt_info * r
     robust_sqrt_info = sqrt_info * torch.sqrt(huber(whitened_r, k=cfg["huber"]))
@@ -146,8 +155,7 @@ def opt_pose_ray_dist_sim3(Xf, Xk, T_WCf, T_WCk, Qk, valid, cfg=TRACKING, max_it
         tau, new_cost = solve(sqrt_info, r, J, cfg)
         T_CkCf = T_CkCf.retr(tau)
         iters += 1
-        rel_dec = math.fabs((old_cost - new_cost) / old_cost) if old_cost != float("inf") else float("inf")
-        if rel_dec < cfg["rel_error"] or torch.linalg.norm(tau) < cfg["delta_norm"]:
+        if check_convergence(cfg["rel_error"], cfg["delta_norm"], old_cost, new_cost, tau):
             break
         old_cost = new_cost
     return T_WCk * T_CkCf, T_CkCf, iters
@@ -214,8 +222,7 @@ def opt_pose_calib_sim3(Xf, Xk, T_WCf, T_WCk, Qk, valid, meas_k, valid_meas_k, K
         tau, new_cost = solve(sqrt_info2, r, J, cfg)
         T_CkCf = T_CkCf.retr(tau)
         iters += 1
-        rel_dec = math.fabs((old_cost - new_cost) / old_cost) if old_cost != float("inf") else float("inf")
-        if rel_dec < cfg["rel_error"] or torch.linalg.norm(tau) < cfg["delta_norm"]:
+        if check_convergence(cfg["rel_error"], cfg["delta_norm"], old_cost, new_cost, tau):
             break
         old_cost = new_cost
     return T_WCk * T_CkCf, T_CkCf, iters

@@ -1,0 +1,221 @@
+"""GPU parity at BASELINE.json's own sizes (512x384) against the REFERENCE's CUDA kernels, run side by side on the same
+B200: oracle/_ref/mast3r_slam_backends_ref*.so is the reference's gn.cpp / gn_kernels.cu / matching_kernels.cu compiled
+for sm_100a by oracle/build_ref.py (test infrastructure; the product never loads it).  Also runs the reference's own
+mast3r_slam/matching.py UNCHANGED (staged under oracle/_ref/pyref by the same recipe) over the drop-in shim
+`mast3r_slam_backends.py`.
+
+Bars (BASELINE.json north_star): iter_proj |du|,|dv| <= 1e-3 px and `converged` equal; refine_matches indices bit-exact;
+GN first-iteration dx and final poses within 1e-4 relative.  Where the first-iteration dx differs from the reference
+by more than 1e-4 the test proves that the gap is the reference's own fp32 accumulation error: with the fp64-accumulating
+CPU oracle as truth, ours must be within 1e-4 of the truth, closer to it than the reference is, and
+|ours - ref| <= |ours - truth| + |ref - truth|.  Every measured figure goes to gpurun_out/parity_full_size.json (a copy is
+committed under profiles/)."""
+import json
+import os
+import sys
+
+import numpy as np
+import pytest
+import torch
+
+from conftest import ROOT
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda:0"
+H, W = 384, 512
+REF_DIR = os.path.join(ROOT, "oracle", "_ref")
+RESULTS = {}
+
+
+@pytest.fixture(scope="module")
+def ref():
+    if not torch.cuda.is_available():
+        pytest.skip("no CUDA device")
+    if REF_DIR not in sys.path:
+        sys.path.insert(0, REF_DIR)
+    try:
+        import mast3r_slam_backends_ref as mod
+    except Exception as ex:  # loud: these are the parity tests proper
+        pytest.skip(f"REFERENCE CUDA MODULE MISSING (oracle/_ref, built by __graft_entry__.build()): {ex!r}")
+    return mod
+
+
+@pytest.fixture(scope="module", autouse=True)
+def _dump_results():
+    yield
+    if RESULTS:
+        out = os.path.join(ROOT, "gpurun_out")
+        os.makedirs(out, exist_ok=True)
+        with open(os.path.join(out, "parity_full_size.json"), "w") as f:
+            json.dump(RESULTS, f, indent=1, sort_keys=True)
+
+
+def _syn():
+    from mast3r_slam_ysh_b200 import synthetic as syn
+    return syn
+
+
+# ------------------------------------------------------------------------------------------------------- matching
+@pytest.mark.parametrize("b,warm", [(1, False), (2, True)])
+def test_iter_proj_and_refine_512x384_vs_reference_cuda(be, ref, b, warm):
+    syn = _syn()
+    mt = syn.MATCHING
+    m = syn.make_match_problem(b, H, W, seed=1235 + b, device=DEV, warm_start=warm)
+    rays, pts, p0 = m["rays_img_with_grad"], m["pts_3d_norm"], m["p_init"]
+    args = (mt["max_iter"], mt["lambda_init"], mt["convergence_thresh"])
+    p_new, conv = be.iter_proj(rays, pts, p0, *args)
+    p_ref, c_ref = ref.iter_proj(rays, pts, p0, *args)
+    torch.cuda.synchronize()
+    err = float((p_new - p_ref).abs().max())
+    conv_mismatch = int((conv != c_ref).sum())
+    D11, D21 = m["D11"].half(), m["D21"].view(b, H * W, -1).half()
+    p1 = p_ref.long()
+    (q,) = be.refine_matches(D11, D21, p1, mt["radius"], mt["dilation_max"])
+    (q_ref,) = ref.refine_matches(D11, D21, p1, mt["radius"], mt["dilation_max"])
+    torch.cuda.synchronize()
+    refine_mismatch = int((q != q_ref).any(-1).sum())
+    RESULTS[f"match_b{b}_{'warm' if warm else 'identity'}"] = dict(
+        iter_proj_max_abs_err_px=err, converged_mismatches=conv_mismatch, converged_frac=float(c_ref.float().mean()),
+        refine_index_mismatches=refine_mismatch, refine_moved_frac=float((q_ref != p1).any(-1).float().mean()),
+        queries=b * H * W)
+    assert err <= 1e-3, err                      # north_star: iter_proj coordinates within 1e-3 px
+    assert conv_mismatch == 0
+    assert refine_mismatch == 0                  # north_star: refine_matches indices bit-exact
+    assert float((q_ref != p1).any(-1).float().mean()) > 0.05  # the refinement really moved points
+
+
+def test_reference_matching_py_unchanged_over_the_shim(be, ref):
+    """mast3r_slam/matching.py:52-91 of the reference, byte for byte, with `import mast3r_slam_backends` resolving to
+    the repo-root shim (north_star: "matching.py ... call it unchanged"); then the same file over the reference's CUDA
+    module.  Both runs must give identical indices and validity flags; the fused device path (mm.match) is held to
+    >= 99.8 % (its ray image is not cuDNN's conv2d bit for bit)."""
+    pyref = os.path.join(REF_DIR, "pyref")
+    if not os.path.exists(os.path.join(pyref, "mast3r_slam", "matching.py")):
+        pytest.skip("REFERENCE PYTHON NOT STAGED (oracle/_ref/pyref, written by oracle/build_ref.py)")
+    for p in (pyref, ROOT):
+        if p not in sys.path:
+            sys.path.insert(0, p)
+    import mast3r_slam_backends as shim
+    from mast3r_slam.config import config, load_config
+    load_config(os.path.join(pyref, "config", "base.yaml"))
+    import mast3r_slam.matching as ref_matching
+    assert ref_matching.mast3r_slam_backends is shim and shim.iter_proj is be.iter_proj
+    from mast3r_slam_ysh_b200 import matching as mm
+    syn = _syn()
+    out = {}
+    for (b, h, w, warm, noise) in [(1, H, W, False, 0.005), (2, H, W, True, 0.005), (1, 96, 128, False, 0.0)]:
+        m = syn.make_match_problem(b, h, w, seed=31 + b + h, device=DEV, warm_start=warm, point_noise=noise)
+        idx0 = (m["p_init"][..., 0] + w * m["p_init"][..., 1]).long() if warm else None
+        a = (m["X11"], m["X21"], m["D11"], m["D21"], idx0)
+        idx_s, val_s = ref_matching.match(*a)                       # reference Python + our kernels
+        ref_matching.mast3r_slam_backends = ref
+        try:
+            idx_r, val_r = ref_matching.match(*a)                   # reference Python + reference CUDA
+        finally:
+            ref_matching.mast3r_slam_backends = shim
+        idx_u, val_u = mm.match_unfused(*a)                         # our restatement of the glue
+        idx_f, val_f = mm.match(*a)                                 # fused device path
+        torch.cuda.synchronize()
+        assert idx_s.shape == idx_r.shape == (b, h * w) and val_s.shape == val_r.shape == (b, h * w, 1)
+        assert idx_s.dtype == torch.int64 and val_s.dtype == torch.bool
+        n_idx, n_val = int((idx_s != idx_r).sum()), int((val_s != val_r).sum())
+        fused_same = float((idx_f == idx_r).float().mean())
+        fused_val = float((val_f == val_r).float().mean())
+        out[f"b{b}_{h}x{w}_{'warm' if warm else 'identity'}"] = dict(
+            index_mismatches_shim_vs_ref_cuda=n_idx, valid_mismatches_shim_vs_ref_cuda=n_val,
+            valid_frac=float(val_r.float().mean()), fused_identical_index_frac=fused_same,
+            fused_identical_valid_frac=fused_val)
+        assert n_idx == 0 and n_val == 0
+        assert torch.equal(idx_u, idx_s) and torch.equal(val_u, val_s)
+        if noise == 0.0:  # rough (noisy) ray images make non-converged LM steps chaotic in the last bit, DESIGN 3.5
+            assert fused_same >= 0.998 and fused_val >= 0.998, (fused_same, fused_val)
+    RESULTS["reference_matching_py_over_shim"] = out
+    assert config["matching"]["radius"] == 3
+
+
+# ------------------------------------------------------------------------------------------------------- Gauss-Newton
+def _run(mod, kind, g, T, iters, lo, **kw):
+    a = [g[k] for k in ("Xs", "Cs")]
+    rest = [g[k] for k in ("ii", "jj", "idx_ii2jj", "valid_match", "Q")]
+    if kind == "rays":
+        return mod.gauss_newton_rays(T, *a, *rest, lo["sigma_ray"], lo["sigma_dist"], lo["C_conf"], lo["Q_conf"], iters,
+                                     lo["delta_norm"], **kw)
+    if kind == "calib":
+        return mod.gauss_newton_calib(T, *a, g["K"], *rest, g["h"], g["w"], lo["pixel_border"], lo["depth_eps"],
+                                      lo["sigma_pixel"], lo["sigma_depth"], lo["C_conf"], lo["Q_conf"], iters,
+                                      lo["delta_norm"], **kw)
+    return mod.gauss_newton_points(T, *a, *rest, lo["sigma_point"], lo["C_conf"], lo["Q_conf"], iters, lo["delta_norm"],
+                                   **kw)
+
+
+def _truth_dx1(orc, kind, g, lo):
+    """First-iteration dx with the per-edge sums accumulated in fp64 (oracle accum=0) and a dense fp64 solve."""
+    n = {k: (v.cpu().numpy() if isinstance(v, torch.Tensor) else v) for k, v in g.items()}
+    T = n["Twc"].copy()
+    a = (n["Xs"], n["Cs"])
+    rest = (n["ii"], n["jj"], n["idx_ii2jj"], n["valid_match"], n["Q"])
+    if kind == "rays":
+        (dx,), _ = orc.gauss_newton_rays(T, *a, *rest, lo["sigma_ray"], lo["sigma_dist"], lo["C_conf"], lo["Q_conf"], 1,
+                                         lo["delta_norm"], accum=0)
+    elif kind == "calib":
+        (dx,), _ = orc.gauss_newton_calib(T, *a, n["K"], *rest, g["h"], g["w"], lo["pixel_border"], lo["depth_eps"],
+                                          lo["sigma_pixel"], lo["sigma_depth"], lo["C_conf"], lo["Q_conf"], 1,
+                                          lo["delta_norm"], accum=0)
+    else:
+        (dx,), _ = orc.gauss_newton_points(T, *a, *rest, lo["sigma_point"], lo["C_conf"], lo["Q_conf"], 1,
+                                           lo["delta_norm"], accum=0)
+    return dx.astype(np.float64)
+
+
+GN_CASES = {
+    # name: (kind, keyframes, graph, yaw step, iterations)
+    "rays_10kf_E48": ("rays", 10, ("chain", 3), 10.0, 10),
+    "rays_configs2_32kf_E512": ("rays", 32, ("ring", 8), None, 10),          # BASELINE.json configs[2]
+    "calib_configs3_10kf_E48": ("calib", 10, ("chain", 3), 10.0, 10),        # BASELINE.json configs[3]
+    "points_10kf_E48": ("points", 10, ("chain", 3), 10.0, 10),
+}
+
+
+@pytest.mark.parametrize("name", list(GN_CASES))
+def test_gauss_newton_512x384_vs_reference_cuda(be, ref, orc, name):
+    syn = _syn()
+    lo = syn.LOCAL_OPT
+    kind, nkf, (shape, span), yaw, iters = GN_CASES[name]
+    edges = syn.ring_edges(nkf, span, wrap=(shape == "ring"))
+    g = syn.make_gn_problem(nkf, H, W, edges, seed=1236, device=DEV, calib=(kind == "calib"), yaw_step_deg=yaw)
+    T1, R1 = g["Twc"].clone(), g["Twc"].clone()
+    (dx1,) = _run(be, kind, g, T1, 1, lo)
+    (rdx1,) = _run(ref, kind, g, R1, 1, lo)
+    Tn, Rn = g["Twc"].clone(), g["Twc"].clone()
+    (_,), info = _run(be, kind, g, Tn, iters, lo, return_info=True)
+    _run(ref, kind, g, Rn, iters, lo)
+    torch.cuda.synchronize()
+    info = info.cpu().numpy()
+    dx1n, rdx1n = dx1.double().cpu().numpy(), rdx1.double().cpu().numpy()
+    nrm = np.linalg.norm(rdx1n)
+    rel_dx1 = float(np.linalg.norm(dx1n - rdx1n) / nrm)
+    rel_T1 = float((T1 - R1).norm() / R1.norm())
+    rel_Tn = float((Tn - Rn).norm() / Rn.norm())
+    rec = dict(kind=kind, keyframes=nkf, directed_edges=int(g["ii"].numel()), pixels=H * W,
+               valid_match_frac=float(g["valid_match"].float().mean()), dx1_rel_ours_vs_ref=rel_dx1,
+               T1_rel_ours_vs_ref=rel_T1, Tfinal_rel_ours_vs_ref=rel_Tn, iterations=int(info[0]),
+               failed_factorisations=int(info[2]),
+               gt_err_init=float((g["Twc"] - g["Twc_gt"]).abs().max()),
+               gt_err_final_ours=float((Tn - g["Twc_gt"]).abs().max()),
+               gt_err_final_ref=float((Rn - g["Twc_gt"]).abs().max()))
+    if rel_dx1 > 1e-4:
+        truth = _truth_dx1(orc, kind, g, lo)
+        tn = np.linalg.norm(truth)
+        e_ours = float(np.linalg.norm(dx1n - truth) / tn)
+        e_ref = float(np.linalg.norm(rdx1n - truth) / tn)
+        rec.update(dx1_rel_ours_vs_fp64_truth=e_ours, dx1_rel_ref_vs_fp64_truth=e_ref,
+                   truth="oracle/m3r_oracle.c accum=0 (per-edge sums in fp64) + dense fp64 solve")
+        RESULTS[name] = rec
+        assert e_ours <= 1e-4, rec                                   # ours meets the bar against the exact sums
+        assert e_ours < e_ref, rec                                   # and is closer to them than the reference is
+        assert rel_dx1 * nrm / tn <= e_ours + e_ref + 1e-7, rec      # the gap is accounted for by the two errors
+    RESULTS[name] = rec
+    assert info[2] == 0
+    assert rel_T1 <= 1e-5, rec            # poses after the first update
+    assert rel_Tn <= 1e-4, rec            # north_star: final poses within 1e-4 relative
+    assert torch.equal(Tn[0], g["Twc"][0])  # gauge keyframe untouched

@@ -29,4 +29,6 @@ res["accumulate_ms"] = timed(acc, 10)
 def both(): acc(); sol()
 T.copy_(g["Twc"]); res["iter_ms"] = timed(both, 10)
 acc(); res["solve_ms"] = res["iter_ms"] - res["accumulate_ms"]
+res["records"] = int(lib.m3r_gn_record_count(C.c_void_p(s.ws_ptr), s.num_kf, s.num_pts, s.E))
+res["pixel_edges"] = int(g["ii"].numel()) * 384 * 512
 print(json.dumps(res))
