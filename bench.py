@@ -3,17 +3,25 @@
 
 Contract (one JSON line on rank 0):
   metric  gn_solve_ms_per_iter: one "step" = one gauss_newton_rays solve (max_iter = 10 GN iterations: Hessian
-          assembly + reduction + fp64 Cholesky + retraction + convergence flag) of BASELINE.json configs[2]
-          (32 keyframes per GPU, 8 edges/kf -> 512 directed edges per GPU, dense 512x384 points), value = step time /
-          iterations executed.  N > 1: weak scaling -- 32*N keyframes, 512*N directed edges sharded by edge, one
-          NCCL all-reduce of the dense fp64 [H | b] per iteration, replicated Cholesky (at N = 8 this is the
-          256-keyframe graph of configs[4]).
+          assembly + reduction + fp64 Cholesky + retraction + convergence flag, pre-pass included) of BASELINE.json
+          configs[2] (32 keyframes per GPU, 8 edges/kf -> 512 directed edges per GPU, dense 512x384 points), value = step
+          time / iterations executed.  N > 1: weak scaling -- 32*N keyframes, 512*N directed edges sharded by edge, the
+          fp64 [H | b] summed inside the solver kernel over peer-mapped memory (NCCL all-reduce as fallback).
   e2e     same metric through the reference-facing Python call with pinned HOST buffers: H2D of every input and D2H of
           the poses/dx inside the timed region.
-  roofline  the per-pixel Hessian kernel timed alone with CUDA events; algorithmic bytes = 45 B per pixel per directed
-          edge against MEASURED_PEAKS.json hbm_gbs.
-  cpu_baseline  the CPU oracle port (oracle/m3r_oracle.c, OpenMP) on a bounded sample of the same workload.
-  --impl reference  times that CPU port as the reference arm (the reference's GN kernels are CUDA-only; its CPU code
+  roofline  the per-record Hessian kernel timed alone with CUDA events.  Unit = one surviving (pixel, directed edge)
+          record of the packing pre-pass, 32 B streamed per record and iteration; achieved = records x
+          32 B / launch time against MEASURED_PEAKS.json hbm_gbs; `traffic` = DRAM bytes of the same launch from the
+          committed ncu capture.  The reference layout's 45 B per pixel-edge is kept as
+          `reference_layout_equivalent_gbs` -- it is not a roofline fraction because gated-out pixels are never read
+          again after the pre-pass.
+  cpu_baseline  the CPU oracle port (oracle/m3r_oracle.c, OpenMP, all host cores) on a bounded sample of the same
+          workload, scaled to the full edge count (`extrapolated: true`).
+  extra   configs[1] (iter_proj / refine_matches / match at b = 1, 8, 64, 256), configs[3] (gauss_newton_calib),
+          configs[4] (fixed 256-keyframe loop-closure graph + 256 pair matches, strong-scaled over the N ranks),
+          reference_cuda (the reference's own CUDA kernels, oracle/_ref, on the same GPU and inputs), cpu_tracker
+          (configs[0]), tracker, graph_prep, a dense-overlap Hessian point.
+  --impl reference  times the CPU port as the reference arm (the reference's GN kernels are CUDA-only; its CPU code
           for this math is the tracker solve, reported as extra.cpu_tracker).
 """
 import argparse
@@ -30,7 +38,9 @@ sys.path.insert(0, ROOT)
 H, W = 384, 512
 N_PIX = H * W
 KF_PER_GPU, SPAN, GN_ITERS = 32, 8, 10
-ALGO_BYTES_PER_PIXEL_EDGE = 45  # valid 1 + idx 8 + X_j 12 + X_i 12 + Q 4 + C_i 4 + C_j 4
+RECORD_BYTES = 32               # two float4 per surviving (pixel, edge) record, streamed once per iteration
+REF_LAYOUT_BYTES_PER_PIXEL_EDGE = 45  # valid 1 + idx 8 + X_j 12 + X_i 12 + Q 4 + C_i 4 + C_j 4
+INPUT_BYTES_PER_PIXEL_EDGE = 13       # idx 8 + valid 1 + Q 4, read once per solve by the pre-pass
 ITER_PROJ_BYTES_PER_QUERY = 65  # 36 ray image + 12 target + 8 init + 8 out + 1 flag
 
 
@@ -88,18 +98,29 @@ def gn_params():
 
 
 # ====================================================================================================== reference arm
-def cpu_gn_sample(target_seconds=12.0, device="cpu"):
-    """Times the CPU oracle port on a bounded sample of configs[2]: S of the 512 directed edges, ONE GN iteration of
-    edge-block evaluation (the O(E*N) part), scaled to 512 edges, plus the dense solve of the 217-dim system."""
+def host_cores():
+    try:
+        return len(os.sched_getaffinity(0))
+    except Exception:
+        return os.cpu_count() or 1
+
+
+def cpu_gn_sample(n_gpus=1, device="cpu"):
+    """Times the CPU oracle port on a bounded sample of the workload bench.py --gpus n_gpus names: S of its directed
+    edges, ONE GN iteration of edge-block evaluation (the O(E*N) part), scaled to all edges, plus the dense fp64 solve of
+    its system.  All host cores, set explicitly (a launcher may export OMP_NUM_THREADS=1)."""
     import numpy as np
+    import torch
     from mast3r_slam_ysh_b200 import synthetic as syn
     from oracle import oracle as orc
     lo = syn.LOCAL_OPT
-    cores = orc.num_threads()
-    nkf = KF_PER_GPU
+    cores = orc.set_num_threads(host_cores())
+    nkf = KF_PER_GPU * n_gpus
     edges = syn.ring_edges(nkf, SPAN)
-    S = max(cores, 8)
-    g = syn.make_gn_problem(nkf, H, W, edges, seed=1236, device=device, directed_subset=__import__("torch").arange(S))
+    E_full = 2 * len(edges[0])
+    S = min(E_full, max(cores, 8))
+    g = syn.make_gn_problem(nkf, H, W, edges, seed=1236, device=device, directed_subset=torch.arange(S),
+                            yaw_step_deg=360.0 / KF_PER_GPU)
     a = [g[k].cpu().numpy() for k in ("Twc", "Xs", "Cs")]
     ie, je = g["ii"].cpu().numpy(), g["jj"].cpu().numpy()
     rest = [g[k].cpu().numpy() for k in ("idx_ii2jj", "valid_match", "Q")]
@@ -110,10 +131,9 @@ def cpu_gn_sample(target_seconds=12.0, device="cpu"):
                            rest[2][:n_edges], lo["C_conf"], lo["Q_conf"], accum=1, sigma_ray=lo["sigma_ray"],
                            sigma_dist=lo["sigma_dist"])
         return time.perf_counter() - t
-    one(cores)  # warm
+    one(min(S, cores))  # warm
     t_s = one(S)
-    E_full = 2 * len(edges[0])
-    # dense solve part on a random SPD 217-dim system (same code path as the oracle's per-iteration solve)
+    # dense solve part on a random SPD system of the workload's dimension (same code path as the oracle's solve)
     rng = np.random.default_rng(0)
     Hs = np.zeros((4, nkf - 1, 7, 7), np.float32)
     Mb = rng.standard_normal((nkf - 1, 7, 7)).astype(np.float32)
@@ -124,31 +144,42 @@ def cpu_gn_sample(target_seconds=12.0, device="cpu"):
     orc.gn_solve(Hs, gs, io, io - 10 ** 6, nkf - 1)
     t_solve = time.perf_counter() - t
     ms_iter = (t_s * E_full / S + t_solve) * 1e3
-    return dict(value=ms_iter, unit="ms/iter", cores=cores, kind="port",
-                sample=f"{S} of {E_full} directed edges x {N_PIX} px, 1 GN iteration of oracle/m3r_oracle.c "
-                       f"(fp32 reference-order accumulation, OpenMP), scaled x{E_full / S:.0f}, + dense fp64 solve"), t_s
+    return dict(value=ms_iter, unit="ms/iter", cores=cores, kind="port", extrapolated=True, scale=E_full / S,
+                measured_sample_seconds=t_s + t_solve,
+                sample=f"{S} of {E_full} directed edges x {N_PIX} px of the {nkf}-keyframe graph, 1 GN iteration of "
+                       f"oracle/m3r_oracle.c (fp32 reference-order accumulation, OpenMP x{cores}), edge part scaled "
+                       f"x{E_full / S:.0f}, + dense fp64 solve (n = {7 * (nkf - 1)})"), t_s
 
 
-def cpu_tracker_baseline(threads=None):
-    """configs[0]: pure-torch tracker solve (oracle/tracker_torch.py) on one synthetic 512x384 pair, host cores."""
+def cpu_tracker_baseline():
+    """BASELINE.md 3b / configs[0]: pure-torch tracker solve (oracle/tracker_torch.py) on one synthetic 512x384 pair on the
+    host cores: 1 thread and all cores, median of 20 solves after 3 warm-ups, core count in the report."""
     import torch
     from mast3r_slam_ysh_b200 import synthetic as syn
     from oracle import tracker_torch as tt
-    if threads:
-        torch.set_num_threads(threads)
     g = syn.make_gn_problem(2, H, W, ([0], [1]), seed=1234, yaw_step_deg=8.0)
     idx = g["idx_ii2jj"][0]
     valid = g["valid_match"][0].float() * (g["Q"][0] > 1.5).float()
     Xf, Xk, Qk = g["Xs"][1], g["Xs"][0][idx], g["Q"][0]
-    ts, its = [], 0
-    for rep in range(4):
-        t = time.perf_counter()
-        _, _, its = tt.opt_pose_ray_dist_sim3(Xf, Xk, tt.Sim3(g["Twc"][1:2].clone()), tt.Sim3(g["Twc"][0:1].clone()), Qk, valid)
-        if rep:
-            ts.append((time.perf_counter() - t) / its)
-    ts.sort()
-    return dict(ms_per_iter=ts[len(ts) // 2] * 1e3, iters=its, threads=torch.get_num_threads(),
-                what="tracker.opt_pose_ray_dist_sim3 port, 1 pair 512x384, torch CPU")
+    out = dict(what="tracker.opt_pose_ray_dist_sim3 port (oracle/tracker_torch.py), 1 pair 512x384, torch CPU, "
+                    "config/base.yaml thresholds; median of 20 solves after 3 warm-ups",
+               host_cores=host_cores())
+    keep = torch.get_num_threads()
+    for label, nt in (("threads_1", 1), ("threads_all", host_cores())):
+        torch.set_num_threads(nt)
+        ts, its = [], 0
+        for rep in range(23):
+            t = time.perf_counter()
+            _, _, its = tt.opt_pose_ray_dist_sim3(Xf, Xk, tt.Sim3(g["Twc"][1:2].clone()), tt.Sim3(g["Twc"][0:1].clone()),
+                                                  Qk, valid)
+            if rep >= 3:
+                ts.append(time.perf_counter() - t)
+        ts.sort()
+        med = ts[len(ts) // 2]
+        out[label] = dict(threads=torch.get_num_threads(), solve_ms=med * 1e3, ms_per_iter=med * 1e3 / max(its, 1),
+                          iters=its, p10_ms=ts[len(ts) // 10] * 1e3, p90_ms=ts[(9 * len(ts)) // 10] * 1e3)
+    torch.set_num_threads(keep)
+    return out
 
 
 def run_reference(args):
@@ -158,7 +189,7 @@ def run_reference(args):
     vals = []
     base = None
     for s in range(args.warmup + args.steps):
-        base, _ = cpu_gn_sample()
+        base, _ = cpu_gn_sample(args.gpus)
         if s >= args.warmup:
             vals.append(base["value"])
     v = sum(vals) / len(vals)
@@ -166,9 +197,11 @@ def run_reference(args):
     line = dict(impl="reference", metric="gn_solve_ms_per_iter", value=v, unit="ms/iter", n_gpus=args.gpus,
                 steps=args.steps, warmup=args.warmup, ms_per_step=v * GN_ITERS, higher_is_better=False, scaling="weak",
                 vs_baseline=None, dtype="f32 (fp64 solve)", data="synthetic",
-                config=workload_config(args.gpus), cpu_baseline=base,
-                e2e=dict(value=v, unit="ms/iter", h2d_bytes_per_step=0, d2h_bytes_per_step=0), gpu_launches=0,
-                extra=dict(cpu_tracker=cpu_tracker_baseline()))
+                config=workload_config(args.gpus), cpu_baseline=base, extrapolated=True,
+                note="CPU port of the reference's CUDA-only GN path (oracle/m3r_oracle.c) on the host cores; every step "
+                     "times a bounded edge sample of the named workload and scales the edge part to all edges -- value "
+                     "and ms_per_step are extrapolations, not wall-clock of a full solve",
+                e2e=dict(value=v, unit="ms/iter", h2d_bytes_per_step=0, d2h_bytes_per_step=0), gpu_launches=0)
     print(json.dumps(line), flush=True)
 
 

@@ -6,7 +6,8 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libm3r_backends_b200.so")
+# M3R_LIB_PATH: development switch for timing compile-time variants of the library (tools/build_variants.sh)
+LIB_PATH = os.environ.get("M3R_LIB_PATH") or os.path.join(_HERE, "libm3r_backends_b200.so")
 
 M3R_GN_POINTS, M3R_GN_RAYS, M3R_GN_CALIB = 0, 1, 2
 M3R_ROBUST_HUBER, M3R_ROBUST_TUKEY = 0, 1

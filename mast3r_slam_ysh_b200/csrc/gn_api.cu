@@ -96,9 +96,7 @@ GnLayout gn_layout(int num_kf, int num_pts, int num_edges, int num_all_edges) {
   L.off_lfac = take(sizeof(double) * kBlk * kBlk * (size_t)(L.nblk + 1));
   L.off_pflag = take(sizeof(int) * (size_t)(L.n / 64 + 4) * (size_t)(L.n / 64 + 5));  // pflag + pmask rows
   L.off_sky = take(sizeof(int) * (size_t)SkyPlan::total(L.n_free));
-  L.off_xc = take(sizeof(float4) * (size_t)num_kf * (size_t)num_pts);
-  L.off_rec = take(sizeof(EdgeRec) * E * (size_t)num_pts);
-  L.off_sqv = take(sizeof(float) * E * (size_t)num_pts);
+  L.off_rec = take(sizeof(GnRecord) * E * (size_t)num_pts);
   L.total = o;
   return L;
 }
@@ -169,7 +167,7 @@ static int gn_begin_impl(GnWs& ws, const m3r_gn_params* p, const float* Xs, cons
     M3R_LAUNCH_CHECK();
   }
   if ((rc = launch_pack_points(ws, Xs, Cs, p->C_thresh, st)) != M3R_OK) return rc;
-  if ((rc = launch_pack_edges(ws, *p, Cs, idx, valid, Q, st)) != M3R_OK) return rc;
+  if ((rc = launch_pack_edges(ws, *p, Xs, Cs, idx, valid, Q, st)) != M3R_OK) return rc;
   return M3R_OK;
 }
 
@@ -379,7 +377,7 @@ extern "C" int m3r_gn_edge_blocks(const m3r_gn_params* params, const float* Twc,
   if (params->kind == M3R_GN_CALIB)
     M3R_CUDA(cudaMemcpyAsync(ws.Kdev(), params->K, sizeof(float) * 9, cudaMemcpyDeviceToDevice, st));
   if ((rc = launch_pack_points(ws, Xs, Cs, params->C_thresh, st)) != M3R_OK) return rc;
-  if ((rc = launch_pack_edges(ws, *params, Cs, idx_ii2jj, valid_match, Q, st)) != M3R_OK) return rc;
+  if ((rc = launch_pack_edges(ws, *params, Xs, Cs, idx_ii2jj, valid_match, Q, st)) != M3R_OK) return rc;
   if ((rc = launch_hessian(ws, *params, Twc, st)) != M3R_OK) return rc;
   if ((rc = launch_finalize_edges(ws, Twc, st)) != M3R_OK) return rc;
   return launch_export_blocks(ws, Hs, gs, st);

@@ -15,6 +15,7 @@
 #include "gn_finalize.cuh"
 #include "gn_sim3.cuh"
 #include "gn_small.cuh"
+#include "tma.cuh"
 
 namespace m3r {
 
@@ -809,33 +810,6 @@ __device__ __forceinline__ void backsolve_phase(const FusedArgs& A, BackSmem& sm
 // ---- TMA bulk copies (cp.async.bulk, 1-D) + mbarrier: a 32 x 32 fp64 tile moves as 32 rows of 256 bytes, one
 //      instruction per lane, instead of 16 cp.async / 32 STG per lane with their address arithmetic (the update warps
 //      spent 2.8 us per step issuing the prefetch and 1.9 us storing the finished column of L that way; r1)
-__device__ __forceinline__ unsigned smem_u32(const void* p) { return (unsigned)__cvta_generic_to_shared(p); }
-__device__ __forceinline__ void mbar_init(unsigned long long* b, int count) {
-  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(b)), "r"(count) : "memory");
-  asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-}
-__device__ __forceinline__ void mbar_arrive_expect_tx(unsigned long long* b, unsigned bytes) {
-  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(b)), "r"(bytes) : "memory");
-}
-__device__ __forceinline__ bool mbar_try_wait(unsigned long long* b, unsigned parity) {
-  unsigned ok;
-  asm volatile(
-      "{ .reg .pred p; mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2; selp.u32 %0, 1, 0, p; }"
-      : "=r"(ok)
-      : "r"(smem_u32(b)), "r"(parity)
-      : "memory");
-  return ok != 0;
-}
-__device__ __forceinline__ void bulk_g2s(void* dst, const void* src, unsigned bytes, unsigned long long* b) {
-  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(smem_u32(dst)),
-               "l"(src), "r"(bytes), "r"(smem_u32(b))
-               : "memory");
-}
-__device__ __forceinline__ void bulk_s2g(void* dst, const void* src, unsigned bytes) {
-  asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(dst), "r"(smem_u32(src)), "r"(bytes)
-               : "memory");
-}
-
 constexpr int kSkyTiles = kSkyMaxLanes * (kSkyMaxLanes + 1) / 2;
 constexpr int kSkyPrefetched = 1 << 8;  // schedule word 1: the new members' tiles were fetched during the previous step
 constexpr int kSkyStride = kBlk + 2;  // 272-byte rows: conflict-free LDS.128 for "one row per lane" and "8 rows per quarter warp"

@@ -7,44 +7,42 @@
 //     S = sum w J_local J_local^T (28 entries) and g = sum w e J_local (7 entries) in the local frame and apply
 //     M = A S A^T, v = A g once per edge in fp64 (finalize kernel).  H_ii = H_jj = M, H_ij = H_ji = -M,
 //     g_j = v, g_i = -v.
-//   * Pose-independent work is hoisted into a packing pre-pass that runs once per solve: points and confidences
-//     become one float4 record (one LDG.128 per gather), and idx/valid/Q/C-gates become one 8-byte edge record.
+//   * Pose-independent work is hoisted into a packing pre-pass that runs once per solve: gates, the data-dependent
+//     gathers of X_i / C_i and the normalisation of X_i end up in one self-contained 32-byte record per surviving
+//     (pixel, edge); the per-iteration kernel streams those records with TMA bulk copies and gathers nothing.
 //   * Persistent stream-K decomposition over the flat list of compacted records (the reference runs one 256-thread
 //     block per edge), two records per thread in packed f32x2 arithmetic, fp32 warp-shuffle + shared-memory tree per
 //     segment, deterministic fp64 second stage across segments (no atomics).
 #include "f32x2.cuh"
+#include "tma.cuh"
 #include "gn_finalize.cuh"
 
 namespace m3r {
 
 // ------------------------------------------------------------------------------------------------ pre-pass
-// Also answers "does any point of any keyframe fail the confidence gate c > C_thresh?" (state[kCFail]); when none does
-// -- the usual case, C_conf = 0 and MASt3R confidences are >= 1 -- pack_edges skips its two confidence gathers per pixel.
-__global__ void __launch_bounds__(256) pack_points_kernel(const float* __restrict__ Xs, const float* __restrict__ Cs,
-                                                          float4* __restrict__ xc, long long total, float C_thresh,
-                                                          int* __restrict__ cfail) {
-  const long long p = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+// Answers "does any point of any keyframe fail the confidence gate c > C_thresh?" (state[kCFail]); when none does -- the
+// usual case, C_conf = 0 and MASt3R confidences are >= 1 -- pack_edges skips its two confidence gathers per pixel.
+__global__ void __launch_bounds__(256) conf_scan_kernel(const float* __restrict__ Cs, long long total, float C_thresh,
+                                                        int* __restrict__ cfail) {
   bool fail = false;
-  if (p < total) {
-    const float c = __ldg(Cs + p);
-    fail = !(c > C_thresh);  // NaN fails, as in the gate itself
-    const float x = __ldg(Xs + 3 * p), y = __ldg(Xs + 3 * p + 1), z = __ldg(Xs + 3 * p + 2);
-    // .w = -1/|X|: the Hessian kernel gets r_i = X_i/|X_i| and |X_i| without a rsqrt chain per record and iteration
-    // (the confidence is only needed by the gates, which read Cs directly)
-    xc[p] = make_float4(x, y, z, -1.0f / sqrtf(fmaf(x, x, fmaf(y, y, z * z))));
-  }
+  for (long long p = (long long)blockIdx.x * blockDim.x + threadIdx.x; p < total; p += (long long)gridDim.x * blockDim.x)
+    fail |= !(__ldg(Cs + p) > C_thresh);  // NaN fails, as in the gate itself
   if (__any_sync(0xffffffffu, fail) && (threadIdx.x & 31) == 0) atomicOr(cfail, 1);
 }
 
-// Gate + compact.  One CTA per (edge, 8192-pixel tile); work items are handed out by a ticket so that the owners of
-// the earlier tiles of an edge are guaranteed to be running (or finished) when a CTA looks back at them.
+// Gate + compact + materialise.  One CTA per (edge, 8192-pixel tile); work items are handed out by a ticket so that the
+// owners of the earlier tiles of an edge are guaranteed to be running (or finished) when a CTA looks back at them.
 //   phase 1: every warp walks 1024 consecutive pixels (coalesced), evaluates the pose-independent gates and parks the
 //            match index (or -1) in shared memory; survivors are counted with ballots.  The 8-byte index is only
 //            fetched where valid_match and the Q gate pass, so whole sectors of it are never read outside the overlap
 //            region of the two frames.
 //   scan   : the CTA publishes its own count at once, then warp 0 sums the counts of the earlier tiles of the same edge
 //            (decoupled look-back: nobody waits on a chain, only on each predecessor's phase 1).
-//   phase 2: warps re-walk their pixels and write the survivors, in pixel order, to rec/sqv at the scanned offset.
+//   phase 2: warps re-walk their pixels and write one SELF-CONTAINED 32-byte record per survivor, in pixel order, at the
+//            scanned offset: everything the per-iteration kernel needs that does not depend on the poses -- the matched
+//            point of frame i (already normalised for the ray residual), the point of frame j and sqrt(q).  The
+//            data-dependent gathers Xs[ix][idx], Cs[ix][idx] (gn_kernels.cu:916-918, 951) are paid once per solve here
+//            instead of once per iteration, and the Hessian kernel becomes a pure stream (TMA bulk copies, no gather).
 __device__ __forceinline__ int ld_acquire(const int* p) {
   int v;
   asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
@@ -54,18 +52,40 @@ __device__ __forceinline__ void st_release(int* p, int v) {
   asm volatile("st.release.gpu.global.s32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
 }
 
-__global__ void __launch_bounds__(256) pack_edges_kernel(const float* __restrict__ Cs, const int64_t* __restrict__ idx,
+// record halves (GnRecord::a, GnRecord::b):
+//   rays  : A = (r_i.x, r_i.y, r_i.z, |X_i|)  with r_i = X_i/|X_i|      B = (X_j.x, X_j.y, X_j.z, sqrt(q))
+//   points: A = (X_i.x, X_i.y, X_i.z, 0)                                B = same
+//   calib : A = (u_t, v_t, log z_i, 0)  target pixel of the match index (gn_kernels.cu:1361-1388)   B = same
+__device__ __forceinline__ float4 make_rec_a(int kind, const float* __restrict__ Xi, int ind, int width) {
+  const float x = __ldg(Xi + 3 * (size_t)ind), y = __ldg(Xi + 3 * (size_t)ind + 1), z = __ldg(Xi + 3 * (size_t)ind + 2);
+  if (kind == M3R_GN_RAYS) {
+    const float n = sqrtf(fmaf(x, x, fmaf(y, y, z * z)));
+    const float inv = 1.0f / n;
+    return make_float4(x * inv, y * inv, z * inv, n);
+  }
+  if (kind == M3R_GN_CALIB) {
+    const int v_t = ind / width;
+    return make_float4((float)(ind - v_t * width), (float)v_t, logf(z), 0.0f);
+  }
+  return make_float4(x, y, z, 0.0f);
+}
+
+constexpr size_t kPackSmemBytes = (size_t)kTilePix * (sizeof(int) + sizeof(unsigned short));
+__global__ void __launch_bounds__(256) pack_edges_kernel(const float* __restrict__ Xs, const float* __restrict__ Cs,
+                                                         const int64_t* __restrict__ idx,
                                                          const uint8_t* __restrict__ valid, const float* __restrict__ Q,
                                                          const int* __restrict__ ie, const int* __restrict__ je,
-                                                         EdgeRec* __restrict__ rec, float* __restrict__ sqv,
-                                                         int* __restrict__ ecount, int* __restrict__ tstate,
+                                                         GnRecord* __restrict__ rec, int* __restrict__ ecount, int* __restrict__ tstate,
                                                          const int* __restrict__ cfail, int num_pts, int tiles,
-                                                         float C_thresh, float Q_thresh) {
+                                                         float C_thresh, float Q_thresh, int kind, int width,
+                                                         float z_eps) {
   // Every lane handles 4 consecutive pixels per pass (one LDG.32 of valid, one LDG.128 of Q, two predicated LDG.128 of
   // the 8-byte indices), 8 passes of 1024 pixels per tile: a quarter of the instructions of the one-pixel-per-lane
-  // version, which was issue-bound at 52 % with 208 M warp instructions (profiles/r1_pack_v3a_ncu.txt).
+  // version, which was issue-bound at 52 % with 208 M warp instructions (r1).
   constexpr int kPasses = kTilePix / 1024;
-  __shared__ __align__(16) int s_idx[kTilePix];
+  extern __shared__ __align__(16) int s_pack_dyn[];  // kPackSmemBytes
+  int* s_idx = s_pack_dyn;                                                           // [kTilePix] match index or -1
+  unsigned short* s_lk = reinterpret_cast<unsigned short*>(s_pack_dyn + kTilePix);  // [kTilePix] phase 2: pixel offset
   __shared__ int s_work, s_base, s_cnt[kPasses * 8];
   if (threadIdx.x == 0) s_work = atomicAdd(&tstate[0], 1);
   __syncthreads();
@@ -75,12 +95,15 @@ __global__ void __launch_bounds__(256) pack_edges_kernel(const float* __restrict
   const int ix = ie[e], jx = je[e];
   const bool edge_ok = ix >= 0 && jx >= 0;
   const bool cgate = __ldg(cfail) != 0;  // some point fails c > C_thresh: evaluate the confidence gates per pixel
+  const bool zgate = kind == M3R_GN_CALIB;  // calib: z_i > z_eps is pose-independent (gn_kernels.cu:1368), gate it here
   const size_t eb = (size_t)e * num_pts;
   // vector path: every edge row of Q / idx starts 16-byte aligned and of valid 4-byte aligned
   const bool vec_ok = ((num_pts & 3) == 0) && ((reinterpret_cast<uintptr_t>(Q) & 15) == 0) &&
                       ((reinterpret_cast<uintptr_t>(idx) & 15) == 0) && ((reinterpret_cast<uintptr_t>(valid) & 3) == 0);
   const float* __restrict__ Ci = Cs + (size_t)(edge_ok ? ix : 0) * num_pts;
   const float* __restrict__ Cj = Cs + (size_t)(edge_ok ? jx : 0) * num_pts;
+  const float* __restrict__ Xi = Xs + 3 * (size_t)(edge_ok ? ix : 0) * num_pts;
+  const float* __restrict__ Xj = Xs + 3 * (size_t)(edge_ok ? jx : 0) * num_pts;
   const long long* __restrict__ idx_e = reinterpret_cast<const long long*>(idx) + eb;
 #pragma unroll 2
   for (int p = 0; p < kPasses; p++) {
@@ -121,28 +144,23 @@ __global__ void __launch_bounds__(256) pack_edges_kernel(const float* __restrict
       }
 #pragma unroll
       for (int j = 0; j < 4; j++)
-        if (!pass[j] || ind[j] < 0 || ind[j] >= num_pts) ind[j] = -1;  // corrupt indices never reach the gather
+        if (!pass[j] || ind[j] < 0 || ind[j] >= num_pts) ind[j] = -1;  // corrupt indices never reach a gather
     }
-    int4 id;
-    if (cgate) {
-      float ci[4], cj[4];
+    int id[4];
 #pragma unroll
-      for (int j = 0; j < 4; j++) {
-        ci[j] = ind[j] >= 0 ? __ldg(Ci + ind[j]) : 0.0f;
-        cj[j] = ind[j] >= 0 ? __ldg(Cj + k + j) : 0.0f;
-      }
-      id.x = (ind[0] >= 0 && ci[0] > C_thresh && cj[0] > C_thresh) ? (int)ind[0] : -1;
-      id.y = (ind[1] >= 0 && ci[1] > C_thresh && cj[1] > C_thresh) ? (int)ind[1] : -1;
-      id.z = (ind[2] >= 0 && ci[2] > C_thresh && cj[2] > C_thresh) ? (int)ind[2] : -1;
-      id.w = (ind[3] >= 0 && ci[3] > C_thresh && cj[3] > C_thresh) ? (int)ind[3] : -1;
-    } else {  // every confidence of every keyframe passes (pack_points checked them all)
-      id.x = (int)ind[0];
-      id.y = (int)ind[1];
-      id.z = (int)ind[2];
-      id.w = (int)ind[3];
+    for (int j = 0; j < 4; j++) id[j] = (int)ind[j];
+    if (cgate) {
+#pragma unroll
+      for (int j = 0; j < 4; j++)
+        if (id[j] >= 0 && !(__ldg(Ci + id[j]) > C_thresh && __ldg(Cj + k + j) > C_thresh)) id[j] = -1;
     }
-    *reinterpret_cast<int4*>(&s_idx[lk]) = id;
-    const int c = (id.x >= 0) + (id.y >= 0) + (id.z >= 0) + (id.w >= 0);
+    if (zgate) {
+#pragma unroll
+      for (int j = 0; j < 4; j++)
+        if (id[j] >= 0 && !(__ldg(Xi + 3 * (size_t)id[j] + 2) > z_eps)) id[j] = -1;
+    }
+    *reinterpret_cast<int4*>(&s_idx[lk]) = make_int4(id[0], id[1], id[2], id[3]);
+    const int c = (id[0] >= 0) + (id[1] >= 0) + (id[2] >= 0) + (id[3] >= 0);
     const int tot = __reduce_add_sync(0xffffffffu, c);
     if (lane == 0) s_cnt[p * 8 + warp] = tot;
   }
@@ -174,31 +192,41 @@ __global__ void __launch_bounds__(256) pack_edges_kernel(const float* __restrict
     }
   }
   __syncthreads();
+  // ---- phase 2a: compact (match index, pixel) of the tile's survivors in shared memory, in pixel order.  Every thread
+  //      first takes its 32 entries into registers; after the barrier the compacted list overwrites s_idx in place.
   const unsigned lt = (1u << lane) - 1u;
   const int base = s_base;
-#pragma unroll 2
+  int4 idr[kPasses];
+#pragma unroll
+  for (int p = 0; p < kPasses; p++) idr[p] = *reinterpret_cast<const int4*>(&s_idx[p * 1024 + warp * 128 + lane * 4]);
+  __syncthreads();
+  int total = 0;
+#pragma unroll
   for (int p = 0; p < kPasses; p++) {
     const int lk = p * 1024 + warp * 128 + lane * 4;
-    const int k = tile * kTilePix + lk;
-    const int4 id = *reinterpret_cast<const int4*>(&s_idx[lk]);
+    const int4 id = idr[p];
     const unsigned b0 = __ballot_sync(0xffffffffu, id.x >= 0), b1 = __ballot_sync(0xffffffffu, id.y >= 0);
     const unsigned b2 = __ballot_sync(0xffffffffu, id.z >= 0), b3 = __ballot_sync(0xffffffffu, id.w >= 0);
-    if ((b0 | b1 | b2 | b3) == 0) continue;
-    int pos = base + s_cnt[p * 8 + warp] + __popc(b0 & lt) + __popc(b1 & lt) + __popc(b2 & lt) + __popc(b3 & lt);
-    {
-      float q[4];
-      if (vec_ok && k < num_pts) {
-        const float4 qv = __ldcs(reinterpret_cast<const float4*>(Q + eb + k));
-        q[0] = qv.x; q[1] = qv.y; q[2] = qv.z; q[3] = qv.w;
-      } else {
-#pragma unroll
-        for (int j = 0; j < 4; j++) q[j] = (k + j < num_pts) ? Q[eb + k + j] : 0.0f;
-      }
-      if (id.x >= 0) { rec[eb + pos] = make_int2(id.x, k);     sqv[eb + pos] = sqrtf(q[0]); pos++; }
-      if (id.y >= 0) { rec[eb + pos] = make_int2(id.y, k + 1); sqv[eb + pos] = sqrtf(q[1]); pos++; }
-      if (id.z >= 0) { rec[eb + pos] = make_int2(id.z, k + 2); sqv[eb + pos] = sqrtf(q[2]); pos++; }
-      if (id.w >= 0) { rec[eb + pos] = make_int2(id.w, k + 3); sqv[eb + pos] = sqrtf(q[3]); pos++; }
-    }
+    int pos = s_cnt[p * 8 + warp] + __popc(b0 & lt) + __popc(b1 & lt) + __popc(b2 & lt) + __popc(b3 & lt);
+    if (id.x >= 0) { s_idx[pos] = id.x; s_lk[pos] = (unsigned short)(lk);     pos++; }
+    if (id.y >= 0) { s_idx[pos] = id.y; s_lk[pos] = (unsigned short)(lk + 1); pos++; }
+    if (id.z >= 0) { s_idx[pos] = id.z; s_lk[pos] = (unsigned short)(lk + 2); pos++; }
+    if (id.w >= 0) { s_idx[pos] = id.w; s_lk[pos] = (unsigned short)(lk + 3); pos++; }
+    if (p == kPasses - 1 && warp == 7) total = s_cnt[p * 8 + warp] + __popc(b0) + __popc(b1) + __popc(b2) + __popc(b3);
+  }
+  if (warp == 7 && lane == 0) s_work = total;
+  __syncthreads();
+  total = s_work;
+  // ---- phase 2b: one thread per surviving record: the gathers of consecutive records are independent (memory-level
+  //      parallelism), the two 16-byte stores of a warp are contiguous
+  for (int r = threadIdx.x; r < total; r += 256) {
+    const int ind = s_idx[r];
+    const int k = tile * kTilePix + (int)s_lk[r];
+    const float* xj = Xj + 3 * (size_t)k;
+    const float q = __ldg(Q + eb + k);
+    const size_t pos = eb + (size_t)base + r;
+    __stcs(&rec[pos].a, make_rec_a(kind, Xi, ind, width));
+    __stcs(&rec[pos].b, make_float4(__ldg(xj), __ldg(xj + 1), __ldg(xj + 2), sqrtf(q)));
   }
 }
 
@@ -337,27 +365,24 @@ __device__ __forceinline__ float act_row(const float* R, float t, const float4& 
   return fmaf(R[0], x.x, fmaf(R[1], x.y, fmaf(R[2], x.z, t)));
 }
 
-// Two records of one edge: residuals, weights, local Jacobian rows, accumulation.  Record B may be a padding lane
-// (sq.hi == 0, inputs copied from A): every weight is then exactly zero and every term finite.
-// xi.w = -1/|X_i| (pack_points_kernel): r_i and |X_i| cost no rsqrt chain here.
+// Two records of one edge: residuals, weights, local Jacobian rows, accumulation.  A padding lane carries sqrt(q) = 0
+// and a copy of a real record: every weight is then exactly zero and every term finite.
 template <int KIND, int ROBUST>
 __device__ __forceinline__ void pair_accumulate(V2 (&acc)[kAcc], const EdgeConst& c, const PixParams& pp,
-                                                const float4 xiA, const float4 xiB, const float4 xjA,
-                                                const float4 xjB, int indA, int indB, V2 sq) {
+                                                const float4 a0, const float4 a1, const float4 b0, const float4 b1,
+                                                V2 sq) {
   // P = s_ij R_ij X_j + t_ij: the edge constants are scalars, one FFMA per record and term
-  const V2 Px = pk(act_row(c.R + 0, c.t[0], xjA), act_row(c.R + 0, c.t[0], xjB));
-  const V2 Py = pk(act_row(c.R + 3, c.t[1], xjA), act_row(c.R + 3, c.t[1], xjB));
-  V2 Pz = pk(act_row(c.R + 6, c.t[2], xjA), act_row(c.R + 6, c.t[2], xjB));
+  const V2 Px = pk(act_row(c.R + 0, c.t[0], b0), act_row(c.R + 0, c.t[0], b1));
+  const V2 Py = pk(act_row(c.R + 3, c.t[1], b0), act_row(c.R + 3, c.t[1], b1));
+  V2 Pz = pk(act_row(c.R + 6, c.t[2], b0), act_row(c.R + 6, c.t[2], b1));
   V2 J[7];
   if (KIND == M3R_GN_RAYS) {
     const V2 n2j = fma2(Px, Px, fma2(Py, Py, mul2(Pz, Pz)));
     const V2 invj = rsqrt2(n2j);
     const V2 n1j = mul2(n2j, invj);
     const V2 rx = mul2(Px, invj), ry = mul2(Py, invj), rz = mul2(Pz, invj);
-    const V2 wi = pk(xiA.w, xiB.w);  // -1/|X_i|
-    const V2 e0 = fma2(pk(xiA.x, xiB.x), wi, rx), e1 = fma2(pk(xiA.y, xiB.y), wi, ry),
-             e2 = fma2(pk(xiA.z, xiB.z), wi, rz);
-    const V2 e3 = add2(n1j, rcp2(wi));  // |P| - |X_i|
+    const V2 e0 = sub2(rx, pk(a0.x, a1.x)), e1 = sub2(ry, pk(a0.y, a1.y)), e2 = sub2(rz, pk(a0.z, a1.z));
+    const V2 e3 = sub2(n1j, pk(a0.w, a1.w));  // |P| - |X_i|
     const V2 sw_ray = mul2(sq, bc(pp.sa_inv)), sw_dist = mul2(sq, bc(pp.sb_inv));
     const V2 wc_ray = mul2(sw_ray, sw_ray), wc_dist = mul2(sw_dist, sw_dist);
     const V2 w0 = mul2(robust_weight2<ROBUST>(mul2(sw_ray, e0)), wc_ray);
@@ -379,7 +404,7 @@ __device__ __forceinline__ void pair_accumulate(V2 (&acc)[kAcc], const EdgeConst
     J[0] = rx; J[1] = ry; J[2] = rz; J[6] = n1j;
     accum_row<0b1000111>(acc, J, w3, e3);
   } else if (KIND == M3R_GN_POINTS) {
-    const V2 e0 = sub2(Px, pk(xiA.x, xiB.x)), e1 = sub2(Py, pk(xiA.y, xiB.y)), e2 = sub2(Pz, pk(xiA.z, xiB.z));
+    const V2 e0 = sub2(Px, pk(a0.x, a1.x)), e1 = sub2(Py, pk(a0.y, a1.y)), e2 = sub2(Pz, pk(a0.z, a1.z));
     const V2 sw = mul2(sq, bc(pp.sa_inv));
     const V2 wc = mul2(sw, sw);
     const V2 w0 = mul2(robust_weight2<ROBUST>(mul2(sw, e0)), wc);
@@ -394,11 +419,11 @@ __device__ __forceinline__ void pair_accumulate(V2 (&acc)[kAcc], const EdgeConst
     J[3] = Py; J[4] = nPx; J[6] = Pz;
     accum_row<0b1011100>(acc, J, w2, e2);
   } else {  // M3R_GN_CALIB, gn_kernels.cu:1360-1479
-    // per-record validity (z > eps on both sides, projection inside the bordered image): an invalid record keeps finite
-    // stand-in values and gets sq = 0, i.e. weight exactly zero as in the reference (:1399-1404)
-    const bool zA = lo(Pz) > pp.z_eps && xiA.z > pp.z_eps, zB = hi(Pz) > pp.z_eps && xiB.z > pp.z_eps;
+    // per-record validity that depends on the poses (projected depth > eps, projection inside the bordered image): an
+    // invalid record keeps a finite stand-in depth and gets sq = 0, i.e. weight exactly zero as in the reference
+    // (:1399-1404); z_i > eps was gated by the pre-pass
+    const bool zA = lo(Pz) > pp.z_eps, zB = hi(Pz) > pp.z_eps;
     Pz = pk(zA ? lo(Pz) : 1.0f, zB ? hi(Pz) : 1.0f);
-    const float ziA = zA ? xiA.z : 1.0f, ziB = zB ? xiB.z : 1.0f;
     const V2 zj_inv = pk(1.0f / lo(Pz), 1.0f / hi(Pz));
     const V2 x = mul2(Px, zj_inv), y = mul2(Py, zj_inv);
     const V2 fx = bc(c.fx), fy = bc(c.fy);
@@ -408,10 +433,8 @@ __device__ __forceinline__ void pair_accumulate(V2 (&acc)[kAcc], const EdgeConst
     const bool okA = zA && lo(u) > ulo && lo(u) < uhi && lo(v) > ulo && lo(v) < vhi;
     const bool okB = zB && hi(u) > ulo && hi(u) < uhi && hi(v) > ulo && hi(v) < vhi;
     sq = pk(okA ? lo(sq) : 0.0f, okB ? hi(sq) : 0.0f);
-    const int vtA = indA / pp.width, vtB = indB / pp.width;
-    const int utA = indA - vtA * pp.width, utB = indB - vtB * pp.width;
-    const V2 e0 = sub2(u, pk((float)utA, (float)utB)), e1 = sub2(v, pk((float)vtA, (float)vtB));
-    const V2 e2 = pk(logf(lo(Pz)) - logf(ziA), logf(hi(Pz)) - logf(ziB));
+    const V2 e0 = sub2(u, pk(a0.x, a1.x)), e1 = sub2(v, pk(a0.y, a1.y));
+    const V2 e2 = pk(logf(lo(Pz)) - a0.z, logf(hi(Pz)) - a1.z);
     const V2 sw_pix = mul2(sq, bc(pp.sa_inv)), sw_dep = mul2(sq, bc(pp.sb_inv));
     const V2 wc_pix = mul2(sw_pix, sw_pix), wc_dep = mul2(sw_dep, sw_dep);
     const V2 w0 = mul2(robust_weight2<ROBUST>(mul2(sw_pix, e0)), wc_pix);
@@ -433,76 +456,42 @@ __device__ __forceinline__ void pair_accumulate(V2 (&acc)[kAcc], const EdgeConst
 
 // ------------------------------------------------------------------------------------------------ Hessian kernel
 // Persistent, stream-K style: the V = sum_e ecount[e] compacted records of all edges form one flat list; CTA c of the
-// grid (kHessCtasPerSm CTAs per SM) owns the records [c*chunk, (c+1)*chunk).  A CTA walks the (at most a few) edge
-// segments inside its range; per segment it builds the edge constants once, streams the records through a software
-// pipeline (records two batches ahead in registers, the gathered points one batch ahead in a cp.async shared-memory
-// ring), and reduces its 35 accumulators once: transposing butterfly across lanes (31 shuffles for 32 values), shared
-// memory across the warps.  The partial sums of segment (e, c) go to slot e + c, which is unique because consecutive
-// segments advance e, c or both; finalize_edge sums an edge's slots in fixed order (no atomics).
+// grid (kHessCtasPerSm CTAs per SM) owns the records [c*chunk, (c+1)*chunk) and walks the (at most a few) edge
+// segments inside its range.  Per segment: edge constants once; the records arrive in shared memory as tiles of
+// 2*kHessThreads through a kHessStages-deep ring of TMA bulk copies (cp.async.bulk + mbarrier: one elected thread arms
+// the barrier and issues two copies per tile, nothing else is spent on the transfer); every thread takes two records of
+// the tile (packed f32x2 arithmetic); 35 accumulators are reduced once per segment: transposing butterfly across lanes
+// (31 shuffles for 32 values), shared memory across the warps.  The partial sums of segment (e, c) go to slot e + c,
+// which is unique because consecutive segments advance e, c or both; finalize_edge sums an edge's slots in fixed order.
 // History (profiles/): v1 one CTA per 2048-px tile, latency-bound at 25 % occupancy; v2 8192-px tiles + pipelined
-// loads; v3 drops gated-out pixels in the pre-pass and amortises the serial edge set-up over ~1e5 records per CTA; v4
-// cp.async ring; v6 (this): two records per thread in packed f32x2 arithmetic, MUFU-only reciprocals, branch-free
-// Huber, pre-normalised X_i -- ~236 -> ~105 issue slots per record.
-struct RecBatch {
-  int2 r[2];
-  float sq[2];
-};
-
-__device__ __forceinline__ void load_recs(const EdgeRec* __restrict__ er, const float* __restrict__ es, int kb, int k1,
-                                          RecBatch& rb) {
-#pragma unroll
-  for (int u = 0; u < 2; u++) {
-    const int k = kb + u * kHessThreads;
-    rb.r[u] = make_int2(-1, 0);
-    rb.sq[u] = 0.0f;
-    if (k < k1) {
-      rb.r[u] = __ldcs(er + k);  // streamed once per iteration: evict-first in L2
-      rb.sq[u] = __ldcs(es + k);
-    }
-  }
-}
-
-// The gathered points go global -> shared memory with cp.async (LDGSTS), one batch ahead of the arithmetic, into a
-// two-slot per-thread ring: no registers are held by loads in flight.  A thread only ever touches its own slots, so
-// there is no barrier in the loop.  (r1: ring depth 1 / 2 / 3 / 4 = 99.4 / 101.3 / 103.0 / 105.1 us at 32 kf.)
-constexpr int kRingSlots = 2;
+// loads; v3 gated-out pixels dropped by the pre-pass, persistent CTAs; v4 gathered points through a cp.async ring
+// (issue-bound, 236 instructions per record); v6 packed f32x2 arithmetic, MUFU-only reciprocals, branch-free Huber (143
+// per record) -- no faster: the two 16-byte gathers per record saturated the L1TEX wavefront rate (~100 G records/s at 32
+// and at 256 keyframes alike, profiles/r2_hessian_v6_ncu_full.txt); v7 (this): the gathers moved into the once-per-solve
+// pre-pass, the kernel streams 32 self-contained bytes per record.
+#ifndef M3R_HESS_STAGES
+#define M3R_HESS_STAGES 4
+#endif
+constexpr int kHessStages = M3R_HESS_STAGES;
+constexpr int kHessTile = 2 * kHessThreads;  // records per ring stage
 struct HessRing {
-  float4 xi[kRingSlots][2][kHessThreads];
-  float4 xj[kRingSlots][2][kHessThreads];
-  float2 meta[kRingSlots][2][kHessThreads];  // (idx as int bits, sq)
+  GnRecord r[kHessStages][kHessTile];
+  unsigned long long full[kHessStages];   // tile landed (TMA transaction bytes)
+  unsigned long long empty[kHessStages];  // every warp has taken its records out of the stage
 };
 
-__device__ __forceinline__ void cp_async16(void* smem, const void* gmem) {
-  const unsigned sa = (unsigned)__cvta_generic_to_shared(smem);
-  // .cg (L2 only): the gathers have no L1 reuse (hit rate 10 %); with .ca the 256-keyframe case, whose 805 MB of
-  // points do not fit L2, ran 1.60 ms instead of 1.32 ms (r1)
-  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(sa), "l"(gmem) : "memory");
-}
-__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
-template <int N>
-__device__ __forceinline__ void cp_async_wait() {
-  asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory");
-}
-
-__device__ __forceinline__ void ring_issue(HessRing& ring, int slot, const float4* __restrict__ xci,
-                                           const float4* __restrict__ xcj, const RecBatch& rb) {
-#pragma unroll
-  for (int u = 0; u < 2; u++) {
-    ring.meta[slot][u][threadIdx.x] = make_float2(__int_as_float(rb.r[u].x), rb.sq[u]);
-    if (rb.r[u].x >= 0) {
-      cp_async16(&ring.xj[slot][u][threadIdx.x], xcj + rb.r[u].y);
-      cp_async16(&ring.xi[slot][u][threadIdx.x], xci + rb.r[u].x);
-    }
-  }
-  cp_async_commit();
-}
+constexpr int kHessMaxSeg = 8;  // edge segments planned at once by a CTA (more are handled in further rounds)
+struct HessPlan {
+  EdgeConst c[kHessMaxSeg];
+  int e[kHessMaxSeg], k0[kHessMaxSeg], k1[kHessMaxSeg];
+  int nseg, e_next;
+  long long p_next;
+};
 
 template <int KIND, int ROBUST>
 __global__ void __launch_bounds__(kHessThreads, kHessCtasPerSm) hessian_kernel(const float* __restrict__ Twc,
                                                                   const float* __restrict__ K,
-                                                                  const float4* __restrict__ xc,
-                                                                  const EdgeRec* __restrict__ rec,
-                                                                  const float* __restrict__ sqv,
+                                                                  const GnRecord* __restrict__ rec,
                                                                   const long long* __restrict__ eoff,
                                                                   const int* __restrict__ ie, const int* __restrict__ je,
                                                                   float* __restrict__ partial,
@@ -514,19 +503,27 @@ __global__ void __launch_bounds__(kHessThreads, kHessCtasPerSm) hessian_kernel(c
   long long p = (long long)blockIdx.x * chunk;
   const long long p_end = min(V, p + chunk);
   if (p >= p_end) return;
-  __shared__ EdgeConst s_c;
-  __shared__ int s_e;
-  __shared__ float s_red[kHessThreads / 32][kAccStride];
-  extern __shared__ __align__(16) unsigned char s_ring_raw[];
+  __shared__ HessPlan plan;
+  __shared__ float s_red[2][kHessThreads / 32][kAccStride];
+  extern __shared__ __align__(128) unsigned char s_ring_raw[];
   HessRing& ring = *reinterpret_cast<HessRing*>(s_ring_raw);
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  int e = -1;
+  if (threadIdx.x == 0) {
+#pragma unroll
+    for (int s = 0; s < kHessStages; s++) {
+      mbar_init(&ring.full[s], 1);
+      mbar_init(&ring.empty[s], kHessThreads / 32);
+    }
+  }
+  // tiles issued / consumed so far by this CTA: stage = count % kHessStages, phase parity from count / kHessStages
+  unsigned issued = 0, consumed = 0, nred = 0;
+  int e_cur = -1;
   while (p < p_end) {
-    // ---- next segment: thread 0 finds the edge that owns record p (binary search once, then a forward walk over
-    //      empty edges) and builds the edge constants
+    // ---- plan the next (up to kHessMaxSeg) edge segments of the CTA's record range: thread 0 finds the edge that owns
+    //      record p (binary search once, then a forward walk over empty edges) and the segment bounds ...
     if (threadIdx.x == 0) {
       int en;
-      if (e < 0) {
+      if (e_cur < 0) {
         int lo_e = 0, hi_e = num_edges - 1;  // last edge with eoff[edge] <= p
         while (lo_e < hi_e) {
           const int mid = (lo_e + hi_e + 1) >> 1;
@@ -534,100 +531,133 @@ __global__ void __launch_bounds__(kHessThreads, kHessCtasPerSm) hessian_kernel(c
         }
         en = lo_e;
       } else {
-        en = e + 1;
+        en = e_cur;
       }
-      while (eoff[en + 1] <= p) en++;
-      s_e = en;
-      edge_setup(Twc, ie[en], je[en], KIND == M3R_GN_CALIB ? K : nullptr, &s_c);
+      int n = 0;
+      long long q = p;
+      while (q < p_end && n < kHessMaxSeg) {
+        long long nxt;
+        while ((nxt = eoff[en + 1]) <= q) en++;
+        const long long b0 = eoff[en];
+        const long long seg_end = min(p_end, nxt);
+        plan.e[n] = en;
+        plan.k0[n] = (int)(q - b0);
+        plan.k1[n] = (int)(seg_end - b0);
+        n++;
+        q = seg_end;
+        en++;
+      }
+      plan.nseg = n;
+      plan.p_next = q;
+      plan.e_next = en;
     }
+    __syncthreads();  // also orders the mbarrier initialisation before their first use
+    // ... and one thread per segment builds its edge constants
+    const int nseg = plan.nseg;
+    if ((int)threadIdx.x < nseg)
+      edge_setup(Twc, ie[plan.e[threadIdx.x]], je[plan.e[threadIdx.x]], KIND == M3R_GN_CALIB ? K : nullptr,
+                 &plan.c[threadIdx.x]);
     __syncthreads();
-    e = s_e;
-    const EdgeConst c = s_c;
-    const long long e0 = eoff[e];
-    const long long seg_end = min(p_end, eoff[e + 1]);
-    const int k1 = (int)(seg_end - e0);
-    const float4* __restrict__ xci = xc + (size_t)ie[e] * num_pts;
-    const float4* __restrict__ xcj = xc + (size_t)je[e] * num_pts;
-    const EdgeRec* __restrict__ er = rec + (size_t)e * num_pts;
-    const float* __restrict__ es = sqv + (size_t)e * num_pts;
 
-    V2 acc2[kAcc];
-#pragma unroll
-    for (int i = 0; i < kAcc; i++) acc2[i] = bc(0.0f);
-    {
-      constexpr int kStep = 2 * kHessThreads;
-      int kb = (int)(p - e0) + threadIdx.x;
-      {  // prologue: gathers of batch 0 in flight, records of the next two batches in registers
-        RecBatch r0;
-        load_recs(er, es, kb, k1, r0);
-        ring_issue(ring, 0, xci, xcj, r0);
+    // Producer cursor (thread 0 only): the tiles of all planned segments form one sequence, so the ring keeps
+    // kHessStages - 1 tiles in flight ACROSS segment boundaries.  (Tried, r2: the role rotating over the warps, 83 ->
+    // 117 us; deeper rings, 4 -> 6 -> 8 stages: 83 -> 94 -> 100 us; an L2 prefetch 8 / 16 tiles ahead: 99 / 109 us; two
+    // tiles per loop trip: 88 us; two float4 streams instead of one 32-byte record stream: the same 83 us.)
+    int pseg = 0, pkb = plan.k0[0];
+    auto issue_next = [&]() {
+      if (pseg >= nseg) return;
+      const unsigned st = issued % kHessStages, round = issued / kHessStages;
+      if (round > 0) mbar_wait(&ring.empty[st], (round - 1) & 1);  // the stage's previous tile has been taken out
+      const int e = plan.e[pseg], k1 = plan.k1[pseg];
+      const unsigned bytes = (unsigned)min(kHessTile, k1 - pkb) * (unsigned)sizeof(GnRecord);
+#ifndef M3R_HESS_NOLOAD
+      mbar_arrive_expect_tx(&ring.full[st], bytes);
+      bulk_g2s(&ring.r[st][0], rec + (size_t)e * num_pts + pkb, bytes, &ring.full[st]);
+#endif
+      issued++;
+      pkb += kHessTile;
+      if (pkb >= k1) {
+        pseg++;
+        if (pseg < nseg) pkb = plan.k0[pseg];
       }
-      RecBatch ra, rb;
-      load_recs(er, es, kb + kStep, k1, ra);
-      load_recs(er, es, kb + 2 * kStep, k1, rb);
-      int slot = 0;
+    };
+    if (threadIdx.x == 0) {
+#pragma unroll
+      for (int i = 0; i < kHessStages - 1; i++) issue_next();
+    }
+
+    for (int sg = 0; sg < nseg; sg++) {
+      const EdgeConst c = plan.c[sg];
+      const int e = plan.e[sg], k0 = plan.k0[sg], k1 = plan.k1[sg];
+      const int ntiles = (k1 - k0 + kHessTile - 1) / kHessTile;
+      V2 acc2[kAcc];
+#pragma unroll
+      for (int i = 0; i < kAcc; i++) acc2[i] = bc(0.0f);
 #pragma unroll 2
-      for (; kb < k1; kb += kStep) {
-        RecBatch rc;
-        load_recs(er, es, kb + 3 * kStep, k1, rc);
-        cp_async_wait<0>();  // this batch has landed
-        const float2 mA = ring.meta[slot][0][threadIdx.x], mB = ring.meta[slot][1][threadIdx.x];
-        const float4 xiA = ring.xi[slot][0][threadIdx.x], xjA = ring.xj[slot][0][threadIdx.x];
-        float4 xiB = ring.xi[slot][1][threadIdx.x], xjB = ring.xj[slot][1][threadIdx.x];
-        ring_issue(ring, slot ^ 1, xci, xcj, ra);
-        // kb < k1 inside the loop, so record A always exists; records are dense, so B = A + kHessThreads can only be
-        // missing at the end of the segment: it becomes a padding lane, a copy of A with weight zero (no branch around
-        // the arithmetic: the 70 accumulator registers would have to be merged behind it)
-        const int idxA = __float_as_int(mA.x);
-        int idxB = __float_as_int(mB.x);
-        float sqB = mB.y;
-        if (idxB < 0) {
-          xiB = xiA;
-          xjB = xjA;
-          idxB = idxA;
-          sqB = 0.0f;
+      for (int t = 0; t < ntiles; t++) {
+        if (threadIdx.x == 0) issue_next();
+        const unsigned st = consumed % kHessStages;
+#ifndef M3R_HESS_NOLOAD  // experiment: compute side only (no copies issued, nothing to wait for)
+        mbar_wait(&ring.full[st], (consumed / kHessStages) & 1);
+#endif
+        // The tile holds cnt >= 1 records.  Every thread always computes: a thread without a record of its own re-reads
+        // the tile's last record with sqrt(q) = 0 (weight exactly zero, all terms finite) -- no branch around the
+        // arithmetic, whose 70 accumulator registers would otherwise have to be merged behind it.
+        const int cnt = min(kHessTile, k1 - (k0 + t * kHessTile));
+        const int i0 = min((int)threadIdx.x, cnt - 1), i1 = min((int)threadIdx.x + kHessThreads, cnt - 1);
+        const float4 a0 = ring.r[st][i0].a, b0 = ring.r[st][i0].b;
+        const float4 a1 = ring.r[st][i1].a, b1 = ring.r[st][i1].b;
+        __syncwarp();  // every lane has its records in registers; one arrival per warp frees the stage
+        if (lane == 0) mbar_arrive(&ring.empty[st]);
+        consumed++;
+        const float sq0 = (int)threadIdx.x < cnt ? b0.w : 0.0f;
+        const float sq1 = (int)threadIdx.x + kHessThreads < cnt ? b1.w : 0.0f;
+#ifdef M3R_HESS_NOCOMPUTE  // experiment: memory side only
+        acc2[0] = add2(acc2[0], pk(a0.x + b0.x + sq0, a1.x + b1.x + sq1));
+#else
+        pair_accumulate<KIND, ROBUST>(acc2, c, pp, a0, a1, b0, b1, pk(sq0, sq1));
+#endif
+      }
+      float acc[kAcc];
+#pragma unroll
+      for (int i = 0; i < kAcc; i++) acc[i] = lo(acc2[i]) + hi(acc2[i]);
+      // ---- block reduction: transposing butterfly for acc[0..31] (lane l ends up with the warp total of acc[l]),
+      //      plain xor-tree for the remaining kAcc-32 values, then the warps through shared memory (two buffers in
+      //      turn: the next segment's writers can only be one barrier ahead of this segment's readers)
+#pragma unroll
+      for (int s = 16; s >= 1; s >>= 1) {
+        const bool upper = (lane & s) != 0;
+#pragma unroll
+        for (int i = 0; i < s; i++) {
+          const float send = upper ? acc[i] : acc[i + s];
+          const float keep = upper ? acc[i + s] : acc[i];
+          acc[i] = keep + __shfl_xor_sync(0xffffffffu, send, s);
         }
-        pair_accumulate<KIND, ROBUST>(acc2, c, pp, xiA, xiB, xjA, xjB, idxA, idxB, pk(mA.y, sqB));
-        ra = rb;
-        rb = rc;
-        slot ^= 1;
       }
-      cp_async_wait<0>();  // drain before the next segment reuses the ring
-    }
-    float acc[kAcc];
+      float(*red)[kAccStride] = s_red[nred & 1];
+      nred++;
+      red[warp][lane] = acc[0];
 #pragma unroll
-    for (int i = 0; i < kAcc; i++) acc[i] = lo(acc2[i]) + hi(acc2[i]);
-    // ---- block reduction: transposing butterfly for acc[0..31] (lane l ends up with the warp total of acc[l]),
-    //      plain xor-tree for the remaining kAcc-32 values, then the warps through shared memory
+      for (int i = 32; i < kAcc; i++) {
+        float v = acc[i];
+        v += __shfl_xor_sync(0xffffffffu, v, 16);
+        v += __shfl_xor_sync(0xffffffffu, v, 8);
+        v += __shfl_xor_sync(0xffffffffu, v, 4);
+        v += __shfl_xor_sync(0xffffffffu, v, 2);
+        v += __shfl_xor_sync(0xffffffffu, v, 1);
+        if (lane == 0) red[warp][i] = v;
+      }
+      __syncthreads();
+      if (threadIdx.x < kAcc) {
+        float v = 0.0f;
 #pragma unroll
-    for (int s = 16; s >= 1; s >>= 1) {
-      const bool upper = (lane & s) != 0;
-#pragma unroll
-      for (int i = 0; i < s; i++) {
-        const float send = upper ? acc[i] : acc[i + s];
-        const float keep = upper ? acc[i + s] : acc[i];
-        acc[i] = keep + __shfl_xor_sync(0xffffffffu, send, s);
+        for (int wv = 0; wv < kHessThreads / 32; wv++) v += red[wv][threadIdx.x];
+        partial[(size_t)(e + (int)blockIdx.x) * kAccStride + threadIdx.x] = v;
       }
     }
-    s_red[warp][lane] = acc[0];
-#pragma unroll
-    for (int i = 32; i < kAcc; i++) {
-      float v = acc[i];
-      v += __shfl_xor_sync(0xffffffffu, v, 16);
-      v += __shfl_xor_sync(0xffffffffu, v, 8);
-      v += __shfl_xor_sync(0xffffffffu, v, 4);
-      v += __shfl_xor_sync(0xffffffffu, v, 2);
-      v += __shfl_xor_sync(0xffffffffu, v, 1);
-      if (lane == 0) s_red[warp][i] = v;
-    }
-    __syncthreads();
-    if (threadIdx.x < kAcc) {
-      float v = 0.0f;
-#pragma unroll
-      for (int wv = 0; wv < kHessThreads / 32; wv++) v += s_red[wv][threadIdx.x];
-      partial[(size_t)(e + (int)blockIdx.x) * kAccStride + threadIdx.x] = v;
-    }
-    p = seg_end;
+    p = plan.p_next;
+    e_cur = plan.e_next;
+    __syncthreads();  // the plan is rewritten by the next round
   }
 }
 
@@ -666,24 +696,30 @@ __global__ void export_blocks_kernel(const double* __restrict__ blocks, float* _
 
 // ------------------------------------------------------------------------------------------------ launchers
 int launch_pack_points(const GnWs& ws, const float* Xs, const float* Cs, float C_thresh, cudaStream_t st) {
+  (void)Xs;  // points are materialised per record by pack_edges; only the confidence scan is left of this pass
   const long long total = (long long)ws.L.num_kf * ws.L.num_pts;
   if (total == 0) return M3R_OK;
-  pack_points_kernel<<<(unsigned)ceil_div_ll(total, 256), 256, 0, st>>>(Xs, Cs, ws.xc(), total, C_thresh,
-                                                                        ws.state() + kCFail);
+  long long blocks = ceil_div_ll(total, 256 * 8);
+  if (blocks > 4 * sm_count()) blocks = 4 * sm_count();
+  conf_scan_kernel<<<(unsigned)blocks, 256, 0, st>>>(Cs, total, C_thresh, ws.state() + kCFail);
   M3R_LAUNCH_CHECK();
   return M3R_OK;
 }
 
-int launch_pack_edges(const GnWs& ws, const m3r_gn_params& p, const float* Cs, const int64_t* idx, const uint8_t* valid,
-                      const float* Q, cudaStream_t st) {
+int launch_pack_edges(const GnWs& ws, const m3r_gn_params& p, const float* Xs, const float* Cs, const int64_t* idx,
+                      const uint8_t* valid, const float* Q, cudaStream_t st) {
   const int E = ws.L.num_edges, tiles = ws.L.tiles;
   M3R_CUDA(cudaMemsetAsync(ws.ecount(), 0, sizeof(int) * (size_t)(E + 1), st));
   if (E > 0 && tiles > 0) {
     M3R_CUDA(cudaMemsetAsync(ws.tstate(), 0, sizeof(int) * ((size_t)E * tiles + 2), st));
-    pack_edges_kernel<<<(unsigned)((long long)E * tiles), 256, 0, st>>>(Cs, idx, valid, Q, ws.ie(), ws.je(), ws.rec(),
-                                                                          ws.sqv(), ws.ecount(), ws.tstate(),
-                                                                          ws.state() + kCFail, ws.L.num_pts, tiles,
-                                                                          p.C_thresh, p.Q_thresh);
+    static DynSmemOptIn attr;  // 48 KB dynamic + the static counters: above the default limit, opt in per device
+    {
+      const int rc = ensure_dyn_smem(pack_edges_kernel, 64 * 1024, attr);
+      if (rc != M3R_OK) return rc;
+    }
+    pack_edges_kernel<<<(unsigned)((long long)E * tiles), 256, kPackSmemBytes, st>>>(
+        Xs, Cs, idx, valid, Q, ws.ie(), ws.je(), ws.rec(), ws.ecount(), ws.tstate(), ws.state() + kCFail,
+        ws.L.num_pts, tiles, p.C_thresh, p.Q_thresh, p.kind, p.width > 0 ? p.width : 1, p.z_eps);
     M3R_LAUNCH_CHECK();
   }
   edge_offsets_kernel<<<1, 1024, 0, st>>>(ws.ecount(), ws.eoff(), E);
@@ -715,11 +751,11 @@ static int launch_hessian_kind(const GnWs& ws, const m3r_gn_params& p, const flo
   }
   if (p.robust == M3R_ROBUST_TUKEY)
     hessian_kernel<KIND, M3R_ROBUST_TUKEY><<<grid, kHessThreads, sizeof(HessRing), st>>>(
-        Twc, ws.Kdev(), ws.xc(), ws.rec(), ws.sqv(), ws.eoff(), ws.ie(), ws.je(), ws.partial(), ws.state(), ws.L.num_pts,
+        Twc, ws.Kdev(), ws.rec(), ws.eoff(), ws.ie(), ws.je(), ws.partial(), ws.state(), ws.L.num_pts,
         ws.L.num_edges, pp);
   else
     hessian_kernel<KIND, M3R_ROBUST_HUBER><<<grid, kHessThreads, sizeof(HessRing), st>>>(
-        Twc, ws.Kdev(), ws.xc(), ws.rec(), ws.sqv(), ws.eoff(), ws.ie(), ws.je(), ws.partial(), ws.state(), ws.L.num_pts,
+        Twc, ws.Kdev(), ws.rec(), ws.eoff(), ws.ie(), ws.je(), ws.partial(), ws.state(), ws.L.num_pts,
         ws.L.num_edges, pp);
   M3R_LAUNCH_CHECK();
   return M3R_OK;

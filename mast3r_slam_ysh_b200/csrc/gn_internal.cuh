@@ -18,7 +18,7 @@ constexpr int kTilePix = 8192;       // pixels of one edge compacted by one CTA 
 #endif
 constexpr int kHessThreads = M3R_HESS_THREADS;
 constexpr int kHessCtasPerSm = M3R_HESS_CTAS;
-constexpr int kHessChunkAlign = 2 * kHessThreads; // the Hessian kernel's per-CTA range of compacted records is a multiple of this
+constexpr int kHessChunkAlign = 512;  // the Hessian kernel's per-CTA range of compacted records is a multiple of this
 constexpr int kMaxHessCtas = 1024;   // upper bound on the persistent Hessian grid (2 CTAs per SM), sizes `partial`
 constexpr int kBlk = 32;             // Cholesky block size
 constexpr int kSmallMaxN = 224;      // largest system of the single-CTA shared-memory solver (gn_small.cuh)
@@ -66,14 +66,17 @@ struct PeerInfo {
 
 // Edge records produced once per solve by the packing pre-pass (iteration-invariant part of the per-pixel work).
 // Only pixels that pass every pose-independent gate (valid_match & q > Q_thresh & c_i > C_thresh & c_j > C_thresh,
-// gn_kernels.cu:953-957) get a record; the others contribute exactly zero in the reference (zero weight, :963-964)
-// and are dropped.  Records of edge e are compacted, in pixel order, into rec[e*num_pts + 0 .. ecount[e]):
-//   rec.x = index of the matched pixel in frame i, rec.y = pixel index k in frame j, sqv = sqrtf(q)
-typedef int2 EdgeRec;
+// gn_kernels.cu:953-957; calib: z_i > z_eps, :1368) get a record; the others contribute exactly zero in the reference
+// (zero weight, :963-964) and are dropped.  Records of edge e are compacted, in pixel order, into
+// rec[e*num_pts + 0 .. ecount[e]): 32 bytes holding everything the per-iteration kernel needs that does not depend on
+// the poses (layout per residual kind: make_rec_a in gn_hessian.cu) -- one contiguous stream per edge, no gather.
+struct __align__(32) GnRecord {
+  float4 a, b;
+};
 
 struct GnLayout {
   int num_kf, num_pts, num_edges, n_free, n, ld, nblk, tiles;
-  size_t off_xc, off_rec, off_ie, off_je, off_io, off_jo, off_partial, off_blocks, off_sqv, off_ecount, off_eoff, off_tstate, off_inc_off, off_inc_list, off_inc_other, off_sys,
+  size_t off_rec, off_ie, off_je, off_io, off_jo, off_partial, off_blocks, off_ecount, off_eoff, off_tstate, off_inc_off, off_inc_list, off_inc_other, off_sys,
       off_lfac, off_pflag, off_sky, off_dx, off_state, off_uniq_flag, off_all, off_K, total;
 };
 
@@ -82,9 +85,7 @@ GnLayout gn_layout(int num_kf, int num_pts, int num_edges, int num_all_edges);
 struct GnWs {
   GnLayout L;
   char* base;
-  float4* xc() const { return (float4*)(base + L.off_xc); }
-  EdgeRec* rec() const { return (EdgeRec*)(base + L.off_rec); }
-  float* sqv() const { return (float*)(base + L.off_sqv); }
+  GnRecord* rec() const { return (GnRecord*)(base + L.off_rec); }
   int* ecount() const { return (int*)(base + L.off_ecount); }      // [E] records per edge
   long long* eoff() const { return (long long*)(base + L.off_eoff); }  // [E+1] exclusive prefix of ecount
   int* tstate() const { return (int*)(base + L.off_tstate); }      // [0] ticket, [1 + e*tiles + t] chained-scan state
@@ -108,7 +109,7 @@ struct GnWs {
 
 // gn_hessian.cu
 int launch_pack_points(const GnWs& ws, const float* Xs, const float* Cs, float C_thresh, cudaStream_t st);
-int launch_pack_edges(const GnWs& ws, const m3r_gn_params& p, const float* Cs, const int64_t* idx, const uint8_t* valid,
+int launch_pack_edges(const GnWs& ws, const m3r_gn_params& p, const float* Xs, const float* Cs, const int64_t* idx, const uint8_t* valid,
                       const float* Q, cudaStream_t st);
 int hessian_grid();
 int launch_hessian(const GnWs& ws, const m3r_gn_params& p, const float* Twc, cudaStream_t st);

@@ -835,6 +835,15 @@ ORC_API int orc_gauss_newton(int kind, const float* params, int robust, int accu
   return it;
 }
 
+/* explicit thread count for the timed CPU baseline (a launcher may have exported OMP_NUM_THREADS=1) */
+ORC_API void orc_set_num_threads(int n) {
+#ifdef _OPENMP
+  if (n > 0) omp_set_num_threads(n);
+#else
+  (void)n;
+#endif
+}
+
 ORC_API int orc_num_threads(void) {
 #ifdef _OPENMP
   return omp_get_max_threads();

@@ -51,6 +51,12 @@ def num_threads():
     return int(lib().orc_num_threads())
 
 
+def set_num_threads(n):
+    """OpenMP threads of the oracle for the timed CPU baseline (torchrun exports OMP_NUM_THREADS=1)."""
+    lib().orc_set_num_threads(C.c_int(int(n)))
+    return num_threads()
+
+
 def f32_to_f16_bits(x):
     x = _c(x, np.float32)
     out = np.empty(x.shape, np.uint16)
