@@ -118,7 +118,7 @@ def cpu_gn_sample(n_gpus=1, device="cpu"):
     nkf = KF_PER_GPU * n_gpus
     edges = syn.ring_edges(nkf, SPAN)
     E_full = 2 * len(edges[0])
-    S = min(E_full, max(cores, 8))
+    S = min(E_full, max(8 * cores, 64))  # a few seconds of CPU work per step; the rest of the edges by scaling
     g = syn.make_gn_problem(nkf, H, W, edges, seed=1236, device=device, directed_subset=torch.arange(S),
                             yaw_step_deg=360.0 / KF_PER_GPU)
     a = [g[k].cpu().numpy() for k in ("Twc", "Xs", "Cs")]
@@ -218,6 +218,35 @@ def workload_config(n):
 
 
 # ====================================================================================================== our arm (GPU)
+def _event_time(torch, fn, reps, warm=3):
+    for _ in range(warm):
+        fn()
+    torch.cuda.synchronize()
+    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    a.record()
+    for _ in range(reps):
+        fn()
+    b.record()
+    torch.cuda.synchronize()
+    return a.elapsed_time(b) / reps
+
+
+def hessian_point(torch, md, _lib, P, g, kind="rays", extra_params=None, reps=20):
+    """The Hessian kernel alone on graph `g`: launch time (CUDA events on the launch stream), surviving records."""
+    import ctypes as C
+    if kind == "rays":
+        params = _lib.GnParams(_lib.M3R_GN_RAYS, _lib.M3R_ROBUST_HUBER, P[0], P[1], P[2], P[3], None, 0, 0, 0, 0.0,
+                               GN_ITERS, P[5])
+    else:
+        params = extra_params
+    sh = md.ShardedGaussNewton(params, g["Twc"].clone(), g["Xs"], g["Cs"], g["ii"], g["jj"], g["idx_ii2jj"],
+                               g["valid_match"], g["Q"], g["all_ii"], g["all_jj"], exchange="nccl")
+    ms = _event_time(torch, sh.hessian_pass, reps)
+    recs = int(sh.lib.m3r_gn_record_count(C.c_void_p(sh.ws_ptr), sh.num_kf, sh.num_pts, sh.E))
+    del sh
+    return ms, recs
+
+
 def run_ours(args):
     import torch
     import torch.distributed as dist
@@ -288,30 +317,38 @@ def run_ours(args):
     ms_per_step = total_ms / args.steps
     value = ms_per_step / max(iters, 1)
 
-    # ---- dominant kernel alone: per-pixel Hessian kernel over this rank's edges, CUDA events on the launch stream
-    params = _lib.GnParams(_lib.M3R_GN_RAYS, _lib.M3R_ROBUST_HUBER, P[0], P[1], P[2], P[3], None, 0, 0, 0, 0.0, GN_ITERS, P[5])
-    sh = md.ShardedGaussNewton(params, T0.clone(), Xs, Cs, ii, jj, idx, vm, Q, g["all_ii"], g["all_jj"])
-    for _ in range(3):
-        sh.hessian_pass()
-    torch.cuda.synchronize()
-    reps = 20
-    k0, k1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    k0.record()
-    for _ in range(reps):
-        sh.hessian_pass()
-    k1.record()
-    torch.cuda.synchronize()
-    hess_ms = k0.elapsed_time(k1) / reps
+    # ---- dominant kernel alone: the per-record Hessian kernel over this rank's edges, CUDA events on the launch stream
+    hess_ms, records = hessian_point(torch, md, _lib, P, dict(g, Twc=T0))
     clocks = sampler.summary() if rank == 0 else None
     peak, peak_src = measured_peak()
-    algo_bytes = ALGO_BYTES_PER_PIXEL_EDGE * N_PIX * E_local
+    algo_bytes = RECORD_BYTES * records
     achieved = algo_bytes / (hess_ms * 1e-3) / 1e9
-    del sh
+    pixel_edges = N_PIX * E_local
+    traffic = ncu_traffic()
+    input_bytes = INPUT_BYTES_PER_PIXEL_EDGE * pixel_edges + 16 * nkf * N_PIX  # read once per solve by the pre-pass
+    per_solve_bytes = input_bytes + RECORD_BYTES * records + iters * algo_bytes   # + records written once, read per iteration
+    roofline = dict(
+        bound="hbm", achieved=achieved, peak=peak, unit="GB/s", frac=achieved / peak, traffic=traffic,
+        kernel="hessian_kernel<RAYS,HUBER>", peak_source=peak_src, launch_ms=hess_ms,
+        unit_of_work="surviving (pixel, directed edge) record, %d B streamed per record and iteration" % RECORD_BYTES,
+        surviving_pixel_edges=records, pixel_edges=pixel_edges, survivor_share=records / max(pixel_edges, 1),
+        algorithmic_bytes_per_launch=algo_bytes,
+        dram_frac=(traffic / (hess_ms * 1e-3) / 1e9 / peak) if traffic else None,
+        traffic_over_algorithmic=(traffic / algo_bytes) if traffic and algo_bytes else None,
+        per_solve=dict(bytes=per_solve_bytes, gbs=per_solve_bytes / (ms_per_step * 1e-3) / 1e9,
+                       frac=per_solve_bytes / (ms_per_step * 1e-3) / 1e9 / peak,
+                       what="(inputs read once + records written once + iterations x records) / step time"),
+        reference_layout_equivalent_gbs=REF_LAYOUT_BYTES_PER_PIXEL_EDGE * pixel_edges / (hess_ms * 1e-3) / 1e9,
+        note="frac = records x 32 B / launch time / measured peak; traffic = DRAM bytes of one launch from the committed "
+             "ncu capture of the same workload (profiles/); reference_layout_equivalent_gbs = the 45 B per pixel-edge of "
+             "the reference's input layout (SURVEY 8d) over the same time -- not a roofline fraction, because pixels "
+             "that fail the pose-independent gates are dropped once per solve by the pre-pass (inside the timed step)")
 
     # ---- what the reference copies on the device before every solve (global_opt.py:104-119: torch.cat of both edge
     #      directions, torch.stack of every keyframe's pointmap / confidence); the graph-resident FactorGraph mirror
     #      (mast3r_slam_ysh_b200/global_opt.py) hands out views instead
     graph_prep = None
+    k0, k1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     if rank == 0 and world == 1:
         m = E_local // 2
 
@@ -338,6 +375,11 @@ def run_ours(args):
                           what="torch.cat of both edge directions + torch.stack of keyframe buffers vs views")
         torch.cuda.empty_cache()
 
+    # ---- the reference's own CUDA kernels on the same GPU and inputs (oracle/_ref; SURVEY 2b's bar)
+    ref_cuda = None
+    if rank == 0 and world == 1:
+        ref_cuda = reference_cuda_extra(torch, be, syn, dev, g, T0, P)
+
     # ---- e2e: pinned host buffers -> device -> solve -> poses/dx back to the host, every step
     host_in = [x.cpu().pin_memory() for x in (T0, Xs, Cs, ii, jj, idx, vm, Q)]
     h2d = sum(x.numel() * x.element_size() for x in host_in)
@@ -347,7 +389,7 @@ def run_ours(args):
     if world > 1:
         all_ii_h, all_jj_h = g["all_ii"].cpu().pin_memory(), g["all_jj"].cpu().pin_memory()
         h2d += 2 * all_ii_h.numel() * 8
-    del Xs, Cs, idx, vm, Q
+    del Xs, Cs, idx, vm, Q, g
     torch.cuda.empty_cache()
 
     def e2e_step():
@@ -364,7 +406,6 @@ def run_ours(args):
     for _ in range(2):
         e2e_step()
     barrier()
-    t0 = time.perf_counter()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
     e2e_steps = max(2, min(args.steps, 5))
@@ -379,11 +420,20 @@ def run_ours(args):
     del host_in
     torch.cuda.empty_cache()
 
+    # ---- BASELINE.json configs[4]: fixed 256-keyframe loop-closure graph + 256 pair matches, strong-scaled over the ranks
+    configs4 = configs4_extra(torch, dist, be, md, syn, dev, rank, world, P)
+
     extra = {}
     if rank == 0:
-        extra = matching_extra(be, syn, dev, torch)
-        extra["tracker"] = tracker_extra(syn, dev, torch)
-        extra["graph_prep"] = graph_prep
+        if world == 1:
+            extra = matching_extra(be, syn, dev, torch)
+            extra["tracker"] = tracker_extra(syn, dev, torch)
+            extra["graph_prep"] = graph_prep
+            extra["configs3_calib"] = configs3_extra(torch, be, md, _lib, syn, dev)
+            extra["hessian_dense_overlap"] = dense_overlap_extra(torch, md, _lib, syn, dev, P, peak)
+            extra["reference_cuda"] = ref_cuda
+            extra["cpu_tracker"] = cpu_tracker_baseline()
+        extra["configs4_strong_scaling"] = configs4
         extra["hessian_kernel_ms"] = hess_ms
         extra["solve_other_ms_per_iter"] = value - hess_ms
         extra["iterations_executed"] = iters
@@ -392,28 +442,180 @@ def run_ours(args):
         extra["linear_solver"] = ("single-CTA shared-memory Cholesky (n = %d)" % n_sys if n_sys <= 224 else
                                   "single-CTA envelope Cholesky, %d lanes (n = %d)" % (lanes, n_sys) if lanes > 0 else
                                   "dense multi-CTA Cholesky (n = %d)" % n_sys)
-        cpu_base = cpu_gn_sample(device=dev)[0] if world == 1 else None
+        cpu_base = cpu_gn_sample(1, device=dev)[0] if world == 1 else None
         line = dict(metric="gn_solve_ms_per_iter", value=value, unit="ms/iter", n_gpus=world, steps=args.steps,
                     warmup=args.warmup, ms_per_step=ms_per_step, higher_is_better=False, scaling="weak", vs_baseline=None,
                     dtype="f32 (fp64 reduction + Cholesky)", data="synthetic", config=workload_config(world),
                     clocks=clocks, gpu_launches=launches,
                     e2e=dict(value=e2e_val, unit="ms/iter", h2d_bytes_per_step=int(h2d), d2h_bytes_per_step=int(d2h)),
-                    roofline=dict(bound="hbm", achieved=achieved, peak=peak, unit="GB/s", frac=achieved / peak,
-                                  traffic=ncu_traffic(), kernel="hessian_kernel<RAYS,HUBER>", peak_source=peak_src,
-                                  algorithmic_bytes_per_launch=algo_bytes, launch_ms=hess_ms,
-                                  dram_frac=(ncu_traffic() / (hess_ms * 1e-3) / 1e9 / peak) if ncu_traffic() else None,
-                                  note="algorithmic bytes = 45 B x pixels x directed edges of the reference's input "
-                                       "layout (SURVEY 8d). frac > 1 is possible because the pose-independent gates "
-                                       "(valid_match, Q, C) are evaluated once per solve by the packing pre-pass and "
-                                       "only surviving pixels (12-byte records + L2-resident 16-byte points) are "
-                                       "streamed per iteration; dram_frac = ncu DRAM bytes per launch / launch time / "
-                                       "peak is what the kernel really pulls from HBM"),
-                    extra=extra)
+                    roofline=roofline, extra=extra)
         if cpu_base is not None:
             line["cpu_baseline"] = cpu_base
         print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()
+
+
+def reference_cuda_extra(torch, be, syn, dev, g2, T0, P):
+    """The reference's gn_kernels.cu / matching_kernels.cu compiled for sm_100a (oracle/build_ref.py -> oracle/_ref,
+    test infrastructure) timed with CUDA events on the same B200 and the same inputs as ours: GN configs[2] and
+    configs[3], iter_proj and refine_matches at b = 1."""
+    ref_dir = os.path.join(ROOT, "oracle", "_ref")
+    if ref_dir not in sys.path:
+        sys.path.insert(0, ref_dir)
+    try:
+        import mast3r_slam_backends_ref as ref
+    except Exception as ex:  # noqa
+        return dict(unavailable=repr(ex))
+    lo, mt = syn.LOCAL_OPT, syn.MATCHING
+    out = dict(what="reference CUDA (gn_kernels.cu, matching_kernels.cu, Eigen host solve) built for sm_100a, same GPU, "
+                    "same inputs, CUDA events; ms per GN iteration = solve time / 10 iterations")
+    a2 = [g2[k] for k in ("Xs", "Cs", "ii", "jj", "idx_ii2jj", "valid_match", "Q")]
+
+    def both(name, run_ref, run_ours, reps, per):
+        r = _event_time(torch, run_ref, reps, warm=1) / per
+        o = _event_time(torch, run_ours, reps, warm=1) / per
+        out[name] = dict(reference_ms=r, ours_ms=o, speedup=r / o)
+
+    both("gn_rays_configs2_ms_per_iter", lambda: ref.gauss_newton_rays(T0.clone(), *a2, *P),
+         lambda: be.gauss_newton_rays(T0.clone(), *a2, *P), 3, GN_ITERS)
+    g3 = syn.make_gn_problem(10, H, W, syn.ring_edges(10, 3, wrap=False), seed=1237, device=dev, calib=True,
+                             yaw_step_deg=10.0)
+    a3 = [g3[k] for k in ("Xs", "Cs")]
+    r3 = [g3[k] for k in ("ii", "jj", "idx_ii2jj", "valid_match", "Q")]
+    c3 = (H, W, lo["pixel_border"], lo["depth_eps"], lo["sigma_pixel"], lo["sigma_depth"], lo["C_conf"], lo["Q_conf"],
+          GN_ITERS, lo["delta_norm"])
+    both("gn_calib_configs3_ms_per_iter", lambda: ref.gauss_newton_calib(g3["Twc"].clone(), *a3, g3["K"], *r3, *c3),
+         lambda: be.gauss_newton_calib(g3["Twc"].clone(), *a3, g3["K"], *r3, *c3), 5, GN_ITERS)
+    del g3, a3, r3
+    m = syn.make_match_problem(1, H, W, seed=1235, device=dev)
+    rays, pts, p0 = m["rays_img_with_grad"], m["pts_3d_norm"], m["p_init"]
+    ia = (mt["max_iter"], mt["lambda_init"], mt["convergence_thresh"])
+    both("iter_proj_b1_ms", lambda: ref.iter_proj(rays, pts, p0, *ia), lambda: be.iter_proj(rays, pts, p0, *ia), 20, 1)
+    D11, D21 = m["D11"].half(), m["D21"].view(1, N_PIX, -1).half()
+    p1 = be.iter_proj(rays, pts, p0, *ia)[0].long()
+    both("refine_matches_b1_ms", lambda: ref.refine_matches(D11, D21, p1, mt["radius"], mt["dilation_max"]),
+         lambda: be.refine_matches(D11, D21, p1, mt["radius"], mt["dilation_max"]), 20, 1)
+    return out
+
+
+def configs3_extra(torch, be, md, _lib, syn, dev):
+    """BASELINE.json configs[3]: FactorGraph.solve_GN_calib, 10 keyframes, edges to the previous 3 -> E = 48, pinhole K,
+    points pre-constrained to the pixel rays (gn.cpp:54-82; global_opt.py:160-213)."""
+    lo = syn.LOCAL_OPT
+    g = syn.make_gn_problem(10, H, W, syn.ring_edges(10, 3, wrap=False), seed=1237, device=dev, calib=True,
+                            yaw_step_deg=10.0)
+    a = [g[k] for k in ("Xs", "Cs")]
+    r = [g[k] for k in ("ii", "jj", "idx_ii2jj", "valid_match", "Q")]
+    c = (H, W, lo["pixel_border"], lo["depth_eps"], lo["sigma_pixel"], lo["sigma_depth"], lo["C_conf"], lo["Q_conf"],
+         GN_ITERS, lo["delta_norm"])
+    info = {}
+
+    def run():
+        T = g["Twc"].clone()
+        (_,), info["i"] = be.gauss_newton_calib(T, *a, g["K"], *r, *c, return_info=True)
+        info["T"] = T
+    ms = _event_time(torch, run, 10)
+    iters = int(info["i"].cpu()[0])
+    params = _lib.GnParams(_lib.M3R_GN_CALIB, _lib.M3R_ROBUST_HUBER, lo["sigma_pixel"], lo["sigma_depth"], lo["C_conf"],
+                           lo["Q_conf"], g["K"].data_ptr(), H, W, lo["pixel_border"], lo["depth_eps"], GN_ITERS,
+                           lo["delta_norm"])
+    hess_ms, recs = hessian_point(torch, md, _lib, None, g, kind="calib", extra_params=params)
+    peak, _ = measured_peak()
+    return dict(workload="solve_GN_calib: 10 keyframes, 48 directed edges, 512x384, max_iter 10", solve_ms=ms,
+                iterations_executed=iters, ms_per_iter=ms / max(iters, 1), hessian_kernel_ms=hess_ms,
+                surviving_pixel_edges=recs, pixel_edges=48 * N_PIX,
+                hessian_hbm_frac=RECORD_BYTES * recs / (hess_ms * 1e-3) / 1e9 / peak,
+                gt_err_init=float((g["Twc"] - g["Twc_gt"]).abs().max()),
+                gt_err_final=float((info["T"] - g["Twc_gt"]).abs().max()))
+
+
+def dense_overlap_extra(torch, md, _lib, syn, dev, P, peak):
+    """The Hessian kernel when the compaction does not thin the work: configs[2]'s graph with a 2 deg yaw step (every
+    edge sees nearly the whole image), so that most pixels that pass the Q gate survive."""
+    nkf = KF_PER_GPU
+    g = syn.make_gn_problem(nkf, H, W, syn.ring_edges(nkf, SPAN), seed=1236, device=dev, yaw_step_deg=2.0)
+    ms, recs = hessian_point(torch, md, _lib, P, g, reps=10)
+    return dict(workload="configs[2] graph at a 2 deg yaw step", hessian_kernel_ms=ms, surviving_pixel_edges=recs,
+                pixel_edges=int(g["ii"].numel()) * N_PIX, survivor_share=recs / (int(g["ii"].numel()) * N_PIX),
+                hbm_frac=RECORD_BYTES * recs / (ms * 1e-3) / 1e9 / peak,
+                records_per_second=recs / (ms * 1e-3))
+
+
+def configs4_extra(torch, dist, be, md, syn, dev, rank, world, P):
+    """BASELINE.json configs[4] as written: a FIXED 256-keyframe loop-closure graph (consecutive + 3 loop-closure edges
+    per keyframe -> 1024 graph edges -> E = 2048 directed, synthetic.loop_closure_edges) solved by gauss_newton_rays
+    with the edges sharded over the N ranks, and 256 keyframe-pair matches (iter_proj + refine_matches, and the fused
+    match) split by pair.  Strong scaling: total work is the same at every N; times are device times, max over ranks."""
+    from mast3r_slam_ysh_b200 import matching as mm
+    nkf, n_pairs = 256, 256
+    edges = syn.loop_closure_edges(nkf, n_loop=3, seed=1238)
+    n_graph = len(edges[0])
+    lo_e, hi_e = md.partition_edges(n_graph, world)[rank]
+    sel = md.directed_slice(n_graph, lo_e, hi_e)
+    g = syn.make_gn_problem(nkf, H, W, edges, seed=1238, device=dev, directed_subset=sel if world > 1 else None,
+                            yaw_step_deg=360.0 / nkf)
+    a = [g[k] for k in ("Xs", "Cs", "ii", "jj", "idx_ii2jj", "valid_match", "Q")]
+    T0 = g["Twc"].clone()
+    keep = {}
+
+    def step():
+        T = T0.clone()
+        if world == 1:
+            (_,), keep["info"] = be.gauss_newton_rays(T, *a, *P, return_info=True)
+        else:
+            (_,), keep["info"] = md.gauss_newton_rays_sharded(T, *a, g["all_ii"], g["all_jj"], *P)
+        keep["T"] = T
+
+    def timed(fn, reps, warm):
+        for _ in range(warm):
+            fn()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(reps):
+            fn()
+        e1.record()
+        torch.cuda.synchronize()
+        t = torch.tensor([e0.elapsed_time(e1) / reps], device=dev, dtype=torch.float64)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    ms = timed(step, 3, 2)
+    info = keep["info"].cpu()
+    iters = int(info[0])
+    out = dict(workload="256-keyframe loop-closure graph, %d graph edges -> %d directed edges, 512x384, max_iter 10; "
+                        "256 pair matches" % (n_graph, 2 * n_graph), n_gpus=world,
+               gn_solve_ms=ms, gn_iterations_executed=iters, gn_ms_per_iter=ms / max(iters, 1),
+               gn_failed_factorisations=int(info[2]), solver_lanes=(int(info[3]) >> 24) & 15,
+               gn_gt_err_init=float((T0 - g["Twc_gt"]).abs().max()),
+               gn_gt_err_final=float((keep["T"] - g["Twc_gt"]).abs().max()))
+    del g, a, keep
+    torch.cuda.empty_cache()
+    # ---- 256 pair matches split by pair: 8 distinct synthetic pairs repeated to this rank's share
+    b_lo, b_hi = md.partition_pairs(n_pairs, world)[rank]
+    b_loc = b_hi - b_lo
+    m8 = syn.make_match_problem(8, H, W, seed=1239, device=dev)
+    rep = lambda t: t.repeat((b_loc + 7) // 8, *([1] * (t.dim() - 1)))[:b_loc].contiguous()
+    rays, pts, p0 = rep(m8["rays_img_with_grad"]), rep(m8["pts_3d_norm"]), rep(m8["p_init"])
+    D11h, D21h = rep(m8["D11"]).half(), rep(m8["D21"]).view(b_loc, N_PIX, -1).half()
+    mt = syn.MATCHING
+    t_unf = timed(lambda: md.match_pairs_sharded(rays, pts, p0, D11h, D21h, mt), 3, 1)
+    t_ip = timed(lambda: be.iter_proj(rays, pts, p0, mt["max_iter"], mt["lambda_init"], mt["convergence_thresh"]), 3, 1)
+    del rays, pts, p0, D11h, D21h
+    torch.cuda.empty_cache()
+    X11, X21, D11, D21 = rep(m8["X11"]), rep(m8["X21"]), rep(m8["D11"]), rep(m8["D21"])
+    t_fus = timed(lambda: mm.match(X11, X21, D11, D21), 3, 1)
+    del X11, X21, D11, D21, m8
+    torch.cuda.empty_cache()
+    out.update(pairs=n_pairs, pairs_per_rank=b_loc,
+               iter_proj_ms=t_ip, iter_proj_mpix_s=n_pairs * N_PIX / (t_ip * 1e-3) / 1e6,
+               iter_proj_plus_refine_ms=t_unf, iter_proj_plus_refine_mpix_s=n_pairs * N_PIX / (t_unf * 1e-3) / 1e6,
+               match_fused_ms=t_fus, match_fused_mpix_s=n_pairs * N_PIX / (t_fus * 1e-3) / 1e6)
+    return out
 
 
 def ncu_traffic():
@@ -428,42 +630,37 @@ def ncu_traffic():
 
 
 def matching_extra(be, syn, dev, torch):
-    """BASELINE.json's second metric: iter_proj (+ refine_matches) Mpix/s at 512x384, configs[1] (b=1) and b=8."""
+    """BASELINE.json's second metric: iter_proj (+ refine_matches, + the whole match()) Mpix/s at 512x384, configs[1]
+    (b = 1) and b = 8, 64, 256 (the bandwidth regime); b > 8 repeats 8 distinct synthetic pairs."""
+    from mast3r_slam_ysh_b200 import matching as mm
     mt = syn.MATCHING
     out = {}
-    for b in (1, 8):
-        m = syn.make_match_problem(b, H, W, seed=1235, device=dev)
-        rays, pts, p0 = m["rays_img_with_grad"], m["pts_3d_norm"], m["p_init"]
-        D11, D21 = m["D11"].half(), m["D21"].view(b, N_PIX, -1).half()
+    m8 = syn.make_match_problem(8, H, W, seed=1235, device=dev)
+    peak, _ = measured_peak()
+    for b in (1, 8, 64, 256):
+        rep = lambda t: t.repeat((b + 7) // 8, *([1] * (t.dim() - 1)))[:b].contiguous()
+        rays, pts, p0 = rep(m8["rays_img_with_grad"]), rep(m8["pts_3d_norm"]), rep(m8["p_init"])
+        D11, D21 = rep(m8["D11"]).half(), rep(m8["D21"]).view(b, N_PIX, -1).half()
         fn_ip = lambda: be.iter_proj(rays, pts, p0, mt["max_iter"], mt["lambda_init"], mt["convergence_thresh"])
         p1 = fn_ip()[0].long()
         fn_rf = lambda: be.refine_matches(D11, D21, p1, mt["radius"], mt["dilation_max"])
-        # whole match() of matching.py:8-91: fused device path (m3r_match) vs the reference's torch glue around the
-        # two drop-in kernels (SURVEY 8f rank 1)
-        from mast3r_slam_ysh_b200 import matching as mm
-        margs = (m["X11"], m["X21"], m["D11"], m["D21"])
-        fn_mf = lambda: mm.match(*margs)
-        fn_mu = lambda: mm.match_unfused(*margs)
+        fns = [("iter_proj", fn_ip), ("refine_matches", fn_rf)]
+        if b <= 64:
+            # whole match() of matching.py:8-91: fused device path (m3r_match) vs the reference's torch glue around the
+            # two drop-in kernels (SURVEY 8f rank 1)
+            margs = (rep(m8["X11"]), rep(m8["X21"]), rep(m8["D11"]), rep(m8["D21"]))
+            fns += [("match_fused", lambda: mm.match(*margs)), ("match_unfused_torch_glue", lambda: mm.match_unfused(*margs))]
         res = {}
-        for name, fn in (("iter_proj", fn_ip), ("refine_matches", fn_rf), ("match_fused", fn_mf),
-                         ("match_unfused_torch_glue", fn_mu)):
-            for _ in range(3):
-                fn()
-            torch.cuda.synchronize()
-            a, c = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-            reps = 20
-            a.record()
-            for _ in range(reps):
-                fn()
-            c.record()
-            torch.cuda.synchronize()
-            ms = a.elapsed_time(c) / reps
+        for name, fn in fns:
+            reps = 20 if b <= 8 else 5
+            ms = _event_time(torch, fn, reps, warm=2)
             res[name + "_ms"] = ms
             res[name + "_mpix_s"] = b * N_PIX / (ms * 1e-3) / 1e6
-        peak, _ = measured_peak()
         res["iter_proj_hbm_frac"] = ITER_PROJ_BYTES_PER_QUERY * b * N_PIX / (res["iter_proj_ms"] * 1e-3) / 1e9 / peak
         out[f"matching_b{b}"] = res
-        del m, rays, pts, p0, D11, D21, margs
+        del rays, pts, p0, D11, D21, p1, fns
+        margs = None
+        torch.cuda.empty_cache()
     return out
 
 
