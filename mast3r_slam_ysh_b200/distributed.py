@@ -184,31 +184,88 @@ class ShardedGaussNewton:
         return dx, info
 
 
-def gauss_newton_rays_sharded(Twc, Xs, Cs, local_ii, local_jj, idx_ii2jj, valid_match, Q, all_ii, all_jj, sigma_ray,
-                              sigma_dist, C_thresh, Q_thresh, max_iter, delta_thresh, group=None, exchange="auto"):
-    """gauss_newton_rays (gn.cpp:28-52) with the directed edges sharded over the ranks of `group`.
-    local_* are this rank's edges, all_ii/all_jj the concatenation over ranks (keyframe numbering must agree)."""
-    params = _lib.GnParams(_lib.M3R_GN_RAYS, _lib.M3R_ROBUST_HUBER, float(sigma_ray), float(sigma_dist), float(C_thresh),
-                           float(Q_thresh), None, 0, 0, 0, 0.0, int(max_iter), float(delta_thresh))
+def _gauss_newton_sharded(params, Twc, Xs, Cs, local_ii, local_jj, idx_ii2jj, valid_match, Q, all_ii, all_jj, max_iter,
+                          group, exchange, keep=()):
     s = ShardedGaussNewton(params, Twc, Xs, Cs, local_ii, local_jj, idx_ii2jj, valid_match, Q, all_ii, all_jj, group,
                            exchange)
+    s.keep = s.keep + tuple(keep)  # tensors the params struct points at must outlive the enqueued work
     for _ in range(int(max_iter)):
         s.iterate()
     dx, info = s.finish()
     return [dx], info
 
 
+def gauss_newton_rays_sharded(Twc, Xs, Cs, local_ii, local_jj, idx_ii2jj, valid_match, Q, all_ii, all_jj, sigma_ray,
+                              sigma_dist, C_thresh, Q_thresh, max_iter, delta_thresh, group=None, exchange="auto"):
+    """gauss_newton_rays (gn.cpp:28-52) with the directed edges sharded over the ranks of `group`.
+    local_* are this rank's edges, all_ii/all_jj the concatenation over ranks (keyframe numbering must agree)."""
+    params = _lib.GnParams(_lib.M3R_GN_RAYS, _lib.M3R_ROBUST_HUBER, float(sigma_ray), float(sigma_dist), float(C_thresh),
+                           float(Q_thresh), None, 0, 0, 0, 0.0, int(max_iter), float(delta_thresh))
+    return _gauss_newton_sharded(params, Twc, Xs, Cs, local_ii, local_jj, idx_ii2jj, valid_match, Q, all_ii, all_jj,
+                                 max_iter, group, exchange)
+
+
+def gauss_newton_points_sharded(Twc, Xs, Cs, local_ii, local_jj, idx_ii2jj, valid_match, Q, all_ii, all_jj, sigma_point,
+                                C_thresh, Q_thresh, max_iter, delta_thresh, group=None, exchange="auto"):
+    """gauss_newton_points (gn.cpp:3-26), edge-sharded like gauss_newton_rays_sharded."""
+    params = _lib.GnParams(_lib.M3R_GN_POINTS, _lib.M3R_ROBUST_HUBER, float(sigma_point), 1.0, float(C_thresh),
+                           float(Q_thresh), None, 0, 0, 0, 0.0, int(max_iter), float(delta_thresh))
+    return _gauss_newton_sharded(params, Twc, Xs, Cs, local_ii, local_jj, idx_ii2jj, valid_match, Q, all_ii, all_jj,
+                                 max_iter, group, exchange)
+
+
+def gauss_newton_calib_sharded(Twc, Xs, Cs, K, local_ii, local_jj, idx_ii2jj, valid_match, Q, all_ii, all_jj, height,
+                               width, pixel_border, z_eps, sigma_pixel, sigma_depth, C_thresh, Q_thresh, max_iter,
+                               delta_thresh, group=None, exchange="auto"):
+    """gauss_newton_calib (gn.cpp:54-82), edge-sharded like gauss_newton_rays_sharded; K (3,3) f32 on the device."""
+    params = _lib.GnParams(_lib.M3R_GN_CALIB, _lib.M3R_ROBUST_HUBER, float(sigma_pixel), float(sigma_depth),
+                           float(C_thresh), float(Q_thresh), K.data_ptr(), int(height), int(width), int(pixel_border),
+                           float(z_eps), int(max_iter), float(delta_thresh))
+    return _gauss_newton_sharded(params, Twc, Xs, Cs, local_ii, local_jj, idx_ii2jj, valid_match, Q, all_ii, all_jj,
+                                 max_iter, group, exchange, keep=(K,))
+
+
 # ------------------------------------------------------------------------------------------------ sharded matching
+def gather_ragged(t, group=None):
+    """All-gather along dim 0 with per-rank lengths that may differ (pairs are split by partition_pairs, the last ranks
+    may hold one pair less): pad to the longest, all_gather, trim, concatenate in rank order.  bool tensors travel as
+    uint8.  Identity without an initialised process group or at world size 1."""
+    if not (dist.is_available() and dist.is_initialized()) or dist.get_world_size(group) <= 1:
+        return t
+    ws = dist.get_world_size(group)
+    is_bool = t.dtype == torch.bool
+    src = t.to(torch.uint8) if is_bool else t
+    counts = torch.zeros(ws, dtype=torch.int64, device=t.device)
+    counts[dist.get_rank(group)] = t.shape[0]
+    dist.all_reduce(counts, group=group)
+    counts = counts.tolist()
+    cmax = max(int(c) for c in counts)
+    padded = torch.cat((src, src.new_zeros((cmax - src.shape[0],) + tuple(src.shape[1:]))), 0).contiguous()
+    outs = [torch.empty_like(padded) for _ in range(ws)]
+    dist.all_gather(outs, padded, group=group)
+    out = torch.cat([o[:int(c)] for o, c in zip(outs, counts)], 0)
+    return out.bool() if is_bool else out
+
+
 def match_pairs_sharded(rays_img_with_grad, pts_3d_norm, p_init, D11, D21, matching_cfg, group=None, gather=False):
-    """iter_proj + refine_matches on THIS rank's pairs (split by pair, no data-path collective).  With gather=True the
-    per-rank results are all-gathered (equal pair counts per rank required)."""
+    """iter_proj + refine_matches on THIS rank's pairs (split by pair with partition_pairs, no data-path collective:
+    pairs are independent units).  With gather=True the per-rank results are all-gathered in rank order
+    (ragged pair counts allowed), so that one rank can assemble the graph.  Returns (p1 (b,n,2) int64, converged (b,n))."""
     from . import backends as be
     p, conv = be.iter_proj(rays_img_with_grad, pts_3d_norm, p_init, matching_cfg["max_iter"],
                            matching_cfg["lambda_init"], matching_cfg["convergence_thresh"])
-    (p1,) = be.refine_matches(D11, D21, p.long(), matching_cfg["radius"], matching_cfg["dilation_max"])
-    if gather and dist.is_initialized() and dist.get_world_size(group) > 1:
-        ws = dist.get_world_size(group)
-        outs = [torch.empty_like(p1) for _ in range(ws)]
-        dist.all_gather(outs, p1, group=group)
-        p1 = torch.cat(outs, 0)
+    p1 = p.long()
+    if matching_cfg["radius"] > 0:
+        (p1,) = be.refine_matches(D11, D21, p1, matching_cfg["radius"], matching_cfg["dilation_max"])
+    if gather:
+        p1, conv = gather_ragged(p1, group), gather_ragged(conv, group)
     return p1, conv
+
+
+def match_sharded(X11, X21, D11, D21, idx_1_to_2_init=None, cfg=None, group=None, gather=False):
+    """The fused device match (matching.match == mast3r_slam/matching.py:8-10) on THIS rank's pairs; gather as above."""
+    from . import matching as mm
+    idx, valid = mm.match(X11, X21, D11, D21, idx_1_to_2_init, cfg)
+    if gather:
+        idx, valid = gather_ragged(idx, group), gather_ragged(valid, group)
+    return idx, valid

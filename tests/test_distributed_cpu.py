@@ -63,3 +63,35 @@ def test_sharded_system_allreduce_gloo(tmp_path):
     mp.spawn(_worker, args=(2, port, out), nprocs=2, join=True)
     rel, fail = np.load(out)
     assert fail == 0 and rel < 1e-6  # dx of the oracle is rounded to fp32
+
+
+def _gather_worker(rank, world, port, out):
+    sys.path.insert(0, ROOT)
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    from mast3r_slam_ysh_b200 import distributed as md
+    lo, hi = md.partition_pairs(5, world)[rank]           # 5 pairs over 2 ranks: 3 + 2 (ragged)
+    idx = torch.arange(lo, hi)[:, None].repeat(1, 4) * 10 + torch.arange(4)[None, :]
+    valid = (idx % 3 == 0)[..., None]
+    gi, gv = md.gather_ragged(idx), md.gather_ragged(valid)
+    if rank == 1:
+        want = torch.arange(5)[:, None].repeat(1, 4) * 10 + torch.arange(4)[None, :]
+        ok = torch.equal(gi, want) and torch.equal(gv, (want % 3 == 0)[..., None]) and gv.dtype == torch.bool
+        np.save(out, np.array([float(ok), gi.shape[0]]))
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def test_pair_sharded_gather_ragged_gloo(tmp_path):
+    """Pair-sharded matching (configs[4]: 256 pair matches split by pair): the optional result gather keeps rank order
+    and handles ragged pair counts; world size 2 over gloo."""
+    out = str(tmp_path / "gather.npy")
+    port = 31500 + os.getpid() % 2000
+    mp.spawn(_gather_worker, args=(2, port, out), nprocs=2, join=True)
+    ok, n = np.load(out)
+    assert ok == 1.0 and n == 5
+    from mast3r_slam_ysh_b200 import distributed as md
+    assert md.partition_pairs(256, 8) == [(32 * r, 32 * r + 32) for r in range(8)]
+    t = torch.arange(6)
+    assert md.gather_ragged(t) is t  # no process group: identity
