@@ -231,9 +231,10 @@ M3R_API int m3r_constrain_points_to_ray(const float* Xs, const float* K, float* 
                                         void* stream);
 
 /* Frame.update_pointmap (mast3r_slam/frame.py:41-105) for the running filters, in place on X_canon (n,3) / C (n):
- * mode 0 = "weighted_pointmap" (config default, :73-76), mode 1 = "indep_conf" (:68-72).  T = 8 floats [t, q, s] on the
+ * mode 0 = "weighted_pointmap" (config default, :73-76), mode 1 = "indep_conf" (:68-72), mode 2 = "weighted_spherical"
+ * (:76-101: confidence-weighted mean in (r, phi, theta), device libm trigonometry).  T = 8 floats [t, q, s] on the
  * device or NULL: when given, X_new is first moved by that Sim(3) (Xkk = T_CkCf.act(Xkf), tracker.py:96-97).  With
- * T == NULL the result is bit-identical to the reference's torch ops. */
+ * T == NULL modes 0 and 1 are bit-identical to the reference's torch ops. */
 M3R_API int m3r_update_pointmap(float* X_canon, float* C, const float* X_new, const float* C_new, const float* T,
                                 long long n, int mode, void* stream);
 

@@ -37,6 +37,24 @@ __global__ void __launch_bounds__(256) update_pointmap_kernel(float* __restrict_
     for (int k = 0; k < 3; k++)
       X[3 * i + k] = __fdiv_rn(__fadd_rn(__fmul_rn(c, X[3 * i + k]), __fmul_rn(cn, p[k])), den);
     Cc[i] = den;
+  } else if (mode == 2) {
+    // weighted_spherical (frame.py:76-101): confidence-weighted mean of (r, phi, theta) = (|P|, atan2(y, x), acos(z / r)),
+    // back to cartesian.  atan2f/acosf/sinf/cosf are the device libm versions: agreement with torch's CUDA ops to a few ulp
+    // of the angles (tests/test_gpu_geometry.py), not bit for bit.
+    const float den = __fadd_rn(c, cn);
+    const float x0 = X[3 * i], y0 = X[3 * i + 1], z0 = X[3 * i + 2];
+    const float r0 = sqrtf(__fadd_rn(__fadd_rn(__fmul_rn(x0, x0), __fmul_rn(y0, y0)), __fmul_rn(z0, z0)));
+    const float r1 = sqrtf(__fadd_rn(__fadd_rn(__fmul_rn(p[0], p[0]), __fmul_rn(p[1], p[1])), __fmul_rn(p[2], p[2])));
+    const float ph0 = atan2f(y0, x0), ph1 = atan2f(p[1], p[0]);
+    const float th0 = acosf(__fdiv_rn(z0, r0)), th1 = acosf(__fdiv_rn(p[2], r1));
+    const float r = __fdiv_rn(__fadd_rn(__fmul_rn(c, r0), __fmul_rn(cn, r1)), den);
+    const float ph = __fdiv_rn(__fadd_rn(__fmul_rn(c, ph0), __fmul_rn(cn, ph1)), den);
+    const float th = __fdiv_rn(__fadd_rn(__fmul_rn(c, th0), __fmul_rn(cn, th1)), den);
+    const float st = sinf(th);
+    X[3 * i] = __fmul_rn(__fmul_rn(r, st), cosf(ph));
+    X[3 * i + 1] = __fmul_rn(__fmul_rn(r, st), sinf(ph));
+    X[3 * i + 2] = __fmul_rn(r, cosf(th));
+    Cc[i] = den;
   } else if (cn > c) {
     X[3 * i] = p[0];
     X[3 * i + 1] = p[1];
@@ -79,7 +97,8 @@ extern "C" int m3r_constrain_points_to_ray(const float* Xs, const float* K, floa
 extern "C" int m3r_update_pointmap(float* X_canon, float* C, const float* X_new, const float* C_new, const float* T,
                                    long long n, int mode, void* stream) {
   M3R_REQUIRE(n >= 0, "update_pointmap: negative size");
-  M3R_REQUIRE(mode == 0 || mode == 1, "update_pointmap: mode must be 0 (weighted_pointmap) or 1 (indep_conf)");
+  M3R_REQUIRE(mode >= 0 && mode <= 2,
+              "update_pointmap: mode must be 0 (weighted_pointmap), 1 (indep_conf) or 2 (weighted_spherical)");
   if (n == 0) return M3R_OK;
   M3R_REQUIRE(X_canon && C && X_new && C_new, "update_pointmap: null pointer");
   update_pointmap_kernel<<<(unsigned)ceil_div_ll(n, 256), 256, 0, (cudaStream_t)stream>>>(X_canon, C, X_new, C_new, T, n,

@@ -27,7 +27,7 @@ def constrain_points_to_ray(img_size, Xs, K, out=None):
     return out.view(Xs.shape)
 
 
-_MODES = {"weighted_pointmap": 0, "indep_conf": 1}
+_MODES = {"weighted_pointmap": 0, "indep_conf": 1, "weighted_spherical": 2}
 
 
 def update_pointmap(X_canon, C, X_new, C_new, T=None, filtering_mode="weighted_pointmap"):

@@ -29,12 +29,16 @@ LOCAL_OPT = dict(pin=1, window_size=1e+6, C_conf=0.0, Q_conf=1.5, min_match_frac
 
 
 class KeyframeStore:
-    """Stacked keyframe buffers: X_canon (cap,N,3), average confidence (cap,N,1), T_WC (cap,8) [t, q_xyzw, s]."""
+    """Stacked keyframe buffers: X_canon (cap,N,3), ACCUMULATED confidence C (cap,N,1) with its update count N_upd (what
+    Frame keeps as self.C and self.N, frame.py:41-105), T_WC (cap,8) [t, q_xyzw, s].  The solver gets the AVERAGE confidence
+    C / N (Frame.get_average_conf, frame.py:107-108; global_opt.py:116) -- a view of C while every count is 1 (no fusion
+    happened, or only the modes that reset the count), one element-wise pass otherwise."""
 
     def __init__(self, num_points, capacity=64, device="cuda"):
         self.device = torch.device(device)
         self.N = int(num_points)
         self.n = 0
+        self._counts = []  # host copy of the update counts (the reference keeps Frame.N on the host as well)
         self._alloc(int(capacity))
 
     def _alloc(self, cap):
@@ -48,25 +52,45 @@ class KeyframeStore:
     def __len__(self):
         return self.n
 
-    def append(self, X_canon, C_avg, T_WC):
+    def append(self, X_canon, C, T_WC, N_updates=1):
+        """C: the keyframe's accumulated confidence, N_updates its count (Frame.C, Frame.N); 1 for a fresh keyframe."""
         if self.n == self.cap:
             self._alloc(2 * self.cap)
         k = self.n
         self.X[k] = X_canon.reshape(self.N, 3)
-        self.C[k] = C_avg.reshape(self.N, 1)
+        self.C[k] = C.reshape(self.N, 1)
         self.T_WC[k] = T_WC.reshape(8)
+        self._counts.append(int(N_updates))
         self.n += 1
         return k
 
-    def update_pointmap(self, k, X_canon, C_avg):
+    def update_pointmap(self, k, X_canon, C, N_updates=1):
+        """Replacement of keyframe k's pointmap (filtering modes first / recent / best_score, frame.py:53-66: N = 1)."""
         self.X[k] = X_canon.reshape(self.N, 3)
-        self.C[k] = C_avg.reshape(self.N, 1)
+        self.C[k] = C.reshape(self.N, 1)
+        self._counts[k] = int(N_updates)
 
     def fuse_pointmap(self, k, X_new, C_new, T=None, filtering_mode="weighted_pointmap"):
-        """Frame.update_pointmap (frame.py:41-105) on keyframe k's rows, in place, one kernel; `self.C` holds the
-        accumulated confidence as in the reference (get_average_conf divides by the update count, frame.py:107-108)."""
+        """Frame.update_pointmap (frame.py:41-105) on keyframe k's rows, in place, one kernel.  The weighted modes add the
+        new confidence to C and count the update (frame.py:74-75, :99-100); indep_conf resets the count to 1 (:71)."""
         geometry.update_pointmap(self.X[k], self.C[k], X_new.reshape(self.N, 3).contiguous(),
                                  C_new.reshape(self.N, 1).contiguous(), T, filtering_mode)
+        if filtering_mode in ("weighted_pointmap", "weighted_spherical"):
+            self._counts[k] += 1
+        else:
+            self._counts[k] = 1
+
+    def update_count(self, k):
+        return self._counts[k]
+
+    def average_conf(self, idx=None):
+        """C / N of keyframes idx (LongTensor) or of all: Frame.get_average_conf (frame.py:107-108)."""
+        ks = list(range(self.n)) if idx is None else [int(i) for i in idx.tolist()]
+        Cs = self.C[:self.n] if idx is None else self.C.index_select(0, idx)
+        if all(self._counts[k] == 1 for k in ks):
+            return Cs
+        cnt = torch.tensor([float(self._counts[k]) for k in ks], dtype=torch.float32, device=self.device)
+        return Cs / cnt.view(-1, 1, 1)
 
     def update_T_WCs(self, T_WCs, idx):
         """SharedKeyframes.update_T_WCs (frame.py:258-262): scatter (m,8) poses to keyframes idx."""
@@ -169,12 +193,13 @@ class FactorGraph:
         return e.ii[:E], e.jj[:E], e.idx[:E], e.valid[:E], e.Q[:E]
 
     def get_poses_points(self, unique_kf_idx):
-        """Xs, T_WCs (m,8), Cs of the keyframes that have edges; views of the store when those are 0..m-1."""
+        """Xs, T_WCs (m,8), average confidences of the keyframes that have edges (global_opt.py:112-119); views of the
+        store when those are 0..m-1 (and no keyframe has fused updates, see KeyframeStore.average_conf)."""
         m = unique_kf_idx.numel()
         if m == len(self.frames) and int(unique_kf_idx[-1]) == m - 1:
-            return self.frames.X[:m], self.frames.T_WC[:m], self.frames.C[:m], True
+            return self.frames.X[:m], self.frames.T_WC[:m], self.frames.average_conf(), True
         return (self.frames.X.index_select(0, unique_kf_idx), self.frames.T_WC.index_select(0, unique_kf_idx),
-                self.frames.C.index_select(0, unique_kf_idx), False)
+                self.frames.average_conf(unique_kf_idx), False)
 
     def _finish(self, pose_data, unique_kf_idx, in_place):
         pin = self.cfg["pin"]

@@ -87,3 +87,24 @@ def test_product_package_never_imports_oracle():
             if f.endswith((".py", ".cu", ".cuh", ".h")):
                 text = open(os.path.join(dirpath, f)).read()
                 assert "oracle" not in text.replace("# oracle", ""), f
+
+
+def test_compiled_binding_exports_the_reference_function_table():
+    """The compiled torch extension (csrc/ext/gn_b200.cpp) is the pybind module of gn.cpp:116-123: same five names, and
+    like the reference's CHECK_CONTIGUOUS (gn.h:5) it raises RuntimeError -- also for CPU tensors (no CPU path)."""
+    import importlib
+    mod = importlib.import_module("mast3r_slam_ysh_b200.mast3r_slam_backends_b200")
+    for name in ("gauss_newton_points", "gauss_newton_rays", "gauss_newton_calib", "iter_proj", "refine_matches"):
+        assert callable(getattr(mod, name))
+    with pytest.raises(RuntimeError, match="CUDA tensor"):
+        mod.iter_proj(torch.zeros(1, 4, 4, 9), torch.zeros(1, 2, 3), torch.zeros(1, 2, 2), 10, 1e-8, 1e-6)
+    with pytest.raises(RuntimeError, match="contiguous"):
+        mod.iter_proj(torch.zeros(1, 4, 9, 4).permute(0, 1, 3, 2), torch.zeros(1, 2, 3), torch.zeros(1, 2, 2), 10, 1e-8, 1e-6)
+    with pytest.raises(TypeError):  # positional signature of gn.h:112-117
+        mod.refine_matches(torch.zeros(1), torch.zeros(1))
+    import sys
+    sys.path.insert(0, ROOT)
+    import mast3r_slam_backends as shim
+    assert shim.BINDING in ("compiled", "ctypes")
+    if os.environ.get("M3R_BINDING", "auto") == "auto":
+        assert shim.BINDING == "compiled" and shim.iter_proj is mod.iter_proj

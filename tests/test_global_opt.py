@@ -105,14 +105,14 @@ def test_keyframe_store_growth_and_updates():
     assert s.T_WC[1].abs().sum() == 0 and s.T_WC[3].abs().sum() == 0 and s.T_WC[2, 0] == 2.0
 
 
-def _graph_from_problem(g, dev, batches=2):
+def _graph_from_problem(g, dev, batches=2, cfg=None):
     """Feed a synthetic problem's graph edges through add_factors_from_matches in `batches` calls."""
     from mast3r_slam_ysh_b200 import global_opt as go
     nkf, N = g["Xs"].shape[0], g["Xs"].shape[1]
     store = go.KeyframeStore(N, capacity=4, device=dev)
     for k in range(nkf):
         store.append(g["Xs"][k], g["Cs"][k], g["Twc"][k])
-    fg = go.FactorGraph(store, K=g["K"], device=dev)
+    fg = go.FactorGraph(store, K=g["K"], device=dev, cfg=cfg)
     m = g["ii"].numel() // 2
     ones = torch.ones((m, N, 1), device=dev)
     Qf, Qb = g["Q"][:m], g["Q"][m:]
@@ -182,3 +182,27 @@ def test_resident_graph_is_zero_copy_and_handles_unused_keyframes(be):
     fg.solve_GN_rays()
     assert torch.equal(store.T_WC[5], before[5]) and torch.equal(store.T_WC[0], before[0])
     assert (store.T_WC[1:5] - before[1:5]).abs().max() > 1e-4
+
+
+@pytest.mark.gpu
+def test_solver_gets_average_confidence_after_fusion(be, orc):
+    """C_conf > 0: after a weighted pointmap fusion the confidence gate must see C / N (frame.py:107-108, global_opt.py:116),
+    not the accumulated sum -- checked against the oracle run on the averaged confidences."""
+    import numpy as np
+    from mast3r_slam_ysh_b200 import global_opt as go, synthetic as syn
+    dev = torch.device("cuda:0")
+    g = syn.make_gn_problem(5, 24, 32, syn.ring_edges(5, 2, wrap=False), seed=6, device=dev, yaw_step_deg=9.0)
+    c_gate = float(g["Cs"].median())
+    fg, store = _graph_from_problem(g, dev, batches=1, cfg=dict(C_conf=c_gate))
+    # fuse a second observation into keyframe 2: accumulated C doubles (every point would now pass the gate on the sum),
+    # its average stays where it was
+    store.fuse_pointmap(2, g["Xs"][2], g["Cs"][2])
+    assert store.update_count(2) == 2 and float((store.C[2] > c_gate).float().mean()) > 0.95
+    Cs_avg = store.average_conf()
+    assert torch.allclose(Cs_avg[2], g["Cs"][2]) and Cs_avg.data_ptr() != store.C.data_ptr()
+    T_o = g["Twc"].cpu().numpy().copy()
+    lo = fg.cfg
+    orc.gauss_newton_rays(T_o, store.X[:5].cpu().numpy(), Cs_avg.cpu().numpy(), *[t.cpu().numpy() for t in fg.prep_two_way_edges()],
+                          lo["sigma_ray"], lo["sigma_dist"], lo["C_conf"], lo["Q_conf"], lo["max_iters"], lo["delta_norm"])
+    fg.solve_GN_rays()
+    assert np.linalg.norm(store.T_WC[:5].cpu().numpy() - T_o) / np.linalg.norm(T_o) <= 1e-4

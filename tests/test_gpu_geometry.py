@@ -67,7 +67,32 @@ def test_update_pointmap_with_pose_matches_act_then_merge():
     geometry.update_pointmap(Xc, Cc, X, C, T=T)
     assert torch.allclose(Xc, X_ref, rtol=0, atol=2e-6)
     with pytest.raises(NotImplementedError):
-        geometry.update_pointmap(Xc, Cc, X, C, filtering_mode="weighted_spherical")
+        geometry.update_pointmap(Xc, Cc, X, C, filtering_mode="best_score")  # a plain copy in the reference, no kernel
+
+
+def test_update_pointmap_weighted_spherical_vs_reference_formulas():
+    """filtering_mode 'weighted_spherical' (frame.py:76-101): the reference's own torch expressions on the same device."""
+    from mast3r_slam_ysh_b200 import geometry
+    g = torch.Generator().manual_seed(9)
+    n = 384 * 512 + 3
+    Xc = (torch.randn(n, 3, generator=g) + torch.tensor([0.0, 0.0, 3.0])).cuda()
+    X = (Xc.cpu() + 0.02 * torch.randn(n, 3, generator=g)).cuda()
+    Cc, C = (1.0 + 3.0 * torch.rand(n, 1, generator=g)).cuda(), (1.0 + 3.0 * torch.rand(n, 1, generator=g)).cuda()
+
+    def cartesian_to_spherical(P):
+        r = torch.linalg.norm(P, dim=-1, keepdim=True)
+        x, y, z = torch.tensor_split(P, 3, dim=-1)
+        return torch.cat((r, torch.atan2(y, x), torch.acos(z / r)), dim=-1)
+
+    def spherical_to_cartesian(sph):
+        r, phi, theta = torch.tensor_split(sph, 3, dim=-1)
+        return torch.cat((r * torch.sin(theta) * torch.cos(phi), r * torch.sin(theta) * torch.sin(phi), r * torch.cos(theta)), dim=-1)
+
+    sph = ((Cc * cartesian_to_spherical(Xc)) + (C * cartesian_to_spherical(X))) / (Cc + C)
+    X_ref, C_ref = spherical_to_cartesian(sph), Cc + C
+    geometry.update_pointmap(Xc, Cc, X, C, filtering_mode="weighted_spherical")
+    assert torch.equal(Cc, C_ref)
+    assert float((Xc - X_ref).abs().max()) <= 2e-6 * float(X_ref.abs().max())
 
 
 def test_keyframe_store_fuse_pointmap():
@@ -77,5 +102,10 @@ def test_keyframe_store_fuse_pointmap():
     X0, C0 = torch.randn(100, 3, generator=g).cuda(), (1 + torch.rand(100, 1, generator=g)).cuda()
     s.append(X0, C0, torch.tensor([0, 0, 0, 0, 0, 0, 1, 1.0]).cuda())
     X1, C1 = torch.randn(100, 3, generator=g).cuda(), (1 + torch.rand(100, 1, generator=g)).cuda()
+    assert s.average_conf().data_ptr() == s.C.data_ptr()  # count 1 everywhere: a view, no copy
     s.fuse_pointmap(0, X1, C1)
     assert torch.equal(s.X[0], ((C0 * X0) + (C1 * X1)) / (C0 + C1)) and torch.equal(s.C[0], C0 + C1)
+    # Frame.get_average_conf (frame.py:107-108): C / N with N = 2 after one weighted update
+    assert s.update_count(0) == 2 and torch.equal(s.average_conf()[0], (C0 + C1) / 2)
+    s.fuse_pointmap(0, X1, 10 * C1, filtering_mode="indep_conf")  # frame.py:68-72: N back to 1
+    assert s.update_count(0) == 1 and torch.equal(s.average_conf()[0], s.C[0])

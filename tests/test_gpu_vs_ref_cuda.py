@@ -99,7 +99,7 @@ def test_reference_matching_py_unchanged_over_the_shim(be, ref):
     from mast3r_slam.config import config, load_config
     load_config(os.path.join(pyref, "config", "base.yaml"))
     import mast3r_slam.matching as ref_matching
-    assert ref_matching.mast3r_slam_backends is shim and shim.iter_proj is be.iter_proj
+    assert ref_matching.mast3r_slam_backends is shim  # compiled pybind module if built, else the ctypes mirror
     from mast3r_slam_ysh_b200 import matching as mm
     syn = _syn()
     out = {}
@@ -107,12 +107,15 @@ def test_reference_matching_py_unchanged_over_the_shim(be, ref):
         m = syn.make_match_problem(b, h, w, seed=31 + b + h, device=DEV, warm_start=warm, point_noise=noise)
         idx0 = (m["p_init"][..., 0] + w * m["p_init"][..., 1]).long() if warm else None
         a = (m["X11"], m["X21"], m["D11"], m["D21"], idx0)
-        idx_s, val_s = ref_matching.match(*a)                       # reference Python + our kernels
-        ref_matching.mast3r_slam_backends = ref
+        idx_s, val_s = ref_matching.match(*a)                       # reference Python + our kernels (shim as imported)
         try:
+            ref_matching.mast3r_slam_backends = be
+            idx_c, val_c = ref_matching.match(*a)                   # reference Python + the ctypes mirror
+            ref_matching.mast3r_slam_backends = ref
             idx_r, val_r = ref_matching.match(*a)                   # reference Python + reference CUDA
         finally:
             ref_matching.mast3r_slam_backends = shim
+        assert torch.equal(idx_c, idx_s) and torch.equal(val_c, val_s)
         idx_u, val_u = mm.match_unfused(*a)                         # our restatement of the glue
         idx_f, val_f = mm.match(*a)                                 # fused device path
         torch.cuda.synchronize()
@@ -129,6 +132,7 @@ def test_reference_matching_py_unchanged_over_the_shim(be, ref):
         assert torch.equal(idx_u, idx_s) and torch.equal(val_u, val_s)
         if noise == 0.0:  # rough (noisy) ray images make non-converged LM steps chaotic in the last bit, DESIGN 3.5
             assert fused_same >= 0.998 and fused_val >= 0.998, (fused_same, fused_val)
+    out["binding"] = shim.BINDING
     RESULTS["reference_matching_py_over_shim"] = out
     assert config["matching"]["radius"] == 3
 
