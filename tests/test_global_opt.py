@@ -194,10 +194,10 @@ def test_solver_gets_average_confidence_after_fusion(be, orc):
     g = syn.make_gn_problem(5, 24, 32, syn.ring_edges(5, 2, wrap=False), seed=6, device=dev, yaw_step_deg=9.0)
     c_gate = float(g["Cs"].median())
     fg, store = _graph_from_problem(g, dev, batches=1, cfg=dict(C_conf=c_gate))
-    # fuse a second observation into keyframe 2: accumulated C doubles (every point would now pass the gate on the sum),
+    # fuse a second observation into keyframe 2: accumulated C doubles (most points would now pass the gate on the sum),
     # its average stays where it was
     store.fuse_pointmap(2, g["Xs"][2], g["Cs"][2])
-    assert store.update_count(2) == 2 and float((store.C[2] > c_gate).float().mean()) > 0.95
+    assert store.update_count(2) == 2 and float((store.C[2] > c_gate).float().mean()) > 0.75  # vs ~0.5 for the average
     Cs_avg = store.average_conf()
     assert torch.allclose(Cs_avg[2], g["Cs"][2]) and Cs_avg.data_ptr() != store.C.data_ptr()
     T_o = g["Twc"].cpu().numpy().copy()
