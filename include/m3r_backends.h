@@ -74,6 +74,12 @@ M3R_API int m3r_iter_proj(const float* rays_img_with_grad, const float* pts_3d_n
  * ------------------------------------------------------------------------------------------------------- */
 M3R_API int m3r_refine_matches_f16(const uint16_t* D11, const uint16_t* D21, const int64_t* p1, int64_t* p1_new, int b,
                            int h, int w, int n, int fdim, int radius, int dilation_max, void* stream);
+/* refine_matches kernel selection (process-wide): 0 = one thread per query gathering its candidates (default), 1 = where
+ * the queries are the pixel grid of the image (n == h*w, radius 3, fdim 16/24) the tile-staged kernel: a CTA per 16x16
+ * query tile, the D11 window of each dilation level fetched by a TMA tensor copy and scored from shared memory.  Same
+ * arithmetic and scan order, bit-identical results; -1 = decided by the environment (M3R_REFINE_TILE).  No reference
+ * counterpart (matching_kernels.cu:84-116 has one kernel). */
+M3R_API void m3r_debug_set_refine_mode(int mode);
 M3R_API int m3r_refine_matches_f32(const float* D11, const float* D21, const int64_t* p1, int64_t* p1_new, int b, int h,
                            int w, int n, int fdim, int radius, int dilation_max, void* stream);
 

@@ -42,6 +42,7 @@ SYMBOLS = {
     "m3r_launch_count": (C.c_uint64, []),
     "m3r_debug_set_timeline": (None, [_vp, _i]),
     "m3r_debug_set_solver": (None, [_i]),
+    "m3r_debug_set_refine_mode": (None, [_i]),
     "m3r_debug_solver_lanes": (_i, [_vp]),
     "m3r_iter_proj": (_i, [_vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _f, _f, _vp]),
     "m3r_refine_matches_f16": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _vp]),

@@ -169,6 +169,34 @@ __device__ __forceinline__ float score_f16(const __half2* q, const uint4* t) {
   return __half2float(score);
 }
 
+// NJ candidates at once, their rounding chains interleaved: each candidate's score is the same serial sequence of
+// 2 * FDIM/2 rounded additions as in score_f16 (so the results are bit-identical), but the NJ chains are independent and
+// are issued round-robin -- one chain alone is 24-48 dependent HADD2 with nothing to overlap them.
+template <int NV, int NJ>
+__device__ __forceinline__ void score_f16_multi(const __half2* q, const uint4 (&t)[NJ][NV], float (&out)[NJ]) {
+  __half sc[NJ];
+#pragma unroll
+  for (int j = 0; j < NJ; j++) sc[j] = __ushort_as_half(0);
+#pragma unroll
+  for (int k = 0; k < NV; k++) {
+#pragma unroll
+    for (int c = 0; c < 4; c++) {
+      __half2 pr[NJ];
+#pragma unroll
+      for (int j = 0; j < NJ; j++) {
+        const unsigned wv = c == 0 ? t[j][k].x : c == 1 ? t[j][k].y : c == 2 ? t[j][k].z : t[j][k].w;
+        pr[j] = __hmul2_rn(q[4 * k + c], *reinterpret_cast<const __half2*>(&wv));
+      }
+#pragma unroll
+      for (int j = 0; j < NJ; j++) sc[j] = __hadd_rn(sc[j], __low2half(pr[j]));
+#pragma unroll
+      for (int j = 0; j < NJ; j++) sc[j] = __hadd_rn(sc[j], __high2half(pr[j]));
+    }
+  }
+#pragma unroll
+  for (int j = 0; j < NJ; j++) out[j] = __half2float(sc[j]);
+}
+
 // RADIUS > 0: compile-time radius; the 2*RADIUS+1 candidates of one scan column are fetched together (all their loads
 // in flight before the first score is reduced) -- the kernel is bound by dependent L1/L2 round trips, one candidate
 // at a time, otherwise.  RADIUS == 0: run-time radius, one candidate at a time.  Scan order and the strict-greater
@@ -198,12 +226,12 @@ __device__ __forceinline__ void refine_core_f16(const __half2 (&q)[FDIM / 2], co
 #pragma unroll
           for (int k = 0; k < NV; k++) t[jj][k] = in[jj] ? __ldg(c + (size_t)k * cstride) : make_uint4(0, 0, 0, 0);
         }
+        float sc[NJ];
+        score_f16_multi<NV, NJ>(q, t, sc);
 #pragma unroll
         for (int jj = 0; jj < NJ; jj++) {
-          if (!in[jj]) continue;
-          const float s = score_f16<NV>(q, t[jj]);
-          if (s > max_score) {
-            max_score = s;
+          if (in[jj] && sc[jj] > max_score) {
+            max_score = sc[jj];
             u_new = u;
             v_new = v0 - rd + jj * d;
           }

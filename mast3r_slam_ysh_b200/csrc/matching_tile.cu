@@ -1,0 +1,190 @@
+// Tile-staged refine_matches for sm_100a (opt-in variant of the per-thread gathers of matching.cu, for queries that form
+// the h x w grid of an image, which is how every caller of the reference uses it: matching.py:79-85, n == h * w).
+//
+// refine_matches_kernel (matching_kernels.cu:25-81) scores 245 candidates of 48 bytes per query: 11.8 KB of scattered
+// 16-byte loads per query through L1 (l1tex 97 % busy, profiles/r1_refine_v1_ncu_full.txt), although neighbouring queries
+// look at nearly the same window of D11.  Here a CTA owns a 16 x 16 tile of query pixels.  Per dilation level it
+//   1. takes the mean of its queries' current centres (one block reduction),
+//   2. has ONE thread fetch the box of D11 around that mean with a 4-D TMA tensor copy (cp.async.bulk.tensor, SASS
+//      UTMALDG; 48 x 48 pixels for the wide levels, 32 x 32 for the narrow ones; out-of-image pixels are zero-filled by
+//      the copy engine), completion on an mbarrier,
+//   3. scores out of shared memory: every query whose whole (2 r d + 1)^2 window lies inside the box reads its candidates
+//      with LDS.128 (48-byte pixel pitch: conflict-free for neighbouring pixels), the others -- stragglers whose centre
+//      left the neighbourhood -- fall back to global loads,
+//   4. recentres (matching_kernels.cu:75-76) and goes on to the next level.
+// Arithmetic, scan order and the strict-greater argmax are those of matching_core.cuh (score_f16_multi, u offset outer, v
+// offset inner), so the result is bit-identical to the gather kernel and to the reference.
+#include <cuda_fp16.h>
+
+#include "matching_core.cuh"
+#include "tensormap.cuh"
+
+namespace m3r {
+
+constexpr int kRtQ = 16;        // query tile edge
+constexpr int kRtThreads = kRtQ * kRtQ;
+constexpr int kRtBoxBig = 48;   // box edge for levels with 16 + 2 r d <= 48
+constexpr int kRtBoxSmall = 32;
+
+template <int FDIM>
+struct RefineTileSmem {
+  uint4 tile[kRtBoxBig * kRtBoxBig * (FDIM / 8)];  // dense box, row pitch box * FDIM * 2 bytes
+  unsigned long long bar;
+  int red[3][kRtThreads / 32];
+  int origin[3];  // ox, oy, box edge (0: no box this level)
+};
+
+template <int FDIM, int RADIUS>
+__global__ void __launch_bounds__(kRtThreads, 2)
+    refine_matches_tile_kernel(const __grid_constant__ CUtensorMap map_big, const __grid_constant__ CUtensorMap map_small,
+                               const uint4* __restrict__ D11, const uint4* __restrict__ D21,
+                               const longlong2* __restrict__ p1, longlong2* __restrict__ p1_new, int h, int w,
+                               int dilation_max) {
+  constexpr int NV = FDIM / 8;
+  constexpr int NJ = 2 * RADIUS + 1;
+  extern __shared__ __align__(128) unsigned char s_raw[];
+  RefineTileSmem<FDIM>& sm =  // TMA destinations must be 128-byte aligned
+      *reinterpret_cast<RefineTileSmem<FDIM>*>(s_raw + ((128u - (smem_u32(s_raw) & 127u)) & 127u));
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int b = blockIdx.z;
+  const int qx = blockIdx.x * kRtQ + (tid & (kRtQ - 1)), qy = blockIdx.y * kRtQ + (tid >> 4);
+  const bool has_query = qx < w && qy < h;
+  const long long gid = (long long)b * h * w + (long long)qy * w + qx;
+  if (tid == 0) mbar_init(&sm.bar, 1);
+
+  longlong2 p = make_longlong2(0, 0);
+  if (has_query) p = p1[gid];
+  // coordinates far outside any image can never produce an in-image candidate: result == input
+  const long long lim = 1LL << 29;
+  const bool far_out = p.x < -lim || p.x > lim || p.y < -lim || p.y > lim;
+  const bool active = has_query && !far_out;
+  __half2 q[FDIM / 2];
+  if (active) load_query_f16<FDIM>(D21, gid, q);
+  const uint4* __restrict__ img = D11 + (size_t)b * NV * h * w;
+  int u0 = active ? (int)p.x : 0, v0 = active ? (int)p.y : 0;
+  int u_new = u0, v_new = v0;
+  float max_score = 0.0f;  // cuda::std::numeric_limits<c10::Half>::min() == Half() == +0 (matching_kernels.cu:47)
+  unsigned level = 0;
+  __syncthreads();  // barrier initialised
+
+  for (int d = dilation_max; d > 0; d--, level++) {
+    const int rd = RADIUS * d;
+    // ---- 1. mean centre of the tile's active queries
+    {
+      int su = active ? u0 : 0, sv = active ? v0 : 0, sc = active ? 1 : 0;
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) {
+        su += __shfl_xor_sync(0xffffffffu, su, o);
+        sv += __shfl_xor_sync(0xffffffffu, sv, o);
+        sc += __shfl_xor_sync(0xffffffffu, sc, o);
+      }
+      if (lane == 0) {
+        sm.red[0][warp] = su;
+        sm.red[1][warp] = sv;
+        sm.red[2][warp] = sc;
+      }
+    }
+    __syncthreads();  // also: every thread is done reading the previous level's box
+    // ---- 2. one thread fetches the box
+    if (tid == 0) {
+      long long su = 0, sv = 0;
+      int sc = 0;
+#pragma unroll
+      for (int k = 0; k < kRtThreads / 32; k++) {
+        su += sm.red[0][k];
+        sv += sm.red[1][k];
+        sc += sm.red[2][k];
+      }
+      const int need = kRtQ + 2 * rd;
+      const int box = need <= kRtBoxSmall ? kRtBoxSmall : kRtBoxBig;
+      int ox = 0, oy = 0, edge = 0;
+      if (sc > 0) {
+        ox = (int)(su / sc) - box / 2;
+        oy = (int)(sv / sc) - box / 2;
+        edge = box;
+        mbar_arrive_expect_tx(&sm.bar, (unsigned)(box * box * FDIM * 2));
+        tma_load_4d(sm.tile, box == kRtBoxSmall ? &map_small : &map_big, 0, ox, oy, b, &sm.bar);
+      }
+      sm.origin[0] = ox;
+      sm.origin[1] = oy;
+      sm.origin[2] = edge;
+    }
+    __syncthreads();
+    const int ox = sm.origin[0], oy = sm.origin[1], box = sm.origin[2];
+    if (box == 0) break;  // no active query in this tile (uniform)
+    const bool in_box = active && u0 - rd >= ox && u0 + rd < ox + box && v0 - rd >= oy && v0 + rd < oy + box;
+    mbar_wait(&sm.bar, level & 1);
+    // ---- 3. scan (matching_kernels.cu:51-69): u offset outer, v offset inner, the 7 candidates of a column together
+    if (active) {
+      for (int i = 0; i <= 2 * rd; i += d) {
+        const int u = u0 - rd + i;
+        if (u < 0 || u >= w) continue;
+        uint4 t[NJ][NV];
+        bool in[NJ];
+        if (in_box) {
+#pragma unroll
+          for (int jj = 0; jj < NJ; jj++) {
+            const int v = v0 - rd + jj * d;
+            in[jj] = v >= 0 && v < h;
+            const uint4* c = sm.tile + (size_t)((v - oy) * box + (u - ox)) * NV;
+#pragma unroll
+            for (int k = 0; k < NV; k++) t[jj][k] = c[k];
+          }
+        } else {
+#pragma unroll
+          for (int jj = 0; jj < NJ; jj++) {
+            const int v = v0 - rd + jj * d;
+            in[jj] = v >= 0 && v < h;
+            const uint4* c = img + (size_t)((in[jj] ? v : 0) * w + u) * NV;
+#pragma unroll
+            for (int k = 0; k < NV; k++) t[jj][k] = in[jj] ? __ldg(c + k) : make_uint4(0, 0, 0, 0);
+          }
+        }
+        float sc[NJ];
+        score_f16_multi<NV, NJ>(q, t, sc);  // the NJ rounding chains interleaved (matching_core.cuh)
+#pragma unroll
+        for (int jj = 0; jj < NJ; jj++) {
+          if (in[jj] && sc[jj] > max_score) {
+            max_score = sc[jj];
+            u_new = u;
+            v_new = v0 - rd + jj * d;
+          }
+        }
+      }
+      // ---- 4. recentre
+      u0 = u_new;
+      v0 = v_new;
+    }
+  }
+  if (has_query) p1_new[gid] = far_out ? p : make_longlong2((long long)u_new, (long long)v_new);
+}
+
+template <int FDIM>
+static int launch_tile_fdim(const CUtensorMap& big, const CUtensorMap& small, const uint16_t* D11, const uint16_t* D21,
+                            const int64_t* p1, int64_t* p1_new, int b, int h, int w, int dilation_max, cudaStream_t st) {
+  static DynSmemOptIn attr;  // per device
+  const size_t smem = sizeof(RefineTileSmem<FDIM>) + 128;
+  const int rc = ensure_dyn_smem(refine_matches_tile_kernel<FDIM, 3>, smem, attr);
+  if (rc != M3R_OK) return rc;
+  const dim3 grid((unsigned)ceil_div(w, kRtQ), (unsigned)ceil_div(h, kRtQ), (unsigned)b);
+  refine_matches_tile_kernel<FDIM, 3><<<grid, kRtThreads, smem, st>>>(big, small, (const uint4*)D11, (const uint4*)D21,
+                                                                        (const longlong2*)p1, (longlong2*)p1_new, h, w,
+                                                                        dilation_max);
+  M3R_LAUNCH_CHECK();
+  return M3R_OK;
+}
+
+// returns M3R_OK when the tile kernel ran, 1 when the caller should use the gather kernel, else an error code
+int launch_refine_tile_f16(const uint16_t* D11, const uint16_t* D21, const int64_t* p1, int64_t* p1_new, int b, int h,
+                           int w, int fdim, int radius, int dilation_max, cudaStream_t st) {
+  if (radius != 3 || (fdim != 24 && fdim != 16) || dilation_max < 1) return 1;
+  if (kRtQ + 2 * radius * dilation_max > kRtBoxBig) return 1;  // widest window must fit the big box
+  if (b > 65535 || ((uintptr_t)D11 & 15) != 0) return 1;
+  CUtensorMap big, small;
+  if (!encode_image_tiles(&big, D11, b, h, w, fdim, 2, kRtBoxBig, kRtBoxBig)) return 1;
+  if (!encode_image_tiles(&small, D11, b, h, w, fdim, 2, kRtBoxSmall, kRtBoxSmall)) return 1;
+  if (fdim == 24) return launch_tile_fdim<24>(big, small, D11, D21, p1, p1_new, b, h, w, dilation_max, st);
+  return launch_tile_fdim<16>(big, small, D11, D21, p1, p1_new, b, h, w, dilation_max, st);
+}
+
+}  // namespace m3r

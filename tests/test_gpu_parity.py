@@ -58,6 +58,35 @@ def test_refine_matches_generic_fdim_and_f32(be, orc):
     assert (got.cpu().numpy() != want).any(-1).mean() < 1e-3  # fp32 scores: ties only through FMA contraction
 
 
+def test_refine_matches_tile_kernel_equals_gather_kernel(be):
+    """The TMA tile-staged refine kernel (csrc/matching_tile.cu, opt-in) against the default per-thread kernel: identical
+    indices at 512x384 (coherent and incoherent start points), on a ragged image, and with far-out / border starts."""
+    from mast3r_slam_ysh_b200 import _lib, synthetic as syn
+    lib = _lib.load()
+    try:
+        for (b, h, w, noise) in [(1, 384, 512, 0.005), (2, 384, 512, 0.0), (3, 33, 47, 0.005)]:
+            m = syn.make_match_problem(b, h, w, seed=50 + h, device=DEV, point_noise=noise)
+            p, _ = be.iter_proj(m["rays_img_with_grad"], m["pts_3d_norm"], m["p_init"], MT["max_iter"], MT["lambda_init"],
+                                MT["convergence_thresh"])
+            p1 = p.long()
+            p1[:, ::97, 0] = 0
+            p1[:, ::89, 1] = h - 1
+            p1[:, 5] = torch.tensor([10 ** 12, -7], device=DEV)
+            p1[:, 11] = torch.tensor([-40, h + 40], device=DEV)
+            D11, D21 = m["D11"].half(), m["D21"].view(b, h * w, -1).half()
+            lib.m3r_debug_set_refine_mode(0)
+            (qa,) = be.refine_matches(D11, D21, p1, 3, 5)
+            lib.m3r_debug_set_refine_mode(1)
+            (qb,) = be.refine_matches(D11, D21, p1, 3, 5)
+            (qc,) = be.refine_matches(D11, D21, p1, 3, 2)
+            lib.m3r_debug_set_refine_mode(0)
+            (qd,) = be.refine_matches(D11, D21, p1, 3, 2)
+            assert torch.equal(qa, qb) and torch.equal(qc, qd), (h, w)
+            assert float((qa != p1).any(-1).float().mean()) > 0.05
+    finally:
+        lib.m3r_debug_set_refine_mode(-1)
+
+
 def test_refine_matches_edge_cases(be):
     # non-positive scores never win (max_score starts at +0): all-zero descriptors keep p1; far-out p1 unchanged
     D11 = torch.zeros(1, 8, 8, 24, dtype=torch.float16, device=DEV)

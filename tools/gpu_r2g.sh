@@ -1,5 +1,5 @@
 #!/bin/bash
+# full GPU suite + smoke (round 2)
 mkdir -p gpurun_out; O=gpurun_out
 timeout 1500 python -m pytest tests -m gpu -x -q > $O/pytest_gpu.log 2>&1; echo "pytest rc=$?"; tail -12 $O/pytest_gpu.log
-cat $O/binding_overhead.json
 python -c "import __graft_entry__ as g; g.smoke()" 2>&1 | tail -2
