@@ -66,6 +66,21 @@ M3R_API int m3r_iter_proj(const float* rays_img_with_grad, const float* pts_3d_n
                   uint8_t* converged, int b, int h, int w, int n, int max_iter, float lambda_init,
                   float cost_thresh, void* stream);
 
+/* m3r_iter_proj without any allocation.  NO COUNTERPART IN THE REFERENCE: added for
+ * callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * Same arguments, same kernels and bit-identical results as m3r_iter_proj, but the scratch of the repacked ray image lives
+ * in a fixed device array inside the library (M3R_ITER_PROJ_NOALLOC_SCRATCH_BYTES = 6.75 MiB, held by every GPU that loads
+ * the library until exit) instead of stream-ordered memory; the call makes no cudaMalloc / cudaFree / allocating library
+ * call.  Limit: b*h*w <= M3R_ITER_PROJ_NOALLOC_MAX_PIXELS ray-image pixels (one 512x384 image, the tracker's case); larger
+ * inputs return M3R_ERR_INVALID_ARGUMENT with a message.  All calls on a device SHARE the array: calls that overlap on the
+ * GPU (different streams, or threads launching concurrently) race -- serialise them on one stream.  The array keeps the
+ * last call's contents; every entry a call reads is rewritten by that call first, so nothing needs clearing. */
+#define M3R_ITER_PROJ_NOALLOC_MAX_PIXELS 196608
+#define M3R_ITER_PROJ_NOALLOC_SCRATCH_BYTES (M3R_ITER_PROJ_NOALLOC_MAX_PIXELS * 36)
+M3R_API int m3r_iter_proj_noalloc(const float* rays_img_with_grad, const float* pts_3d_norm, const float* p_init,
+                                  float* p_new, uint8_t* converged, int b, int h, int w, int n, int max_iter,
+                                  float lambda_init, float cost_thresh, void* stream);
+
 /* ---------------------------------------------------------------------------------------------------------
  * refine_matches -- replaces refine_matches (gn.cpp:101-114 -> matching_kernels.cu:84-116, kernel :25-81)
  *   D11 (b,h,w,fdim), D21 (b,n,fdim) fp16 (the dtype every reference caller uses, matching.py:80-81) or fp32;

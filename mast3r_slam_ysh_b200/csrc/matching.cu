@@ -328,6 +328,53 @@ extern "C" int m3r_iter_proj(const float* rays_img_with_grad, const float* pts_3
   return M3R_OK;
 }
 
+// ---------------------------------------------------------------------------------------------------- no-allocation variant
+// m3r_iter_proj for callers that must not allocate (CUDA graph capture, tight serving loops, harnesses that forbid
+// cudaMalloc): the scratch of the repacked ray image (three planes, 36 bytes per pixel) lives in a file-scope device
+// array of fixed size instead of stream-ordered memory.  Every GPU that loads the library holds these 6.75 MiB until the
+// process exits.  In host code the array's NAME is only a host-side stand-in: its device address is looked up once per
+// device with cudaGetSymbolAddress (that device current) and handed to the kernels.
+static __device__ __align__(256) unsigned char g_iter_proj_scratch[M3R_ITER_PROJ_NOALLOC_SCRATCH_BYTES];
+
+extern "C" int m3r_iter_proj_noalloc(const float* rays_img_with_grad, const float* pts_3d_norm, const float* p_init,
+                                     float* p_new, uint8_t* converged, int b, int h, int w, int n, int max_iter,
+                                     float lambda_init, float cost_thresh, void* stream) {
+  M3R_REQUIRE(b >= 0 && n >= 0 && h >= 0 && w >= 0 && max_iter >= 0, "iter_proj_noalloc: negative size");
+  const long long total = (long long)b * n;
+  if (total == 0) return M3R_OK;
+  M3R_REQUIRE(rays_img_with_grad && pts_3d_norm && p_init && p_new && converged, "iter_proj_noalloc: null pointer");
+  M3R_REQUIRE(h >= 3 && w >= 3, "iter_proj_noalloc: image must be at least 3x3 (got %dx%d)", h, w);
+  M3R_REQUIRE(((uintptr_t)p_init & 7) == 0 && ((uintptr_t)p_new & 7) == 0,
+              "iter_proj_noalloc: p_init/p_new must be 8-byte aligned");
+  const long long npix = (long long)b * h * w;
+  M3R_REQUIRE(npix <= M3R_ITER_PROJ_NOALLOC_MAX_PIXELS,
+              "iter_proj_noalloc: b*h*w = %lld pixels of ray image exceed the fixed scratch (at most %d pixels, e.g. one "
+              "512x384 image); use m3r_iter_proj for larger batches", npix, M3R_ITER_PROJ_NOALLOC_MAX_PIXELS);
+  // device address of the scratch, once per device (cached: the look-up itself allocates nothing)
+  static unsigned char* scratch_dev[kMaxDevices] = {};
+  const int slot = current_device_slot();
+  if (scratch_dev[slot] == nullptr) {
+    void* ptr = nullptr;
+    M3R_CUDA(cudaGetSymbolAddress(&ptr, g_iter_proj_scratch));
+    M3R_REQUIRE(ptr != nullptr, "iter_proj_noalloc: cudaGetSymbolAddress returned a null scratch address");
+    scratch_dev[slot] = (unsigned char*)ptr;
+  }
+  // plane offsets for the MAXIMUM size, so they do not depend on this call's npix (16-byte aligned by construction)
+  unsigned char* base = scratch_dev[slot];
+  float4* P0 = (float4*)base;
+  float4* P1 = (float4*)(base + (size_t)M3R_ITER_PROJ_NOALLOC_MAX_PIXELS * sizeof(float4));
+  float* P2 = (float*)(base + 2 * (size_t)M3R_ITER_PROJ_NOALLOC_MAX_PIXELS * sizeof(float4));
+  cudaStream_t st = (cudaStream_t)stream;
+  // the repack writes every plane entry [0, npix) that the LM kernel can read, so nothing of an earlier call's contents is
+  // ever consumed and nothing needs clearing
+  repack_rays_kernel<<<(unsigned)ceil_div_ll(npix, 256), 256, 0, st>>>(rays_img_with_grad, P0, P1, P2, npix);
+  M3R_LAUNCH_CHECK();
+  iter_proj_v2_kernel<<<(unsigned)ceil_div_ll(total, 128), 128, 0, st>>>(P0, P1, P2, pts_3d_norm, p_init, p_new, converged,
+                                                                         total, n, h, w, max_iter, lambda_init, cost_thresh);
+  M3R_LAUNCH_CHECK();
+  return M3R_OK;
+}
+
 template <typename T>
 static int launch_refine_generic(const T* D11, const T* D21, const int64_t* p1, int64_t* p1_new, long long total, int n,
                                  int h, int w, int fdim, int radius, int dilation_max, cudaStream_t st) {
