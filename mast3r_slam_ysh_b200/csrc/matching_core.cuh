@@ -43,6 +43,11 @@ __device__ __forceinline__ float dot3_ref(float x, float xp, float y, float yp, 
 
 // One query of iter_proj (matching_kernels.cu:119-275) on the repacked planes: 10 LM iterations from the clamped (u, v)
 // towards the unit target ray (tx, ty, tz).  Shared by the drop-in kernel and the fused match kernel.
+// Tried and dropped (r2, tools/time_iterproj.py, 512x384): keeping the four corners of the current bilinear cell in
+// registers, tagged with the cell index, so that a candidate in the same cell (70-95 % of them from the third iteration on)
+// needs no loads.  Bit-identical, but SLOWER at b >= 8 -- noise-free scene 1.07 -> 1.58 ms at b = 64, noisy scene 2.39 ->
+// 2.59 ms (b = 1: 0.049 -> 0.047 ms): the repeated loads were L1 hits anyway, and 104 instead of 62 registers plus the
+// divergent "same cell?" paths cost more than they saved.
 __device__ __forceinline__ void iter_proj_core(const float4* __restrict__ p0, const float4* __restrict__ p1,
                                                const float* __restrict__ p2, float tx, float ty, float tz, int w, int h,
                                                int max_iter, float lambda_init, float cost_thresh, float& u, float& v,
