@@ -468,17 +468,36 @@ __device__ __forceinline__ void pair_accumulate(V2 (&acc)[kAcc], const EdgeConst
 // (issue-bound, 236 instructions per record); v6 packed f32x2 arithmetic, MUFU-only reciprocals, branch-free Huber (143
 // per record) -- no faster: the two 16-byte gathers per record saturated the L1TEX wavefront rate (~100 G records/s at 32
 // and at 256 keyframes alike, profiles/r2_hessian_v6_ncu_full.txt); v7 (this): the gathers moved into the once-per-solve
-// pre-pass, the kernel streams 32 self-contained bytes per record.
+// pre-pass, the kernel streams 32 self-contained bytes per record through one CTA-wide ring (83 us at configs[2], 1006 us
+// at 256 keyframes); v8 (default, M3R_HESS_WARPRING=1): warp-private rings -- every warp streams its own quarter of a
+// segment and refills a stage itself, so no warp waits for the slowest one before copies are issued: 79.6 / 955 us with 3
+// stages (4: 82.1 / 966, 6: 80.0 / 959, 8: 81.1 / 968; profiles/r2_hessian_v8_variants.txt).  Also tried on v7 and dropped:
+// 4 CTAs per SM under a 128-register cap (88 B of spills: 91 / 1141 us), 96-thread CTAs x 5 (118 / 1514 us).
+#ifndef M3R_HESS_WARPRING
+#define M3R_HESS_WARPRING 1
+#endif
 #ifndef M3R_HESS_STAGES
-#define M3R_HESS_STAGES 4
+#define M3R_HESS_STAGES (M3R_HESS_WARPRING ? 3 : 4)
 #endif
 constexpr int kHessStages = M3R_HESS_STAGES;
 constexpr int kHessTile = 2 * kHessThreads;  // records per ring stage
+#if M3R_HESS_WARPRING
+// Warp-private rings: every warp streams its own quarter of a segment through its own stages and refills a stage itself
+// as soon as its 32 lanes have taken their records out -- no cross-warp "empty" barrier, so a slow warp never holds back
+// the copies of the others.
+constexpr int kHessWarps = kHessThreads / 32;
+constexpr int kWarpTile = 64;  // records per warp and stage (two per lane)
+struct HessRing {
+  GnRecord r[kHessWarps][kHessStages][kWarpTile];
+  unsigned long long full[kHessWarps][kHessStages];
+};
+#else
 struct HessRing {
   GnRecord r[kHessStages][kHessTile];
   unsigned long long full[kHessStages];   // tile landed (TMA transaction bytes)
   unsigned long long empty[kHessStages];  // every warp has taken its records out of the stage
 };
+#endif
 
 constexpr int kHessMaxSeg = 8;  // edge segments planned at once by a CTA (more are handled in further rounds)
 struct HessPlan {
@@ -508,6 +527,12 @@ __global__ void __launch_bounds__(kHessThreads, kHessCtasPerSm) hessian_kernel(c
   extern __shared__ __align__(128) unsigned char s_ring_raw[];
   HessRing& ring = *reinterpret_cast<HessRing*>(s_ring_raw);
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+#if M3R_HESS_WARPRING
+  if (lane == 0) {
+#pragma unroll
+    for (int s = 0; s < kHessStages; s++) mbar_init(&ring.full[warp][s], 1);
+  }
+#else
   if (threadIdx.x == 0) {
 #pragma unroll
     for (int s = 0; s < kHessStages; s++) {
@@ -515,6 +540,7 @@ __global__ void __launch_bounds__(kHessThreads, kHessCtasPerSm) hessian_kernel(c
       mbar_init(&ring.empty[s], kHessThreads / 32);
     }
   }
+#endif
   // tiles issued / consumed so far by this CTA: stage = count % kHessStages, phase parity from count / kHessStages
   unsigned issued = 0, consumed = 0, nred = 0;
   int e_cur = -1;
@@ -559,6 +585,63 @@ __global__ void __launch_bounds__(kHessThreads, kHessCtasPerSm) hessian_kernel(c
                  &plan.c[threadIdx.x]);
     __syncthreads();
 
+#if M3R_HESS_WARPRING
+    // This warp's slice of planned segment sidx: a quarter of the segment, rounded up to whole warp tiles.
+    auto warp_slice = [&](int sidx, int& ws, int& we) {
+      const int k0 = plan.k0[sidx], k1 = plan.k1[sidx];
+      const int q = ((k1 - k0 + kHessWarps * kWarpTile - 1) / (kHessWarps * kWarpTile)) * kWarpTile;
+      ws = min(k1, k0 + warp * q);
+      we = min(k1, ws + q);
+    };
+    // Producer cursor of the warp (kept uniform over the lanes; lane 0 issues): the warp tiles of all planned segments
+    // form one sequence, so the copies run ahead ACROSS segment boundaries.
+    int pseg = 0, pkb = 0, pend = 0;
+    warp_slice(0, pkb, pend);
+    auto issue_next = [&]() {
+      while (pseg < nseg && pkb >= pend) {  // skip segments in which this warp has no records (left)
+        pseg++;
+        if (pseg < nseg) warp_slice(pseg, pkb, pend);
+      }
+      if (pseg >= nseg) return;
+      const unsigned st = issued % kHessStages;
+      if (lane == 0) {
+        const unsigned bytes = (unsigned)min(kWarpTile, pend - pkb) * (unsigned)sizeof(GnRecord);
+        mbar_arrive_expect_tx(&ring.full[warp][st], bytes);
+        bulk_g2s(&ring.r[warp][st][0], rec + (size_t)plan.e[pseg] * num_pts + pkb, bytes, &ring.full[warp][st]);
+      }
+      issued++;
+      pkb += kWarpTile;
+    };
+#pragma unroll
+    for (int i = 0; i < kHessStages; i++) issue_next();
+
+    for (int sg = 0; sg < nseg; sg++) {
+      const EdgeConst c = plan.c[sg];
+      const int e = plan.e[sg];
+      int ws, we;
+      warp_slice(sg, ws, we);
+      V2 acc2[kAcc];
+#pragma unroll
+      for (int i = 0; i < kAcc; i++) acc2[i] = bc(0.0f);
+#pragma unroll 2
+      for (int kb = ws; kb < we; kb += kWarpTile) {
+        const unsigned st = consumed % kHessStages;
+        mbar_wait(&ring.full[warp][st], (consumed / kHessStages) & 1);
+        // The tile holds cnt >= 1 records; a lane without a record of its own re-reads the last one with sqrt(q) = 0
+        // (weight exactly zero, all terms finite): no branch around the arithmetic and its 70 accumulator registers.
+        const int cnt = min(kWarpTile, we - kb);
+        const int i0 = min(lane, cnt - 1), i1 = min(lane + 32, cnt - 1);
+        const float4 a0 = ring.r[warp][st][i0].a, b0 = ring.r[warp][st][i0].b;
+        const float4 a1 = ring.r[warp][st][i1].a, b1 = ring.r[warp][st][i1].b;
+        __syncwarp();  // every lane has its records in registers: the stage is free
+        if (lane == 0) asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // reads before the copy engine's write
+        consumed++;
+        issue_next();  // refills exactly the stage just freed (issued == consumed + kHessStages - 1 before the call)
+        const float sq0 = lane < cnt ? b0.w : 0.0f;
+        const float sq1 = lane + 32 < cnt ? b1.w : 0.0f;
+        pair_accumulate<KIND, ROBUST>(acc2, c, pp, a0, a1, b0, b1, pk(sq0, sq1));
+      }
+#else
     // Producer cursor (thread 0 only): the tiles of all planned segments form one sequence, so the ring keeps
     // kHessStages - 1 tiles in flight ACROSS segment boundaries.  (Tried, r2: the role rotating over the warps, 83 ->
     // 117 us; deeper rings, 4 -> 6 -> 8 stages: 83 -> 94 -> 100 us; an L2 prefetch 8 / 16 tiles ahead: 99 / 109 us; two
@@ -618,6 +701,7 @@ __global__ void __launch_bounds__(kHessThreads, kHessCtasPerSm) hessian_kernel(c
         pair_accumulate<KIND, ROBUST>(acc2, c, pp, a0, a1, b0, b1, pk(sq0, sq1));
 #endif
       }
+#endif
       float acc[kAcc];
 #pragma unroll
       for (int i = 0; i < kAcc; i++) acc[i] = lo(acc2[i]) + hi(acc2[i]);
