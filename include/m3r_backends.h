@@ -81,6 +81,18 @@ M3R_API int m3r_iter_proj_noalloc(const float* rays_img_with_grad, const float* 
                                   float* p_new, uint8_t* converged, int b, int h, int w, int n, int max_iter,
                                   float lambda_init, float cost_thresh, void* stream);
 
+/* iter_proj kernel selection (process-wide): 0 = one thread per query gathering its bilinear corners from global memory,
+ * 1 = where the queries are the pixel grid of the image (n == h*w, w % 4 == 0) the tile-staged kernel: a CTA per 16x8 query
+ * tile runs the first LM iteration from global memory, then fetches the 32x24 window of the three repacked planes around
+ * its queries' mean position with TMA tensor copies and runs the remaining iterations from shared memory (global fallback
+ * for cells outside the window).  Same arithmetic, bit-identical results; -1 = decided by the environment
+ * (M3R_ITER_PROJ_TILE=0/1; M3R_ITER_PROJ_WARM = iterations before the window is placed, default 1).  No reference
+ * counterpart (matching_kernels.cu:278-311 has one kernel). */
+M3R_API void m3r_debug_set_iter_proj_mode(int mode);
+/* Diagnostics, only counting in -DM3R_IP_STATS builds: two device counters (corner fetches served by the window / by the
+ * global fallback) of the tile-staged iter_proj kernel; NULL switches it off.  No reference counterpart. */
+M3R_API void m3r_debug_set_iter_proj_stats(unsigned long long* dev_counters);
+
 /* ---------------------------------------------------------------------------------------------------------
  * refine_matches -- replaces refine_matches (gn.cpp:101-114 -> matching_kernels.cu:84-116, kernel :25-81)
  *   D11 (b,h,w,fdim), D21 (b,n,fdim) fp16 (the dtype every reference caller uses, matching.py:80-81) or fp32;

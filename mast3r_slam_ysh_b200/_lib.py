@@ -43,6 +43,8 @@ SYMBOLS = {
     "m3r_debug_set_timeline": (None, [_vp, _i]),
     "m3r_debug_set_solver": (None, [_i]),
     "m3r_debug_set_refine_mode": (None, [_i]),
+    "m3r_debug_set_iter_proj_mode": (None, [_i]),
+    "m3r_debug_set_iter_proj_stats": (None, [_vp]),
     "m3r_debug_solver_lanes": (_i, [_vp]),
     "m3r_iter_proj": (_i, [_vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _f, _f, _vp]),
     "m3r_iter_proj_noalloc": (_i, [_vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _f, _f, _vp]),

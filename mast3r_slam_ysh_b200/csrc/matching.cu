@@ -18,11 +18,19 @@
 
 namespace m3r {
 
+#ifndef M3R_ITER_PROJ_TILE_DEFAULT
+#define M3R_ITER_PROJ_TILE_DEFAULT 0
+#endif
 static int g_refine_mode = -1;  // -1: environment, 0: per-thread gathers, 1: tile-staged kernel where it applies
 
 // matching_tile.cu
 int launch_refine_tile_f16(const uint16_t* D11, const uint16_t* D21, const int64_t* p1, int64_t* p1_new, int b, int h,
                            int w, int fdim, int radius, int dilation_max, cudaStream_t st);
+
+int launch_iter_proj_tile(const float4* P0, const float4* P1, const float* P2, const float* pts, const float* p_init,
+                          float* p_new, uint8_t* converged, int b, int h, int w, int max_iter, int warm,
+                          float lambda_init, float cost_thresh, cudaStream_t st);
+static int g_iter_proj_mode = -1;  // -1: environment (M3R_ITER_PROJ_TILE=0/1, default below), 0: gathers, 1: tile-staged
 
 // =================================================================================================== iter_proj
 // 9-channel bilinear sample; weights follow the reference's "opposite area" naming (matching_kernels.cu:161-170):
@@ -321,12 +329,31 @@ extern "C" int m3r_iter_proj(const float* rays_img_with_grad, const float* pts_3
   float* P2 = (float*)((char*)scratch + 2 * plane);
   repack_rays_kernel<<<(unsigned)ceil_div_ll(npix, 256), 256, 0, st>>>(rays_img_with_grad, P0, P1, P2, npix);
   M3R_LAUNCH_CHECK();
-  iter_proj_v2_kernel<<<blocks, threads, 0, st>>>(P0, P1, P2, pts_3d_norm, p_init, p_new, converged, total, n, h, w,
-                                                  max_iter, lambda_init, cost_thresh);
-  M3R_LAUNCH_CHECK();
+  // queries on the image grid (the callers' layout): the tile-staged kernel (matching_tile.cu); anything else, or a
+  // shape it does not take: per-thread gathers
+  static const int env_tile = [] {
+    const char* e = getenv("M3R_ITER_PROJ_TILE");
+    return e == nullptr ? M3R_ITER_PROJ_TILE_DEFAULT : atoi(e);
+  }();
+  static const int env_warm = [] {
+    const char* e = getenv("M3R_ITER_PROJ_WARM");
+    return e == nullptr ? 1 : atoi(e);
+  }();
+  int rc = 1;
+  if ((g_iter_proj_mode == 1 || (g_iter_proj_mode < 0 && env_tile != 0)) && (long long)n == (long long)h * w)
+    rc = launch_iter_proj_tile(P0, P1, P2, pts_3d_norm, p_init, p_new, converged, b, h, w, max_iter, env_warm,
+                               lambda_init, cost_thresh, st);
+  if (rc == 1) {
+    iter_proj_v2_kernel<<<blocks, threads, 0, st>>>(P0, P1, P2, pts_3d_norm, p_init, p_new, converged, total, n, h, w,
+                                                    max_iter, lambda_init, cost_thresh);
+    M3R_LAUNCH_CHECK();
+    rc = M3R_OK;
+  }
   M3R_CUDA(cudaFreeAsync(scratch, st));
-  return M3R_OK;
+  return rc;
 }
+
+extern "C" void m3r_debug_set_iter_proj_mode(int mode) { m3r::g_iter_proj_mode = mode; }
 
 // ---------------------------------------------------------------------------------------------------- no-allocation variant
 // m3r_iter_proj for callers that must not allocate (CUDA graph capture, tight serving loops, harnesses that forbid

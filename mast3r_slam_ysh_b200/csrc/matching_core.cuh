@@ -9,6 +9,7 @@ namespace m3r {
 struct Bil {
   float w11, w12, w21, w22;
   int o22, o21, o12, o11;  // pixel offsets of (v,u), (v,u+1), (v+1,u), (v+1,u+1)
+  int u11, v11;            // the cell itself (tile-staged samplers test it against their window)
 };
 
 __device__ __forceinline__ Bil bil_setup(float u, float v, int w) {
@@ -22,6 +23,8 @@ __device__ __forceinline__ Bil bil_setup(float u, float v, int w) {
   B.w12 = __fmul_rn(cu, dv);
   B.w21 = __fmul_rn(du, cv);
   B.w22 = __fmul_rn(cu, cv);
+  B.u11 = u11;
+  B.v11 = v11;
   B.o22 = v11 * w + u11;
   B.o21 = B.o22 + 1;
   B.o12 = B.o22 + w;
@@ -48,52 +51,97 @@ __device__ __forceinline__ float dot3_ref(float x, float xp, float y, float yp, 
 // needs no loads.  Bit-identical, but SLOWER at b >= 8 -- noise-free scene 1.07 -> 1.58 ms at b = 64, noisy scene 2.39 ->
 // 2.59 ms (b = 1: 0.049 -> 0.047 ms): the repeated loads were L1 hits anyway, and 104 instead of 62 registers plus the
 // divergent "same cell?" paths cost more than they saved.
-__device__ __forceinline__ void iter_proj_core(const float4* __restrict__ p0, const float4* __restrict__ p1,
-                                               const float* __restrict__ p2, float tx, float ty, float tz, int w, int h,
-                                               int max_iter, float lambda_init, float cost_thresh, float& u, float& v,
-                                               bool& conv_out) {
-  float lambda = lambda_init;
-  bool conv = false;
+
+// Where the corner samples come from.  ray(): plane P0 at the four corners of B's cell; grad(): planes P1 and P2.
+struct GlobalRaySampler {
+  const float4* __restrict__ p0;
+  const float4* __restrict__ p1;
+  const float* __restrict__ p2;
+  __device__ __forceinline__ void ray(const Bil& B, float4& a11, float4& a12, float4& a21, float4& a22) const {
+    a11 = __ldg(p0 + B.o11);
+    a12 = __ldg(p0 + B.o12);
+    a21 = __ldg(p0 + B.o21);
+    a22 = __ldg(p0 + B.o22);
+  }
+  __device__ __forceinline__ void grad(const Bil& B, float4& c11, float4& c12, float4& c21, float4& c22, float& d11,
+                                       float& d12, float& d21, float& d22) const {
+    c11 = __ldg(p1 + B.o11);
+    c12 = __ldg(p1 + B.o12);
+    c21 = __ldg(p1 + B.o21);
+    c22 = __ldg(p1 + B.o22);
+    d11 = __ldg(p2 + B.o11);
+    d12 = __ldg(p2 + B.o12);
+    d21 = __ldg(p2 + B.o21);
+    d22 = __ldg(p2 + B.o22);
+  }
+};
+
+// Everything one query carries from one LM iteration to the next, so that the loop can be run in pieces (the tile-staged
+// kernel changes its sampler after the first iteration).
+struct IterProjState {
+  float u, v, lambda;
+  bool conv, have_r, have_g;
   // sample cached at (u,v): raw ray, d/du, d/dv
-  float r0 = 0.f, r1 = 0.f, r2 = 0.f, gx0 = 0.f, gx1 = 0.f, gx2 = 0.f, gy0 = 0.f, gy1 = 0.f, gy2 = 0.f;
-  bool have_r = false, have_g = false;
-  Bil B = bil_setup(u, v, w);
-  for (int it = 0; it < max_iter; it++) {
-    if (!have_r) {
-      const float4 a11 = __ldg(p0 + B.o11), a12 = __ldg(p0 + B.o12), a21 = __ldg(p0 + B.o21), a22 = __ldg(p0 + B.o22);
-      r0 = bil(B, a11.x, a12.x, a21.x, a22.x);
-      r1 = bil(B, a11.y, a12.y, a21.y, a22.y);
-      r2 = bil(B, a11.z, a12.z, a21.z, a22.z);
-      gx0 = bil(B, a11.w, a12.w, a21.w, a22.w);
+  float r0, r1, r2, gx0, gx1, gx2, gy0, gy1, gy2;
+  Bil B;
+};
+
+__device__ __forceinline__ void iter_proj_begin(IterProjState& s, float u, float v, int w, float lambda_init) {
+  s.u = u;
+  s.v = v;
+  s.lambda = lambda_init;
+  s.conv = false;
+  s.have_r = false;
+  s.have_g = false;
+  s.r0 = s.r1 = s.r2 = s.gx0 = s.gx1 = s.gx2 = s.gy0 = s.gy1 = s.gy2 = 0.f;
+  s.B = bil_setup(u, v, w);
+}
+
+// LM iterations [it0, it1) of one query (matching_kernels.cu:155-268)
+template <typename Sampler>
+__device__ __forceinline__ void iter_proj_steps(IterProjState& s, const Sampler& S, float tx, float ty, float tz, int w,
+                                                int h, int it0, int it1, float cost_thresh) {
+  for (int it = it0; it < it1; it++) {
+    if (!s.have_r) {
+      float4 a11, a12, a21, a22;
+      S.ray(s.B, a11, a12, a21, a22);
+      s.r0 = bil(s.B, a11.x, a12.x, a21.x, a22.x);
+      s.r1 = bil(s.B, a11.y, a12.y, a21.y, a22.y);
+      s.r2 = bil(s.B, a11.z, a12.z, a21.z, a22.z);
+      s.gx0 = bil(s.B, a11.w, a12.w, a21.w, a22.w);
     }
-    if (!have_g) {
-      const float4 c11 = __ldg(p1 + B.o11), c12 = __ldg(p1 + B.o12), c21 = __ldg(p1 + B.o21), c22 = __ldg(p1 + B.o22);
-      const float d11 = __ldg(p2 + B.o11), d12 = __ldg(p2 + B.o12), d21 = __ldg(p2 + B.o21), d22 = __ldg(p2 + B.o22);
-      gx1 = bil(B, c11.x, c12.x, c21.x, c22.x);
-      gx2 = bil(B, c11.y, c12.y, c21.y, c22.y);
-      gy0 = bil(B, c11.z, c12.z, c21.z, c22.z);
-      gy1 = bil(B, c11.w, c12.w, c21.w, c22.w);
-      gy2 = bil(B, d11, d12, d21, d22);
+    if (!s.have_g) {
+      float4 c11, c12, c21, c22;
+      float d11, d12, d21, d22;
+      S.grad(s.B, c11, c12, c21, c22, d11, d12, d21, d22);
+      s.gx1 = bil(s.B, c11.x, c12.x, c21.x, c22.x);
+      s.gx2 = bil(s.B, c11.y, c12.y, c21.y, c22.y);
+      s.gy0 = bil(s.B, c11.z, c12.z, c21.z, c22.z);
+      s.gy1 = bil(s.B, c11.w, c12.w, c21.w, c22.w);
+      s.gy2 = bil(s.B, d11, d12, d21, d22);
     }
+    const float r0 = s.r0, r1 = s.r1, r2 = s.r2, gx0 = s.gx0, gx1 = s.gx1, gx2 = s.gx2, gy0 = s.gy0, gy1 = s.gy1,
+                gy2 = s.gy2;
     // normalise, residual, cost (matching_kernels.cu:186-198); 1.0/r_norm compiles to the IEEE fp32 reciprocal
     float inv = __frcp_rn(__fsqrt_rn(dot3_ref(r0, r0, r1, r1, r2, r2)));
     const float e0 = __fmaf_rn(r0, inv, -tx), e1 = __fmaf_rn(r1, inv, -ty), e2 = __fmaf_rn(r2, inv, -tz);
     const float cost = dot3_ref(e0, e0, e1, e1, e2, e2);
     // 2x2 LM system (:202-215)
-    const float A00 = __fadd_rn(dot3_ref(gx0, gx0, gx1, gx1, gx2, gx2), lambda);
+    const float A00 = __fadd_rn(dot3_ref(gx0, gx0, gx1, gx1, gx2, gx2), s.lambda);
     const float A01 = dot3_ref(gx0, gy0, gx1, gy1, gx2, gy2);
-    const float A11 = __fadd_rn(dot3_ref(gy0, gy0, gy1, gy1, gy2, gy2), lambda);
+    const float A11 = __fadd_rn(dot3_ref(gy0, gy0, gy1, gy1, gy2, gy2), s.lambda);
     const float s0 = dot3_ref(gx0, e0, gx1, e1, gx2, e2);  // = -b0
     const float s1 = dot3_ref(gy0, e0, gy1, e1, gy2, e2);  // = -b1
     const float det_inv = __frcp_rn(__fmaf_rn(A00, A11, -__fmul_rn(A01, A01)));
     const float xu = __fmaf_rn(A01, s1, -__fmul_rn(s0, A11));  // A11*b0 - A01*b1
     const float xv = __fmaf_rn(A01, s0, -__fmul_rn(s1, A00));  // -A01*b0 + A00*b1
-    const float u_new = fminf(fmaxf(__fmaf_rn(xu, det_inv, u), 1.0f), (float)(w - 2));
-    const float v_new = fminf(fmaxf(__fmaf_rn(xv, det_inv, v), 1.0f), (float)(h - 2));
+    const float u_new = fminf(fmaxf(__fmaf_rn(xu, det_inv, s.u), 1.0f), (float)(w - 2));
+    const float v_new = fminf(fmaxf(__fmaf_rn(xv, det_inv, s.v), 1.0f), (float)(h - 2));
 
     // candidate cost (:225-256)
     const Bil Bn = bil_setup(u_new, v_new, w);
-    const float4 a11 = __ldg(p0 + Bn.o11), a12 = __ldg(p0 + Bn.o12), a21 = __ldg(p0 + Bn.o21), a22 = __ldg(p0 + Bn.o22);
+    float4 a11, a12, a21, a22;
+    S.ray(Bn, a11, a12, a21, a22);
     const float t0 = bil(Bn, a11.x, a12.x, a21.x, a22.x);
     const float t1 = bil(Bn, a11.y, a12.y, a21.y, a22.y);
     const float t2 = bil(Bn, a11.z, a12.z, a21.z, a22.z);
@@ -101,23 +149,35 @@ __device__ __forceinline__ void iter_proj_core(const float4* __restrict__ p0, co
     const float f0 = __fmaf_rn(t0, inv, -tx), f1 = __fmaf_rn(t1, inv, -ty), f2 = __fmaf_rn(t2, inv, -tz);
     const float new_cost = dot3_ref(f0, f0, f1, f1, f2, f2);
     if (new_cost < cost) {  // accept (:259-264): the ray sampled at the candidate becomes the cached ray
-      u = u_new;
-      v = v_new;
-      lambda = __double2float_rn((double)lambda * 0.1);
-      conv = new_cost < cost_thresh;
-      r0 = t0; r1 = t1; r2 = t2;
-      gx0 = bil(Bn, a11.w, a12.w, a21.w, a22.w);
-      B = Bn;
-      have_r = true;
-      have_g = false;
+      s.u = u_new;
+      s.v = v_new;
+      s.lambda = __double2float_rn((double)s.lambda * 0.1);
+      s.conv = new_cost < cost_thresh;
+      s.r0 = t0; s.r1 = t1; s.r2 = t2;
+      s.gx0 = bil(Bn, a11.w, a12.w, a21.w, a22.w);
+      s.B = Bn;
+      s.have_r = true;
+      s.have_g = false;
     } else {  // reject (:265-268): same (u,v) next time, everything cached
-      lambda = __fmul_rn(lambda, 10.0f);
-      conv = cost < cost_thresh;
-      have_r = true;
-      have_g = true;
+      s.lambda = __fmul_rn(s.lambda, 10.0f);
+      s.conv = cost < cost_thresh;
+      s.have_r = true;
+      s.have_g = true;
     }
   }
-  conv_out = conv;
+}
+
+__device__ __forceinline__ void iter_proj_core(const float4* __restrict__ p0, const float4* __restrict__ p1,
+                                               const float* __restrict__ p2, float tx, float ty, float tz, int w, int h,
+                                               int max_iter, float lambda_init, float cost_thresh, float& u, float& v,
+                                               bool& conv_out) {
+  IterProjState s;
+  iter_proj_begin(s, u, v, w, lambda_init);
+  const GlobalRaySampler S{p0, p1, p2};
+  iter_proj_steps(s, S, tx, ty, tz, w, h, 0, max_iter, cost_thresh);
+  u = s.u;
+  v = s.v;
+  conv_out = s.conv;
 }
 
 // One query of refine_matches in fp16 (matching_kernels.cu:25-81): query descriptor q (fp16 pairs), descriptor image of

@@ -187,4 +187,188 @@ int launch_refine_tile_f16(const uint16_t* D11, const uint16_t* D21, const int64
   return launch_tile_fdim<16>(big, small, D11, D21, p1, p1_new, b, h, w, dilation_max, st);
 }
 
+// ================================================================================================ iter_proj, tile-staged
+// iter_proj_v2_kernel (matching.cu) is bound by L1 wavefronts: every LM iteration gathers four bilinear corners from
+// three planes, and on real (noisy) pointmaps the 32 queries of a warp land on different rows of the ray image, so one
+// LDG.128 touches up to 32 cache lines.  Queries that are neighbours in the image still converge to the same
+// neighbourhood.  Here a CTA owns a 16 x 8 tile of queries (n == h * w, the callers' layout: matching.py:41-60) and
+//   1. runs the first `warm` LM iterations from global memory (the first Gauss-Newton step is the long one: p_init may be
+//      a hundred pixels from the solution),
+//   2. takes the mean of its queries' positions and has ONE thread fetch the 32 x 24 pixel window around it from the
+//      three repacked planes with TMA tensor copies (rank-4 maps with the image row innermost, so a window row is one
+//      request; the window starts at a multiple of four pixels; 27 KB, one mbarrier),
+//   3. runs the remaining iterations out of shared memory: a cell whose four corners lie in the window is read with
+//      LDS.128 (at most 4 wavefronts per warp instead of one per row touched), any other cell falls back to global loads.
+// The arithmetic is iter_proj_steps of matching_core.cuh in both phases: bit-identical to the gather kernel.
+constexpr int kIpQW = 16, kIpQH = 8;
+constexpr int kIpThreads = kIpQW * kIpQH;
+constexpr int kIpBW = 32, kIpBH = 24;
+
+struct IterProjTileSmem {
+  float4 t0[kIpBH * kIpBW];
+  float4 t1[kIpBH * kIpBW];
+  float t2[kIpBH * kIpBW];
+  unsigned long long bar;
+  float red[3][kIpThreads / 32];
+  int origin[2];
+};
+
+struct TileRaySampler {
+  GlobalRaySampler g;
+  const float4* t0;
+  const float4* t1;
+  const float* t2;
+  int ox, oy;
+#ifdef M3R_IP_STATS
+  mutable unsigned hits = 0, misses = 0;
+#endif
+  __device__ __forceinline__ bool inside(const Bil& B, int& i) const {
+    const unsigned lx = (unsigned)(B.u11 - ox), ly = (unsigned)(B.v11 - oy);
+    i = (int)(ly * kIpBW + lx);
+    const bool in = lx < (unsigned)(kIpBW - 1) && ly < (unsigned)(kIpBH - 1);
+#ifdef M3R_IP_STATS
+    if (in) hits++; else misses++;
+#endif
+    return in;
+  }
+  __device__ __forceinline__ void ray(const Bil& B, float4& a11, float4& a12, float4& a21, float4& a22) const {
+    int i;
+    if (inside(B, i)) {
+      a22 = t0[i];
+      a21 = t0[i + 1];
+      a12 = t0[i + kIpBW];
+      a11 = t0[i + kIpBW + 1];
+    } else {
+      g.ray(B, a11, a12, a21, a22);
+    }
+  }
+  __device__ __forceinline__ void grad(const Bil& B, float4& c11, float4& c12, float4& c21, float4& c22, float& d11,
+                                       float& d12, float& d21, float& d22) const {
+    int i;
+    if (inside(B, i)) {
+      c22 = t1[i];
+      c21 = t1[i + 1];
+      c12 = t1[i + kIpBW];
+      c11 = t1[i + kIpBW + 1];
+      d22 = t2[i];
+      d21 = t2[i + 1];
+      d12 = t2[i + kIpBW];
+      d11 = t2[i + kIpBW + 1];
+    } else {
+      g.grad(B, c11, c12, c21, c22, d11, d12, d21, d22);
+    }
+  }
+};
+
+__global__ void __launch_bounds__(kIpThreads)
+    iter_proj_tile_kernel(const __grid_constant__ CUtensorMap map0, const __grid_constant__ CUtensorMap map1,
+                          const __grid_constant__ CUtensorMap map2, const float4* __restrict__ P0,
+                          const float4* __restrict__ P1, const float* __restrict__ P2, const float* __restrict__ pts,
+                          const float* __restrict__ p_init, float* __restrict__ p_new, uint8_t* __restrict__ converged,
+                          int h, int w, int max_iter, int warm, float lambda_init, float cost_thresh,
+                          unsigned long long* __restrict__ stats) {
+  extern __shared__ __align__(128) unsigned char s_raw[];
+  IterProjTileSmem& sm =  // TMA destinations must be 128-byte aligned
+      *reinterpret_cast<IterProjTileSmem*>(s_raw + ((128u - (smem_u32(s_raw) & 127u)) & 127u));
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int b = blockIdx.z;
+  const int qx = blockIdx.x * kIpQW + (tid & (kIpQW - 1)), qy = blockIdx.y * kIpQH + (tid / kIpQW);
+  const bool has = qx < w && qy < h;
+  const size_t img = (size_t)b * h * w;
+  const size_t gid = img + (size_t)qy * w + qx;
+  if (tid == 0) mbar_init(&sm.bar, 1);
+
+  float tx = 0.f, ty = 0.f, tz = 1.f;
+  float2 pi = make_float2(1.f, 1.f);
+  if (has) {
+    pi = __ldg(reinterpret_cast<const float2*>(p_init) + gid);
+    tx = __ldg(pts + gid * 3 + 0);
+    ty = __ldg(pts + gid * 3 + 1);
+    tz = __ldg(pts + gid * 3 + 2);
+  }
+  IterProjState s;
+  iter_proj_begin(s, fminf(fmaxf(pi.x, 1.0f), (float)(w - 2)), fminf(fmaxf(pi.y, 1.0f), (float)(h - 2)), w, lambda_init);
+  const GlobalRaySampler G{P0 + img, P1 + img, P2 + img};
+  const int it_warm = min(warm, max_iter);
+  if (has) iter_proj_steps(s, G, tx, ty, tz, w, h, 0, it_warm, cost_thresh);
+
+  if (it_warm < max_iter) {  // uniform over the CTA
+    // ---- mean position of the tile's queries
+    float su = has ? s.u : 0.f, sv = has ? s.v : 0.f, sc = has ? 1.f : 0.f;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      su += __shfl_xor_sync(0xffffffffu, su, o);
+      sv += __shfl_xor_sync(0xffffffffu, sv, o);
+      sc += __shfl_xor_sync(0xffffffffu, sc, o);
+    }
+    if (lane == 0) {
+      sm.red[0][warp] = su;
+      sm.red[1][warp] = sv;
+      sm.red[2][warp] = sc;
+    }
+    __syncthreads();  // also: the mbarrier is initialised
+    if (tid == 0) {
+      float mu = 0.f, mv = 0.f, mc = 0.f;
+#pragma unroll
+      for (int k = 0; k < kIpThreads / 32; k++) {
+        mu += sm.red[0][k];
+        mv += sm.red[1][k];
+        mc += sm.red[2][k];
+      }
+      // mc >= 1: a CTA always has its first query
+      // the window starts at a multiple of four pixels (floor, also for negative origins): 16-byte aligned rows in all
+      // three planes
+      const int ox = (((int)(mu / mc) - (kIpBW / 2 - 1)) >> 2) << 2, oy = (int)(mv / mc) - (kIpBH / 2 - 1);
+      sm.origin[0] = ox;
+      sm.origin[1] = oy;
+      asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+      mbar_arrive_expect_tx(&sm.bar, (unsigned)(sizeof(sm.t0) + sizeof(sm.t1) + sizeof(sm.t2)));
+      tma_load_4d(sm.t0, &map0, 4 * ox, oy, b, 0, &sm.bar);  // coordinates in floats along the row
+      tma_load_4d(sm.t1, &map1, 4 * ox, oy, b, 0, &sm.bar);
+      tma_load_4d(sm.t2, &map2, ox, oy, b, 0, &sm.bar);
+    }
+    __syncthreads();
+    TileRaySampler T{G, sm.t0, sm.t1, sm.t2, sm.origin[0], sm.origin[1]};
+    mbar_wait(&sm.bar, 0);
+    if (has) iter_proj_steps(s, T, tx, ty, tz, w, h, it_warm, max_iter, cost_thresh);
+#ifdef M3R_IP_STATS
+    if (stats != nullptr) {
+      atomicAdd(stats + 0, (unsigned long long)T.hits);
+      atomicAdd(stats + 1, (unsigned long long)T.misses);
+    }
+#endif
+  }
+  if (has) {
+    reinterpret_cast<float2*>(p_new)[gid] = make_float2(s.u, s.v);
+    converged[gid] = s.conv ? 1 : 0;
+  }
+}
+
+static unsigned long long* g_ip_stats = nullptr;
+
+// returns M3R_OK when the tile kernel ran, 1 when the caller should use the gather kernel, else an error code
+int launch_iter_proj_tile(const float4* P0, const float4* P1, const float* P2, const float* pts, const float* p_init,
+                          float* p_new, uint8_t* converged, int b, int h, int w, int max_iter, int warm,
+                          float lambda_init, float cost_thresh, cudaStream_t st) {
+  if (b > 65535 || b < 1 || (w & 3) != 0) return 1;
+  CUtensorMap m0, m1, m2;
+  // image rows are the innermost dimension of the maps: a window row is ONE request of the copy engine (512 / 512 / 128
+  // bytes), 72 requests per window.  (First version: boxes over {4 floats, w, h, b}, a request per pixel, 2304 per
+  // window -- the engine's request rate made the kernel slower than the gathers even with every corner served from the
+  // window.  A rank-3 map over the scalar plane raised an illegal instruction on the box, hence rank 4 with a unit
+  // dimension.)
+  if (!encode_row_tiles_f32(&m0, P0, b, h, 4 * w, 4 * kIpBW, kIpBH)) return 1;
+  if (!encode_row_tiles_f32(&m1, P1, b, h, 4 * w, 4 * kIpBW, kIpBH)) return 1;
+  if (!encode_row_tiles_f32(&m2, P2, b, h, w, kIpBW, kIpBH)) return 1;
+  const size_t smem = sizeof(IterProjTileSmem) + 128;
+  const dim3 grid((unsigned)ceil_div(w, kIpQW), (unsigned)ceil_div(h, kIpQH), (unsigned)b);
+  iter_proj_tile_kernel<<<grid, kIpThreads, smem, st>>>(m0, m1, m2, P0, P1, P2, pts, p_init, p_new, converged, h, w,
+                                                        max_iter, warm, lambda_init, cost_thresh, g_ip_stats);
+  M3R_LAUNCH_CHECK();
+  return M3R_OK;
+}
+
 }  // namespace m3r
+
+// diagnostics (-DM3R_IP_STATS builds only): two device counters, corner fetches served by the window / by the fallback
+extern "C" void m3r_debug_set_iter_proj_stats(unsigned long long* dev_counters) { m3r::g_ip_stats = dev_counters; }

@@ -44,6 +44,24 @@ static inline bool encode_image_tiles(CUtensorMap* map, const void* base, int b,
              CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
 }
 
+// Plane (b, h, row) of fp32 with the whole image row as the innermost dimension: rank-4 tensor {row, h, b, 1}, box =
+// {box_elems, box_h, 1, 1}.  One request of the copy engine is then box_elems * 4 contiguous bytes (at most 256 elements)
+// instead of one pixel: a box over {c, w, h, b} with c = 4 floats costs a request per pixel, and the engine's request rate,
+// not its bandwidth, then sets the pace.  row * 4 and box_elems * 4 must be multiples of 16.
+static inline bool encode_row_tiles_f32(CUtensorMap* map, const void* base, int b, int h, int row, int box_elems,
+                                        int box_h) {
+  EncodeTiledFn enc = tensormap_encoder();
+  if (enc == nullptr || (row & 3) != 0 || (box_elems & 3) != 0 || box_elems > 256) return false;
+  const cuuint64_t dims[4] = {(cuuint64_t)row, (cuuint64_t)h, (cuuint64_t)b, 1};
+  const cuuint64_t rb = (cuuint64_t)row * 4;
+  const cuuint64_t strides[3] = {rb, rb * h, rb * h * b};
+  const cuuint32_t box[4] = {(cuuint32_t)box_elems, (cuuint32_t)box_h, 1, 1};
+  const cuuint32_t estr[4] = {1, 1, 1, 1};
+  return enc(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, const_cast<void*>(base), dims, strides, box, estr,
+             CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+             CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
+
 // one box -> shared memory (128-byte aligned), completion on the mbarrier; coordinates may be negative / past the edge
 __device__ __forceinline__ void tma_load_4d(void* dst, const CUtensorMap* map, int c0, int c1, int c2, int c3,
                                             unsigned long long* bar) {

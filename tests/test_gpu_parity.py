@@ -87,6 +87,35 @@ def test_refine_matches_tile_kernel_equals_gather_kernel(be):
         lib.m3r_debug_set_refine_mode(-1)
 
 
+def test_iter_proj_tile_kernel_equals_gather_kernel(be):
+    """The TMA tile-staged iter_proj kernel (csrc/matching_tile.cu) against the per-thread gather kernel: bit-identical
+    positions and flags at 512x384 (identity start 100 px from the solution, warm start, noisy and smooth scene), on a
+    ragged image whose width the tile grid does not divide, and with a window placed after 0, 1 and 3 iterations."""
+    import os
+    from mast3r_slam_ysh_b200 import _lib, synthetic as syn
+    lib = _lib.load()
+    try:
+        for (b, h, w, noise, warm) in [(1, 384, 512, 0.005, False), (2, 384, 512, 0.0, True), (3, 36, 52, 0.005, False),
+                                       (1, 9, 12, 0.005, True)]:
+            m = syn.make_match_problem(b, h, w, seed=60 + h, device=DEV, point_noise=noise, warm_start=warm)
+            args = (m["rays_img_with_grad"], m["pts_3d_norm"], m["p_init"], MT["max_iter"], MT["lambda_init"],
+                    MT["convergence_thresh"])
+            lib.m3r_debug_set_iter_proj_mode(0)
+            pa, ca = be.iter_proj(*args)
+            lib.m3r_debug_set_iter_proj_mode(1)
+            pb, cb = be.iter_proj(*args)
+            assert torch.equal(pa, pb) and torch.equal(ca, cb), (h, w)
+            assert float((pa - m["p_init"]).abs().max()) > 1.0
+            for it in (0, 1, 2):  # fewer iterations than the warm-up, exactly the warm-up, one more
+                lib.m3r_debug_set_iter_proj_mode(0)
+                pa, ca = be.iter_proj(*args[:3], it, *args[4:])
+                lib.m3r_debug_set_iter_proj_mode(1)
+                pb, cb = be.iter_proj(*args[:3], it, *args[4:])
+                assert torch.equal(pa, pb) and torch.equal(ca, cb), (h, w, it)
+    finally:
+        lib.m3r_debug_set_iter_proj_mode(-1)
+
+
 def test_refine_matches_edge_cases(be):
     # non-positive scores never win (max_score starts at +0): all-zero descriptors keep p1; far-out p1 unchanged
     D11 = torch.zeros(1, 8, 8, 24, dtype=torch.float16, device=DEV)

@@ -39,6 +39,9 @@ small = 7 * (nkf - 1) <= 224
 prev = None
 cyc = [(tag - 10000, t) for tag, t in marks if tag >= 10000]
 marks = [m for m in marks if m[0] < 9000]
+sky_marks = [m for m in marks if 7000 <= m[0] < 8000]  # steps 20/21 of the envelope solver (SKY_MARK)
+marks = [m for m in marks if not (7000 <= m[0] < 8000)]
+if not small: names[8] = "envelope_factor"
 if any(5000 <= tag < 6000 for tag, _ in marks):  # -DM3R_PANEL_MARKS: steps inside panel 3 of CTA 0
     pm = [(tag, t) for tag, t in marks if tag < 5000 or tag in (5100, 5200, 5300, 5400, 5500)]
     for i, (tag, t) in enumerate(pm):
@@ -61,4 +64,7 @@ if cyc:  # clock64 stamps inside the single-CTA solver, relative to its start (1
         agg2.setdefault(key, []).append(c - prevc); prevc = c
     out["small_solver_cycles"] = {k: {"sum": sum(v), "max": max(v), "n": len(v)} for k, v in agg2.items()}
     out["small_solver_total_us"] = round(prevc / 1965.0, 2)
+if sky_marks:
+    t0 = sky_marks[0][1]
+    out["envelope_step_20_21_us"] = [(tag, round((t - t0) / 1e3, 2)) for tag, t in sky_marks]
 print(json.dumps(out))
