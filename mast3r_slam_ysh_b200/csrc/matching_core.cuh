@@ -8,8 +8,7 @@ namespace m3r {
 
 struct Bil {
   float w11, w12, w21, w22;
-  int o22, o21, o12, o11;  // pixel offsets of (v,u), (v,u+1), (v+1,u), (v+1,u+1)
-  int u11, v11;            // the cell itself (tile-staged samplers test it against their window)
+  int u11, v11;  // the cell: its corners are pixels (v,u) "22", (v,u+1) "21", (v+1,u) "12", (v+1,u+1) "11"
 };
 
 __device__ __forceinline__ Bil bil_setup(float u, float v, int w) {
@@ -25,10 +24,6 @@ __device__ __forceinline__ Bil bil_setup(float u, float v, int w) {
   B.w22 = __fmul_rn(cu, cv);
   B.u11 = u11;
   B.v11 = v11;
-  B.o22 = v11 * w + u11;
-  B.o21 = B.o22 + 1;
-  B.o12 = B.o22 + w;
-  B.o11 = B.o12 + 1;
   return B;
 }
 
@@ -57,22 +52,33 @@ struct GlobalRaySampler {
   const float4* __restrict__ p0;
   const float4* __restrict__ p1;
   const float* __restrict__ p2;
+  int w;
+  // one address per image row of the cell, the second corner of a row at an immediate offset (the kernel is issue-bound
+  // on smooth input, profiles/r2_iterproj_b64_ncu_full.txt, and four independent 64-bit addresses per fetch were a
+  // noticeable share of its instructions)
   __device__ __forceinline__ void ray(const Bil& B, float4& a11, float4& a12, float4& a21, float4& a22) const {
-    a11 = __ldg(p0 + B.o11);
-    a12 = __ldg(p0 + B.o12);
-    a21 = __ldg(p0 + B.o21);
-    a22 = __ldg(p0 + B.o22);
+    const float4* __restrict__ r0 = p0 + (B.v11 * w + B.u11);
+    const float4* __restrict__ r1 = r0 + w;
+    a22 = __ldg(r0);
+    a21 = __ldg(r0 + 1);
+    a12 = __ldg(r1);
+    a11 = __ldg(r1 + 1);
   }
   __device__ __forceinline__ void grad(const Bil& B, float4& c11, float4& c12, float4& c21, float4& c22, float& d11,
                                        float& d12, float& d21, float& d22) const {
-    c11 = __ldg(p1 + B.o11);
-    c12 = __ldg(p1 + B.o12);
-    c21 = __ldg(p1 + B.o21);
-    c22 = __ldg(p1 + B.o22);
-    d11 = __ldg(p2 + B.o11);
-    d12 = __ldg(p2 + B.o12);
-    d21 = __ldg(p2 + B.o21);
-    d22 = __ldg(p2 + B.o22);
+    const int o = B.v11 * w + B.u11;
+    const float4* __restrict__ r0 = p1 + o;
+    const float4* __restrict__ r1 = r0 + w;
+    c22 = __ldg(r0);
+    c21 = __ldg(r0 + 1);
+    c12 = __ldg(r1);
+    c11 = __ldg(r1 + 1);
+    const float* __restrict__ q0 = p2 + o;
+    const float* __restrict__ q1 = q0 + w;
+    d22 = __ldg(q0);
+    d21 = __ldg(q0 + 1);
+    d12 = __ldg(q1);
+    d11 = __ldg(q1 + 1);
   }
 };
 
@@ -173,7 +179,7 @@ __device__ __forceinline__ void iter_proj_core(const float4* __restrict__ p0, co
                                                bool& conv_out) {
   IterProjState s;
   iter_proj_begin(s, u, v, w, lambda_init);
-  const GlobalRaySampler S{p0, p1, p2};
+  const GlobalRaySampler S{p0, p1, p2, w};
   iter_proj_steps(s, S, tx, ty, tz, w, h, 0, max_iter, cost_thresh);
   u = s.u;
   v = s.v;

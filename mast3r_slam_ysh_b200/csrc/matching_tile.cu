@@ -288,7 +288,7 @@ __global__ void __launch_bounds__(kIpThreads)
   }
   IterProjState s;
   iter_proj_begin(s, fminf(fmaxf(pi.x, 1.0f), (float)(w - 2)), fminf(fmaxf(pi.y, 1.0f), (float)(h - 2)), w, lambda_init);
-  const GlobalRaySampler G{P0 + img, P1 + img, P2 + img};
+  const GlobalRaySampler G{P0 + img, P1 + img, P2 + img, w};
   const int it_warm = min(warm, max_iter);
   if (has) iter_proj_steps(s, G, tx, ty, tz, w, h, 0, it_warm, cost_thresh);
 
