@@ -278,12 +278,26 @@ M3R_API void m3r_debug_set_timeline(unsigned long long* dev_buf, int cap);
 
 /* diagnostics / tests: linear solver of systems with more than 224 unknowns.  0 (default): the single-CTA envelope
  * Cholesky wherever the keyframe graph's envelope fits (at most 6 active 32-row blocks), else the dense multi-CTA
- * Cholesky; 1: always the dense multi-CTA Cholesky.  Both replace Eigen::SimplicialLLT (gn_kernels.cu:115-159).
+ * Cholesky; 1: always the dense multi-CTA Cholesky; 2: envelope Cholesky without the
+ * segmentation below.  All replace Eigen::SimplicialLLT (gn_kernels.cu:115-159).
  * Process-wide; takes effect at the next solve. */
 M3R_API void m3r_debug_set_solver(int mode);
 /* lanes (1..6) of the envelope solver chosen for the solve that last used `workspace`, 0 = dense / small solver ran;
  * negative = CUDA error.  Synchronises the device. */
 M3R_API int m3r_debug_solver_lanes(const void* workspace);
+/* Segmented envelope solver (csrc/nd_plan.cuh): when the block structure of the system splits into interiors separated by
+ * a few 32-row blocks (chains and rings of keyframes with a bounded window), the interiors are eliminated by one CTA each
+ * at the same time, one CTA sums their Schur complements in a fixed order and eliminates the separators, and the
+ * interiors back-substitute in parallel.  m3r_debug_set_solver(2) keeps the plain single-CTA envelope solver.
+ * m3r_debug_solver_segments: interiors used by the solve that last used `workspace` (0 = not segmented; negative = CUDA
+ * error; synchronises the device).  m3r_debug_nd_plan runs the planner on the HOST (no GPU): adj = [nblk][4] ints, bit cb
+ * of row rb (cb <= rb) set when tile (rb, cb) of the assembled matrix is structurally non-zero; P = 0 picks the candidate
+ * like the device planner, otherwise candidate (P interiors, sw separator blocks) is simulated; plan_out receives
+ * m3r_debug_nd_plan_ints() ints (layout: NdPlan); returns the number of interiors, 0 = no valid plan.  The reference
+ * reorders inside Eigen::SimplicialLLT (AMD, gn_kernels.cu:115-159); these entry points have no counterpart there. */
+M3R_API int m3r_debug_solver_segments(const void* workspace);
+M3R_API int m3r_debug_nd_plan_ints(void);
+M3R_API int m3r_debug_nd_plan(const int* adj, int nblk, int P, int sw, int* plan_out);
 
 /* ---------------------------------------------------------------------------------------------------------
  * Host-buffer convenience wrappers (end-to-end path: pageable/pinned HOST pointers in, results back on the host).

@@ -46,6 +46,9 @@ SYMBOLS = {
     "m3r_debug_set_iter_proj_mode": (None, [_i]),
     "m3r_debug_set_iter_proj_stats": (None, [_vp]),
     "m3r_debug_solver_lanes": (_i, [_vp]),
+    "m3r_debug_solver_segments": (_i, [_vp]),
+    "m3r_debug_nd_plan_ints": (_i, []),
+    "m3r_debug_nd_plan": (_i, [_vp, _i, _i, _i, _vp]),
     "m3r_iter_proj": (_i, [_vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _f, _f, _vp]),
     "m3r_iter_proj_noalloc": (_i, [_vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _f, _f, _vp]),
     "m3r_refine_matches_f16": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _vp]),

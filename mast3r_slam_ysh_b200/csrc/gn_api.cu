@@ -7,6 +7,7 @@
 #include <atomic>
 
 #include "gn_internal.cuh"
+#include "nd_plan.cuh"
 
 namespace m3r {
 
@@ -95,7 +96,10 @@ GnLayout gn_layout(int num_kf, int num_pts, int num_edges, int num_all_edges) {
   L.off_sys = take(sizeof(double) * (size_t)L.ld * (size_t)(L.n + 1));
   L.off_lfac = take(sizeof(double) * kBlk * kBlk * (size_t)(L.nblk + 1));
   L.off_pflag = take(sizeof(int) * (size_t)(L.n / 64 + 4) * (size_t)(L.n / 64 + 5));  // pflag + pmask rows
-  L.off_sky = take(sizeof(int) * (size_t)SkyPlan::total(L.n_free));
+  // the envelope solver's plan; systems it can take (gn_fused.cu) also get the segmented schedule and its scratch
+  const bool nd = L.n > kSmallMaxN && L.nblk <= kSkyMaxBlk;
+  L.off_sky = take(sizeof(int) * (size_t)(SkyPlan::total(L.n_free) + (nd ? NdPlan::total : 0)));
+  L.off_nd = nd ? take(sizeof(double) * NdBuf::total) : 0;
   L.off_rec = take(sizeof(GnRecord) * E * (size_t)num_pts);
   L.total = o;
   return L;
@@ -142,7 +146,7 @@ __global__ void finish_kernel(const float* __restrict__ dx, const int* __restric
     const int v = t == 0   ? state[kIters]
                   : t == 1 ? state[kConverged]
                   : t == 2 ? state[kFailCount]
-                           : ((state[kBadEdges] & 0xffffff) | ((state[kSkyLanes] & 15) << 24) |
+                           : ((state[kBadEdges] & 0xfffff) | ((state[kNdSegs] & 15) << 20) | ((state[kSkyLanes] & 15) << 24) |
                               (state[kPeerTimeout] ? 0x40000000 : 0));
     info_out[t] = v;
   }

@@ -15,6 +15,7 @@
 #include "gn_finalize.cuh"
 #include "gn_sim3.cuh"
 #include "gn_small.cuh"
+#include "nd_plan.cuh"
 #include "tma.cuh"
 
 namespace m3r {
@@ -40,6 +41,8 @@ struct FusedArgs {
   int* pmask;   // [panel][64-row group] non-zero flags of the factor (for the back substitution), stride pstride
   int pstride;
   const int* sky;  // envelope plan (SkyPlan), nullptr when the envelope solver cannot run (shared memory, debug switch)
+  const int* nd;   // segmented schedule of the envelope solver (NdPlan, nd_plan.cuh), nullptr when switched off
+  double* ndbuf;   // its scratch: Schur complements and right-hand sides of the interiors, the solution (NdBuf)
   int sy_off;      // gn_fused_kernel: byte offset of the solution vector behind the phase union in dynamic shared memory
   float* dx;
   int* state;
@@ -818,9 +821,11 @@ struct SkySmem {
   DiagAux d;
   unsigned long long mbar;  // completion of the tile loads of one join (one arrival carrying the byte count)
   int lane[kSkyMaxBlk];
-  int adj[kSkyMaxBlk][4];  // bit cb of row rb: tile (rb, cb) of the ASSEMBLED matrix has a structural non-zero
+  int adj[kSkyMaxBlk][4];  // bit lo of row hi (lo <= hi): the tile of row blocks {hi, lo} has a structural non-zero to load
   int sched[kSkyMaxBlk][kSkySched];  // the whole plan: no L2 round trip on the per-step critical path
+  int order[kSkyMaxBlk];   // segmented solver: this stage's pivots in elimination order
 };
+
 
 __device__ __forceinline__ double (*sky_tile(SkySmem& sm, int la, int lb))[kSkyStride] {
   const int p = max(la, lb), q = min(la, lb);
@@ -899,10 +904,19 @@ __device__ __forceinline__ void sky_join(const FusedArgs& A, SkySmem& sm, int kb
       const int i = max(p, o), j = min(p, o);
       const int rbi = sched[2 + i], rbj = sched[2 + j];
       double (*Tt)[kSkyStride] = sky_tile(sm, sm.lane[rbi], sm.lane[rbj]);
-      if (!((sm.adj[rbi][rbj >> 5] >> (rbj & 31)) & 1)) {
+      const int hi = max(rbi, rbj), lo = min(rbi, rbj);
+      if (!((sm.adj[hi][lo >> 5] >> (lo & 31)) & 1)) {
         // a tile inside the envelope that is structurally zero in the assembled matrix (it only receives fill): no copy
         for (int piece = t0; piece < 512; piece += nthr)
           *reinterpret_cast<double2*>(&Tt[piece >> 4][(piece & 15) * 2]) = make_double2(0.0, 0.0);
+      } else if (rbi < rbj) {
+        // segmented solver: the row block precedes the column block in the matrix (a separator in front of its interior);
+        // the assembled tile is the transpose of (rbj, rbi) in the lower triangle.  Plain loads, a few tiles per interior.
+        for (int piece = t0; piece < kBlk * kBlk; piece += nthr) {
+          const int r = piece >> 5, c = piece & 31;  // source element (row r of block rbj, column c of block rbi)
+          const int row = kBlk * rbj + r, col = kBlk * rbi + c;
+          Tt[c][r] = (row < n && col < n) ? __ldcg(A.sys + (size_t)row * ld + col) : 0.0;
+        }
       } else if (kBlk * rbj + kBlk <= n) {
         const int rows = min(kBlk, n - kBlk * rbi);
         bytes += rows * (unsigned)(kBlk * sizeof(double));
@@ -947,19 +961,52 @@ __device__ __forceinline__ void sky_join_wait(const FusedArgs& A, SkySmem& sm, u
   __syncthreads();
 }
 
-__device__ __forceinline__ void sky_factor(const FusedArgs& A, SkySmem& sm, double* s_y) {
+// ND: stage `stage` of the segmented schedule (nd_plan.cuh) -- interior stage < ndP: the pivots of that interior, the
+// separator tiles start from zero and are exported at the end; stage == ndP: the separators, s_y prepared by nd_reduce.
+template <bool ND>
+__device__ __forceinline__ void sky_factor(const FusedArgs& A, SkySmem& sm, double* s_y, int stage, int ndP) {
   const int n = A.n, ld = A.ld, nblk = A.nblk;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  for (int i = tid; i < nblk; i += kFusedThreads) sm.lane[i] = __ldcg(A.sky + SkyPlan::lane(A.n_free) + i);
-  for (int i = tid; i < nblk * kSkySched; i += kFusedThreads)
-    sm.sched[i / kSkySched][i % kSkySched] = __ldcg(A.sky + SkyPlan::sched(A.n_free) + i);
-  for (int i = tid; i < nblk * 4; i += kFusedThreads) sm.adj[i >> 2][i & 3] = __ldcg(A.sky + SkyPlan::adj(A.n_free) + i);
-  for (int c = tid; c < nblk * kBlk; c += kFusedThreads) s_y[c] = (c < n) ? __ldcg(A.sys + (size_t)n * ld + c) : 0.0;
+  int cnt = nblk;
+  if (!ND) {
+    for (int i = tid; i < nblk; i += kFusedThreads) sm.lane[i] = __ldcg(A.sky + SkyPlan::lane(A.n_free) + i);
+    for (int i = tid; i < nblk * kSkySched; i += kFusedThreads)
+      sm.sched[i / kSkySched][i % kSkySched] = __ldcg(A.sky + SkyPlan::sched(A.n_free) + i);
+    for (int i = tid; i < nblk * 4; i += kFusedThreads) sm.adj[i >> 2][i & 3] = __ldcg(A.sky + SkyPlan::adj(A.n_free) + i);
+    for (int c = tid; c < nblk * kBlk; c += kFusedThreads) s_y[c] = (c < n) ? __ldcg(A.sys + (size_t)n * ld + c) : 0.0;
+  } else {
+    const int beg = __ldcg(A.nd + NdPlan::stage_begin + stage);
+    cnt = __ldcg(A.nd + NdPlan::stage_begin + stage + 1) - beg;
+    for (int i = tid; i < cnt; i += kFusedThreads) sm.order[i] = __ldcg(A.nd + NdPlan::order + beg + i);
+    for (int i = tid; i < nblk; i += kFusedThreads) sm.lane[i] = __ldcg(A.nd + NdPlan::lane + stage * kSkyMaxBlk + i);
+    for (int i = tid; i < nblk * kSkySched; i += kFusedThreads)
+      sm.sched[i / kSkySched][i % kSkySched] = __ldcg(A.nd + NdPlan::sched + i);
+    // tiles to load: an interior sees the assembled matrix without the separator-separator tiles (its Schur complement
+    // starts from zero), the separator stage sees them with the fill of the interiors
+    for (int i = tid; i < nblk * 4; i += kFusedThreads) {
+      const int rb = i >> 2, w = i & 3;
+      const unsigned in_s = (unsigned)__ldcg(A.nd + NdPlan::inS + w);
+      const bool row_s = ((unsigned)__ldcg(A.nd + NdPlan::inS + (rb >> 5)) >> (rb & 31)) & 1u;
+      unsigned v;
+      if (stage == ndP) {
+        v = (unsigned)__ldcg(A.nd + NdPlan::adjS + i);
+      } else {
+        v = (unsigned)__ldcg(A.sky + SkyPlan::adj(A.n_free) + i);
+        if (row_s) v &= ~in_s;
+      }
+      sm.adj[rb][w] = (int)v;
+    }
+    if (stage < ndP)
+      for (int c = tid; c < nblk * kBlk; c += kFusedThreads)
+        s_y[c] = (c < n && __ldcg(A.nd + NdPlan::stage_of + c / kBlk) == stage) ? __ldcg(A.sys + (size_t)n * ld + c) : 0.0;
+  }
   if (tid == 0) mbar_init(&sm.mbar, 1);
   asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
   unsigned jparity = 0;  // phase of sm.mbar the next join completes (uniform over the CTA)
   bool looked = false;   // the diagonal tile of this step was factored during the previous step (uniform over the CTA)
-  for (int kb = 0; kb < nblk; kb++) {
+  for (int step = 0; step < cnt; step++) {
+    const int kb = ND ? sm.order[step] : step;                                    // pivot block
+    const int kn = step + 1 < cnt ? (ND ? sm.order[step + 1] : step + 1) : -1;  // next pivot of this stage
     const int c0 = kb * kBlk;
     const int nb = min(kBlk, n - c0);
     asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");  // my bulk stores of the last column have read their tiles
@@ -994,12 +1041,12 @@ __device__ __forceinline__ void sky_factor(const FusedArgs& A, SkySmem& sm, doub
     // the bulk stores of this column (async proxy) read what was just written: writer-side proxy fence, then a CTA barrier,
     // then the stores.  With the look-ahead the fence waits until after the diagonal update (0.4 us on the critical path
     // right here, nothing there: the writes have long drained)
-    const bool ahead = m >= 2 && sched[3] == kb + 1;
+    const bool ahead = m >= 2 && sched[3] == kn;
     if (!ahead) asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
     __syncthreads();
     SKY_MARK(7003);
     // ---- update of the next diagonal tile first (look-ahead): thread = (4 rows, 1 column)
-    const int al1 = sm.lane[min(kb + 1, nblk - 1)];
+    const int al1 = sm.lane[kn >= 0 ? kn : kb];
     if (ahead) {
       const double (*X1)[kSkyStride] = sky_tile(sm, al1, al0);
       double (*C11)[kSkyStride] = sky_tile(sm, al1, al1);
@@ -1024,7 +1071,7 @@ __device__ __forceinline__ void sky_factor(const FusedArgs& A, SkySmem& sm, doub
     }
     SKY_MARK(7004);
     if (ahead && warp == 0) {
-      const int c1 = c0 + kBlk;
+      const int c1 = kn * kBlk;
       const bool bad = factor_diag32(&sky_tile(sm, al1, al1)[lane][0], sm.d, nullptr, min(kBlk, n - c1), lane);
       if (bad && lane == 0) A.state[kFailNow] = 1;
       SKY_MARK(7005);
@@ -1052,7 +1099,7 @@ __device__ __forceinline__ void sky_factor(const FusedArgs& A, SkySmem& sm, doub
         if (kb == 20 && tid == 224) tl_mark_any(A, 7101);
         for (int j = 1 + lw; j < m; j += nlight) sky_rhs_and_store(A, sm, s_y, sched[2 + j], al0, c0, nb, lane);
         if (kb == 20 && tid == 224) tl_mark_any(A, 7102);
-        if (kb + 1 < nblk && (sm.sched[kb + 1][1] & kSkyPrefetched)) sky_join(A, sm, kb + 1, lw * 32 + lane, nlight * 32);
+        if (kn >= 0 && (sm.sched[kn][1] & kSkyPrefetched)) sky_join(A, sm, kn, lw * 32 + lane, nlight * 32);
         if (kb == 20 && tid == 224) tl_mark_any(A, 7103);
       }
       // trailing tiles (act[i], act[j]) -= X_i X_j^T, 1 <= j <= i < m, two 16-row halves each; (1, 1) is done above
@@ -1068,7 +1115,208 @@ __device__ __forceinline__ void sky_factor(const FusedArgs& A, SkySmem& sm, doub
   }
   asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");  // every column of L has reached global memory
   __syncthreads();
+  if (ND && stage < ndP) {
+    // the interior is eliminated; what its steps accumulated on the border blocks is its Schur complement: tiles
+    // (border i, border j), j <= i, and the border parts of the right-hand side, to this interior's scratch slot
+    const int* ex = A.nd + NdPlan::exp + stage * (1 + kNdMaxBorder);
+    const int nbr = __ldcg(ex);
+    double* dst = A.ndbuf + NdBuf::schur + (size_t)stage * kNdBorderTiles * kBlk * kBlk;
+    for (int i = 0; i < nbr; i++)
+      for (int j = 0; j <= i; j++) {
+        const double (*Tt)[kSkyStride] = sky_tile(sm, sm.lane[__ldcg(ex + 1 + i)], sm.lane[__ldcg(ex + 1 + j)]);
+        double* d = dst + (size_t)(i * (i + 1) / 2 + j) * kBlk * kBlk;
+        for (int e = tid; e < kBlk * kBlk; e += kFusedThreads) d[e] = Tt[e >> 5][e & 31];
+      }
+    if (tid < nbr * kBlk)
+      A.ndbuf[NdBuf::srhs + ((size_t)stage * kNdMaxBorder + (tid >> 5)) * kBlk + lane] =
+          s_y[kBlk * __ldcg(ex + 1 + (tid >> 5)) + lane];
+  }
 }
+
+// ============================================================================================== segmented envelope solver
+// Stage layout of the launch (nd_plan.cuh): CTA 0 owns the separator stage, CTA 1 + s interior s.  Three barriers over
+// these 1 + P CTAs: interiors exported | separators solved | interiors solved.
+
+// CTA 0: right-hand side and tiles of the separator system = assembled values + the interiors' Schur complements, summed
+// in interior order by a fixed thread per element (deterministic: the replicas of a multi-GPU run stay bit-identical).
+__device__ __forceinline__ void nd_reduce(const FusedArgs& A, double* s_y, int ndP, int* s_list /* [32 + kNdMaxSeg * 8] */) {
+  const int n = A.n, ld = A.ld, nblk = A.nblk;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  int* sblk = s_list;        // separator blocks, ascending; [31] = their number
+  int* ex = s_list + 32;     // [ndP][1 + kNdMaxBorder] border lists
+  unsigned in_s[4];
+#pragma unroll
+  for (int w = 0; w < 4; w++) in_s[w] = (unsigned)__ldcg(A.nd + NdPlan::inS + w);
+  if (tid == 0) {
+    int k = 0;
+    for (int w = 0; w < 4; w++) {
+      unsigned m = in_s[w];
+      while (m && k < 31) {
+        sblk[k++] = 32 * w + __ffs((int)m) - 1;
+        m &= m - 1;
+      }
+    }
+    sblk[31] = k;
+  }
+  for (int i = tid; i < ndP * (1 + kNdMaxBorder); i += kFusedThreads) ex[i] = __ldcg(A.nd + NdPlan::exp + i);
+  __syncthreads();
+  // right-hand side: a fixed thread per element, contributions added in interior order
+  for (int c = tid; c < nblk * kBlk; c += kFusedThreads) {
+    const int rb = c / kBlk;
+    double v = 0.0;
+    if (((in_s[rb >> 5] >> (rb & 31)) & 1u) && c < n) {
+      double part[kNdMaxSeg];
+#pragma unroll
+      for (int s = 0; s < kNdMaxSeg; s++) {
+        part[s] = 0.0;
+        if (s < ndP) {
+          const int nbr = ex[s * (1 + kNdMaxBorder)];
+          for (int i = 0; i < nbr; i++)
+            if (ex[s * (1 + kNdMaxBorder) + 1 + i] == rb)
+              part[s] = __ldcg(A.ndbuf + NdBuf::srhs + ((size_t)s * kNdMaxBorder + i) * kBlk + (c & 31));
+        }
+      }
+      v = __ldcg(A.sys + (size_t)n * ld + c);
+#pragma unroll
+      for (int s = 0; s < kNdMaxSeg; s++) v += part[s];  // adding 0.0 for an interior that does not touch the block is exact
+    }
+    s_y[c] = v;
+  }
+  // tiles: one warp per pair of separator blocks (a >= b) that the separator stage will load; eight rows in flight
+  const int ns = sblk[31];
+  for (int pr = warp; pr < ns * (ns + 1) / 2; pr += kFusedThreads / 32) {
+    int ia, ib;
+    tile_decode(pr, ia, ib);
+    const int a = sblk[ia], b = sblk[ib];
+    if (!(((unsigned)__ldcg(A.nd + NdPlan::adjS + a * 4 + (b >> 5)) >> (b & 31)) & 1u)) continue;
+    const bool assembled = ((unsigned)__ldcg(A.sky + SkyPlan::adj(A.n_free) + a * 4 + (b >> 5)) >> (b & 31)) & 1u;
+    // sources: interiors whose border list holds both blocks
+    int src[kNdMaxSeg], nsrc = 0;
+    for (int s = 0; s < ndP; s++) {
+      const int nbr = ex[s * (1 + kNdMaxBorder)];
+      int pa = -1, pb = -1;
+      for (int i = 0; i < nbr; i++) {
+        const int blk = ex[s * (1 + kNdMaxBorder) + 1 + i];
+        if (blk == a) pa = i;
+        if (blk == b) pb = i;
+      }
+      if (pa >= 0 && pb >= 0) src[nsrc++] = (s * kNdBorderTiles + pa * (pa + 1) / 2 + pb);
+    }
+    if (nsrc == 0) continue;
+    const int col = kBlk * b + lane;
+    for (int r0 = 0; r0 < kBlk; r0 += 8) {
+      double v[8];
+#pragma unroll
+      for (int i = 0; i < 8; i++) {
+        const int row = kBlk * a + r0 + i;
+        v[i] = (assembled && row < n && col < n) ? __ldcg(A.sys + (size_t)row * ld + col) : 0.0;
+      }
+      for (int q = 0; q < nsrc; q++) {
+        double t[8];
+#pragma unroll
+        for (int i = 0; i < 8; i++) t[i] = __ldcg(A.ndbuf + NdBuf::schur + (size_t)src[q] * kBlk * kBlk + (r0 + i) * kBlk + lane);
+#pragma unroll
+        for (int i = 0; i < 8; i++) v[i] += t[i];
+      }
+#pragma unroll
+      for (int i = 0; i < 8; i++) {
+        const int row = kBlk * a + r0 + i;
+        if (row < n && col < n && !(a == b && lane > r0 + i)) A.sys[(size_t)row * ld + col] = v[i];
+      }
+    }
+  }
+  asm volatile("fence.proxy.async.global;" ::: "memory");  // the separator stage's joins read these through the copy engine
+  __syncthreads();
+}
+
+// Back substitution over the block rows rows[0 .. cnt) in that order.  SOLVE: x_kb = L_kk^-T y_kb first (the rows of a
+// stage, last pivot first); otherwise s_y already holds x_kb (an interior's border blocks).  Then y[c] -= L(kb, c)^T x_kb
+// for the column blocks of L's block row kb (NdPlan::lrow) that lie in `cols` -- wherever the tile sits in sys.
+struct NdBackSmem {
+  BackSmem b;
+  unsigned lrow[kSkyMaxBlk][4];
+  unsigned cols[4];
+  int rows[kSkyMaxBlk];
+  int brows[kNdMaxBorder];
+};
+
+__device__ __forceinline__ void nd_back_stage(const FusedArgs& A, BackSmem& sm, int kb, int buf) {
+  const double* src = A.lfac + (size_t)kb * kBlk * kBlk;
+  for (int l = threadIdx.x; l < kBlk * kBlk / 2; l += kFusedThreads)
+    cp_async16_zfill(&sm.L[buf][l >> 4][2 * (l & 15)], src + 2 * l, 16);
+  asm volatile("cp.async.commit_group;" ::: "memory");
+}
+
+template <bool SOLVE>
+__device__ __forceinline__ void nd_back_rows(const FusedArgs& A, NdBackSmem& sm, double* s_y, const int* rowlist, int cnt) {
+  const int n = A.n, ld = A.ld;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  if (cnt <= 0) return;
+  if (SOLVE) nd_back_stage(A, sm.b, rowlist[0], 0);
+  for (int i = 0; i < cnt; i++) {
+    const int kb = rowlist[i];
+    const int c0 = kb * kBlk;
+    const int rows = min(kBlk, n - c0);
+    if (SOLVE) {
+      asm volatile("cp.async.wait_group 0;" ::: "memory");
+      __syncthreads();  // L_kk landed for everyone; the previous row's y update is complete
+      if (i + 1 < cnt) nd_back_stage(A, sm.b, rowlist[i + 1], (i + 1) & 1);
+      if (warp == 0) {
+        const double (*L)[kBlk + 2] = sm.b.L[i & 1];
+        double yv = s_y[c0 + lane];
+        const double dinv = 1.0 / L[lane][lane];
+#pragma unroll
+        for (int j = kBlk - 1; j >= 0; j--) {
+          const double xj = shfl_d(yv * dinv, j);  // lane j holds the finished y_j
+          if (lane == j) yv = xj;
+          if (lane < j) yv -= L[j][lane] * xj;
+        }
+        s_y[c0 + lane] = yv;
+      }
+    }
+    __syncthreads();
+    // one warp per column block, one column per lane (coalesced along the row of L)
+    int slot = 0;
+    for (int w = 0; w < 4; w++) {
+      unsigned m = sm.lrow[kb][w] & sm.cols[w];
+      while (m) {
+        const int cb = 32 * w + __ffs((int)m) - 1;
+        m &= m - 1;
+        if ((slot++ & (kFusedThreads / 32 - 1)) != warp) continue;
+        const int c = kBlk * cb + lane;
+        double v[kBlk];
+#pragma unroll
+        for (int r = 0; r < kBlk; r++) v[r] = (r < rows && c < n) ? __ldcg(A.sys + (size_t)(c0 + r) * ld + c) : 0.0;
+        double a0 = 0.0, a1 = 0.0;
+#pragma unroll
+        for (int r = 0; r < kBlk; r += 2) {
+          a0 = fma(v[r], s_y[c0 + r], a0);
+          a1 = fma(v[r + 1], s_y[c0 + r + 1], a1);
+        }
+        s_y[c] -= a0 + a1;
+      }
+    }
+    if (!SOLVE) __syncthreads();
+  }
+  __syncthreads();
+}
+
+// stage tables of the back substitution: the rows of `stage` in reverse elimination order, the columns of that stage
+__device__ __forceinline__ void nd_back_setup(const FusedArgs& A, NdBackSmem& sm, int stage, int& cnt) {
+  const int tid = threadIdx.x;
+  const int beg = __ldcg(A.nd + NdPlan::stage_begin + stage);
+  cnt = __ldcg(A.nd + NdPlan::stage_begin + stage + 1) - beg;
+  for (int i = tid; i < cnt; i += kFusedThreads) sm.rows[i] = __ldcg(A.nd + NdPlan::order + beg + cnt - 1 - i);
+  for (int i = tid; i < A.nblk * 4; i += kFusedThreads) sm.lrow[i >> 2][i & 3] = (unsigned)__ldcg(A.nd + NdPlan::lrow + i);
+  if (tid < 4) sm.cols[tid] = 0;
+  __syncthreads();
+  for (int rb = tid; rb < A.nblk; rb += kFusedThreads)
+    if (__ldcg(A.nd + NdPlan::stage_of + rb) == stage) atomicOr(&sm.cols[rb >> 5], 1u << (rb & 31));
+  __syncthreads();
+}
+
+union FusedSmem;
+__device__ __forceinline__ void nd_solve(const FusedArgs& A, FusedSmem& sm, double* s_y, int ndP);
 
 // ============================================================================================== the kernel
 union FusedSmem {
@@ -1077,7 +1325,64 @@ union FusedSmem {
   UpdateSmem upd;
   BackSmem back;
   SkySmem sky;
+  NdBackSmem ndback;
+  int ndlist[32 + kNdMaxSeg * (1 + kNdMaxBorder)];
 };
+
+__device__ __forceinline__ void nd_solve(const FusedArgs& A, FusedSmem& sm, double* s_y, int ndP) {
+  const int tid = threadIdx.x;
+  const int nbar = ndP + 1;
+  double* xg = A.ndbuf + NdBuf::x;
+  if (blockIdx.x == 0) {
+    // ---- separators
+    grid_barrier(A.state, nbar);  // the interiors are eliminated, their Schur complements are in the scratch
+    tl_mark(A, 8100);
+    nd_reduce(A, s_y, ndP, sm.ndlist);
+    tl_mark(A, 8200);
+    sky_factor<true>(A, sm.sky, s_y, ndP, ndP);
+    tl_mark(A, 8300);
+    int cnt;
+    nd_back_setup(A, sm.ndback, ndP, cnt);
+    nd_back_rows<true>(A, sm.ndback, s_y, sm.ndback.rows, cnt);
+    for (int i = tid; i < cnt * kBlk; i += kFusedThreads) {
+      const int c = kBlk * sm.ndback.rows[i >> 5] + (i & 31);
+      xg[c] = s_y[c];
+    }
+    tl_mark(A, 8400);
+    grid_barrier(A.state, nbar);  // the separators' solution is out
+    grid_barrier(A.state, nbar);  // the interiors' solutions are out
+    tl_mark(A, 8500);
+    for (int c = tid; c < A.nblk * kBlk; c += kFusedThreads) s_y[c] = __ldcg(xg + c);
+    if (tid == 0) sm.ndback.b.bad = __ldcg(A.state + kFailNow);
+    __syncthreads();
+    finish_solution(A, s_y, &sm.ndback.b.bad, sm.ndback.b.norm);
+    tl_mark(A, 6);
+  } else {
+    // ---- interior s
+    const int s = blockIdx.x - 1;
+    sky_factor<true>(A, sm.sky, s_y, s, ndP);
+    grid_barrier(A.state, nbar);
+    grid_barrier(A.state, nbar);
+    int cnt;
+    nd_back_setup(A, sm.ndback, s, cnt);
+    // the border blocks' solution, then their share of this interior's right-hand side
+    const int* ex = A.nd + NdPlan::exp + s * (1 + kNdMaxBorder);
+    const int nbr = __ldcg(ex);
+    if (tid < nbr * kBlk) {
+      const int c = kBlk * __ldcg(ex + 1 + (tid >> 5)) + (tid & 31);
+      s_y[c] = __ldcg(xg + c);
+    }
+    if (tid < nbr) sm.ndback.brows[tid] = __ldcg(ex + 1 + tid);
+    __syncthreads();
+    nd_back_rows<false>(A, sm.ndback, s_y, sm.ndback.brows, nbr);
+    nd_back_rows<true>(A, sm.ndback, s_y, sm.ndback.rows, cnt);
+    for (int i = tid; i < cnt * kBlk; i += kFusedThreads) {
+      const int c = kBlk * sm.ndback.rows[i >> 5] + (i & 31);
+      xg[c] = s_y[c];
+    }
+    grid_barrier(A.state, nbar);
+  }
+}
 
 __global__ void __launch_bounds__(kFusedThreads, 1) gn_fused_kernel(const FusedArgs A) {
   extern __shared__ __align__(16) unsigned char s_raw[];
@@ -1110,10 +1415,18 @@ __global__ void __launch_bounds__(kFusedThreads, 1) gn_fused_kernel(const FusedA
   } else if ((A.phases & M3R_PH_FACTOR) && (A.phases & M3R_PH_ASSEMBLE)) {
     grid_barrier(A.state, gridDim.x);
   }
+  const int nd_p = (sky > 0 && A.nd != nullptr && (A.phases & (M3R_PH_FACTOR | M3R_PH_BACKSOLVE)) == (M3R_PH_FACTOR | M3R_PH_BACKSOLVE))
+                       ? __ldcg(A.state + kNdSegs) : 0;
+  if (nd_p > 0) {  // segmented envelope solver: factorisation, back substitution and retraction on 1 + P CTAs
+    if ((int)blockIdx.x > nd_p) return;
+    tl_mark(A, 5);
+    nd_solve(A, sm, s_y, nd_p);
+    return;
+  }
   if ((A.phases & M3R_PH_FACTOR) && sky > 0) {
     if (blockIdx.x != 0) return;
     tl_mark(A, 5);
-    sky_factor(A, sm.sky, s_y);
+    sky_factor<false>(A, sm.sky, s_y, 0, 0);
     tl_mark(A, 8);
   } else if (A.phases & M3R_PH_FACTOR) {
     // only the CTAs that can get work in block column kb take part in its two barriers; the trailing matrix shrinks, so
@@ -1201,7 +1514,7 @@ int fused_grid(const GnWs& ws) {
   int want = T * (T + 1) / 2;
   const int fin = ceil_div(ws.L.num_edges, kFusedThreads / 32);
   if (fin > want) want = fin;
-  if (want < 4) want = 4;
+  if (want < kNdMaxSeg + 1) want = kNdMaxSeg + 1;  // the segmented envelope solver: one CTA per interior + one
   const int cap = sm_count();
   return want < cap ? want : cap;
 }
@@ -1227,6 +1540,8 @@ int launch_fused(const GnWs& ws, float* Twc, float delta_thresh, int phases, cud
   a.pmask = ws.pflag() + (ws.L.n / 64 + 4);
   a.pstride = ws.L.n / 64 + 4;
   a.sky = nullptr;
+  a.nd = nullptr;
+  a.ndbuf = nullptr;
   a.sy_off = 0;
   a.dx = ws.dx();
   a.state = ws.state();
@@ -1273,6 +1588,10 @@ int launch_fused(const GnWs& ws, float* Twc, float delta_thresh, int phases, cud
   // the envelope solver's tile store (183 KB) is only reserved when that solver can run; systems beyond its range keep
   // the dense solver's footprint (101 KB + the solution vector)
   a.sky = (g_solver_mode != 1 && ws.L.nblk <= kSkyMaxBlk) ? ws.sky() : nullptr;
+  if (a.sky != nullptr && g_solver_mode != 2 && ws.L.off_nd != 0) {
+    a.nd = ws.sky() + SkyPlan::total(ws.L.n_free);
+    a.ndbuf = ws.ndbuf();
+  }
   size_t phase_smem = sizeof(PanelSmem);
   if (sizeof(UpdateSmem) > phase_smem) phase_smem = sizeof(UpdateSmem);
   if (sizeof(BackSmem) > phase_smem) phase_smem = sizeof(BackSmem);
@@ -1305,6 +1624,13 @@ extern "C" int m3r_debug_solver_lanes(const void* workspace) {
   int v = 0;  // the solver state is the first region of the workspace (gn_layout)
   if (cudaDeviceSynchronize() != cudaSuccess) return -1;
   if (cudaMemcpy(&v, (const int*)workspace + m3r::kSkyLanes, sizeof(int), cudaMemcpyDeviceToHost) != cudaSuccess) return -1;
+  return v;
+}
+
+extern "C" int m3r_debug_solver_segments(const void* workspace) {
+  int v = 0;
+  if (cudaDeviceSynchronize() != cudaSuccess) return -1;
+  if (cudaMemcpy(&v, (const int*)workspace + m3r::kNdSegs, sizeof(int), cudaMemcpyDeviceToHost) != cudaSuccess) return -1;
   return v;
 }
 

@@ -31,7 +31,8 @@ enum StateSlot {
   kCFail = 8,                  // some point of some keyframe fails the confidence gate (set by pack_points)
   kPeerTimeout = 9,            // a peer rank never arrived at the in-kernel all-reduce (multi-GPU path)
   kSkyLanes = 10,              // > 0: the envelope (skyline) factorisation applies and needs this many lanes (gn_solve.cu)
-  kStateInts = 11
+  kNdSegs = 11,                // > 0: the envelope factorisation runs segmented over this many interiors (nd_plan.cuh)
+  kStateInts = 12
 };
 
 // Envelope ("skyline") plan of the assembled system, built once per solve by skyline_plan_kernel (gn_solve.cu) from the
@@ -77,7 +78,7 @@ struct __align__(32) GnRecord {
 struct GnLayout {
   int num_kf, num_pts, num_edges, n_free, n, ld, nblk, tiles;
   size_t off_rec, off_ie, off_je, off_io, off_jo, off_partial, off_blocks, off_ecount, off_eoff, off_tstate, off_inc_off, off_inc_list, off_inc_other, off_sys,
-      off_lfac, off_pflag, off_sky, off_dx, off_state, off_uniq_flag, off_all, off_K, total;
+      off_lfac, off_pflag, off_sky, off_nd, off_dx, off_state, off_uniq_flag, off_all, off_K, total;
 };
 
 GnLayout gn_layout(int num_kf, int num_pts, int num_edges, int num_all_edges);
@@ -99,7 +100,8 @@ struct GnWs {
   double* sys() const { return (double*)(base + L.off_sys); }
   double* lfac() const { return (double*)(base + L.off_lfac); }
   int* pflag() const { return (int*)(base + L.off_pflag); }
-  int* sky() const { return (int*)(base + L.off_sky); }
+  int* sky() const { return (int*)(base + L.off_sky); }  // SkyPlan, then NdPlan (nd_plan.cuh) when off_nd != 0
+  double* ndbuf() const { return (double*)(base + L.off_nd); }  // scratch of the segmented envelope solver (gn_fused.cu)
   float* dx() const { return (float*)(base + L.off_dx); }
   int* state() const { return (int*)(base + L.off_state); }
   int* uniq_flag() const { return (int*)(base + L.off_uniq_flag); }

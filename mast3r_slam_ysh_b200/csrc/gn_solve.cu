@@ -4,6 +4,7 @@
 // (gn_kernels.cu:161-170), SparseBlock + Eigen::SimplicialLLT in fp64 on the CPU with a D2H/H2D round trip and a
 // .item() sync per iteration (:57-159, :1199-1222), and pose_retr_kernel (:415-453).
 #include "gn_sim3.cuh"
+#include "nd_plan.cuh"
 
 namespace m3r {
 
@@ -452,6 +453,33 @@ __global__ void __launch_bounds__(128) skyline_plan_kernel(int* __restrict__ sky
   }
 }
 
+// ---- segmented schedule of the envelope solver (nd_plan.cuh).  One warp, once per solve, after skyline_plan_kernel: lane c
+//      runs the symbolic elimination of candidate c (interiors x separator width), the cheapest valid one is written out by
+//      lane 0 if its chain is under 3/4 of the plain envelope's.  state[kNdSegs] = number of interiors, 0 = not segmented.
+__global__ void __launch_bounds__(32) nd_plan_kernel(int* __restrict__ sky, int n_free, int nblk, int* __restrict__ state) {
+  const int lane = threadIdx.x;
+  const int* adj = sky + SkyPlan::adj(n_free);
+  int* plan = sky + SkyPlan::total(n_free);
+  int cost = 0x7fffffff;
+  if (state[kSkyLanes] > 0 && lane < kNdCandP * kNdCandSw) {
+    int P, sw, c16;
+    nd_candidate(lane, P, sw);
+    if (nd_simulate(adj, nblk, P, sw, nullptr, &c16)) cost = c16 * 32 + lane;  // ties: the lower candidate index
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) cost = min(cost, __shfl_xor_sync(0xffffffffu, cost, o));
+  if (lane == 0) {
+    int segs = 0;
+    if (cost != 0x7fffffff && (cost >> 5) < 12 * nblk) {
+      int P, sw, c16;
+      nd_candidate(cost & 31, P, sw);
+      if (nd_simulate(adj, nblk, P, sw, plan, &c16)) segs = P;
+    }
+    if (segs == 0) plan[NdPlan::hdr] = 0;
+    state[kNdSegs] = segs;
+  }
+}
+
 int launch_index_prep(const GnWs& ws, const int64_t* local_ii, const int64_t* local_jj, const int64_t* all_ii,
                       const int64_t* all_jj, int num_all_edges, cudaStream_t st) {
   const int E = ws.L.num_edges;
@@ -474,6 +502,10 @@ int launch_index_prep(const GnWs& ws, const int64_t* local_ii, const int64_t* lo
       if (g_solver_mode != 1 && ws.L.n > kSmallMaxN && ws.L.nblk <= kSkyMaxBlk) {
         skyline_plan_kernel<<<1, 128, 0, st>>>(ws.sky(), ws.L.n_free, ws.L.nblk, ws.state());
         M3R_LAUNCH_CHECK();
+        if (g_solver_mode != 2 && ws.L.off_nd != 0 && ws.L.nblk >= 8) {
+          nd_plan_kernel<<<1, 32, 0, st>>>(ws.sky(), ws.L.n_free, ws.L.nblk, ws.state());
+          M3R_LAUNCH_CHECK();
+        }
       }
       return M3R_OK;
     }
@@ -525,3 +557,25 @@ int launch_pose_retr(float* poses, const float* dx, int num_poses, int num_fix, 
 }
 
 }  // namespace m3r
+
+// Host-side run of the planner (no GPU needed): the CPU tests check the schedule on block structures of their own.
+// adj: [nblk][4] ints, bit cb of row rb (cb <= rb) = tile (rb, cb) structurally non-zero.  P = 0: pick like the device
+// planner; otherwise simulate candidate (P, sw).  plan_out: NdPlan::total ints (m3r_debug_nd_plan_ints()).  Returns the
+// number of interiors of the plan written, 0 if the structure does not split (or the candidate is invalid).
+extern "C" int m3r_debug_nd_plan_ints(void) { return m3r::NdPlan::total; }
+extern "C" int m3r_debug_nd_plan(const int* adj, int nblk, int P, int sw, int* plan_out) {
+  using namespace m3r;
+  if (adj == nullptr || plan_out == nullptr || nblk < 1 || nblk > kSkyMaxBlk) return 0;
+  int c16 = 0;
+  if (P > 0) return nd_simulate(adj, nblk, P, sw, plan_out, &c16) ? P : 0;
+  int best = 0x7fffffff;
+  for (int c = 0; c < kNdCandP * kNdCandSw; c++) {
+    int p, w;
+    nd_candidate(c, p, w);
+    if (nd_simulate(adj, nblk, p, w, nullptr, &c16) && c16 * 32 + c < best) best = c16 * 32 + c;
+  }
+  if (best == 0x7fffffff || (best >> 5) >= 12 * nblk) return 0;
+  int p, w;
+  nd_candidate(best & 31, p, w);
+  return nd_simulate(adj, nblk, p, w, plan_out, &c16) ? p : 0;
+}

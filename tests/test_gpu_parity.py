@@ -377,6 +377,7 @@ def _long_graph(kind, nkf):
 
 @pytest.mark.parametrize("kind,nkf,expect_envelope,oracle_tol", [
     ("ring8", 70, True, 1e-4), ("chain3", 40, True, 1e-4),   # north_star tolerance
+    ("ring8", 128, True, 1e-4), ("chain3", 150, True, 2e-3),  # long enough for several interiors of the segmented solver
     # long open chains with two neighbours are weakly constrained: the fp32 rounding of the Hessian blocks (ours and the
     # oracle's accumulate in different orders) is amplified by the conditioning for EITHER solver (the dense one alone
     # runs the last case), so the oracle bar is looser there; solver-vs-solver below stays at 1e-6
@@ -397,20 +398,27 @@ def test_gn_envelope_solver_vs_dense_solver_and_oracle(be, orc, kind, nkf, expec
     (dx_o,), _ = orc.gauss_newton_rays(T_o, *[a.numpy() for a in args], *P, 1, 1e-8)
     out = {}
     try:
-        for mode in (1, 0):
+        for mode in (1, 2, 0):  # dense | plain envelope | envelope, segmented where the structure splits (the default)
             _solver_mode(mode)
             T = g["Twc"].to(DEV)
             (dx,), info = be.gauss_newton_rays(T, *[a.to(DEV) for a in args], *P, 1, 1e-8, return_info=True)
             info = info.cpu().numpy()
             assert info[2] == 0
-            out[mode] = (dx.cpu().numpy().astype(np.float64), (int(info[3]) >> 24) & 15)
+            out[mode] = (dx.cpu().numpy().astype(np.float64), (int(info[3]) >> 24) & 15, (int(info[3]) >> 20) & 15,
+                         T.cpu().numpy())
     finally:
         _solver_mode(0)
-    assert out[1][1] == 0
-    assert (out[0][1] > 0) == expect_envelope
+    assert out[1][1] == 0 and out[1][2] == 0 and out[2][2] == 0
+    assert (out[0][1] > 0) == expect_envelope and (out[2][1] > 0) == expect_envelope
+    if (kind, nkf) in (("ring8", 128), ("chain3", 150), ("chain2+loops", 90), ("chain3", 40), ("chain2", 65)):
+        assert out[0][2] >= 2, "this graph splits: the segmented schedule must have been used"
+    if not expect_envelope:
+        assert out[0][2] == 0
     nrm = np.linalg.norm(dx_o)
-    assert np.linalg.norm(out[0][0] - out[1][0]) / nrm <= 1e-6   # fp32 dx of two fp64 factorisations of the same system
-    assert np.linalg.norm(out[0][0] - dx_o) / nrm <= oracle_tol
+    for mode in (0, 2):
+        assert np.linalg.norm(out[mode][0] - out[1][0]) / nrm <= 1e-6   # fp32 dx of fp64 factorisations of the same system
+        assert np.linalg.norm(out[mode][0] - dx_o) / nrm <= oracle_tol
+        assert np.abs(out[mode][3] - out[1][3]).max() <= 1e-6            # retracted poses
     assert np.linalg.norm(out[1][0] - dx_o) / nrm <= oracle_tol
 
 

@@ -11,6 +11,7 @@ edges = syn.ring_edges(nkf, span) if span > 0 else syn.loop_closure_edges(nkf)
 g = syn.make_gn_problem(nkf, 384, 512, edges, seed=1236, device=dev)
 P = _lib.GnParams(_lib.M3R_GN_RAYS, 0, lo["sigma_ray"], lo["sigma_dist"], lo["C_conf"], lo["Q_conf"], None, 0, 0, 0, 0.0, 10, 1e-8)
 T = g["Twc"].clone()
+_lib.load().m3r_debug_set_solver(int(os.environ.get("M3R_SOLVER_MODE", "0")))  # the plan is made by gn_begin
 s = md.ShardedGaussNewton(P, T, g["Xs"], g["Cs"], g["ii"], g["jj"], g["idx_ii2jj"], g["valid_match"], g["Q"], g["all_ii"], g["all_jj"])
 lib = s.lib
 for _ in range(3): s.iterate()
@@ -33,7 +34,8 @@ torch.cuda.synchronize()
 lib.m3r_debug_set_timeline(None, 0)
 b = buf.cpu().tolist(); k = b[0]
 marks = [(b[2 * (i + 1)], b[2 * (i + 1) + 1]) for i in range(k)]
-names = {1: "start", 2: "finalize+zero", 3: "barrier", 4: "assemble", 5: "barrier/start-factor", 6: "backsolve|finish", 7: "small_backsolve", 8: "small_load"}
+names = {1: "start", 2: "finalize+zero", 3: "barrier", 4: "assemble", 5: "barrier/start-factor", 6: "backsolve|finish", 7: "small_backsolve", 8: "small_load",
+         8100: "nd_interiors_eliminated(wait)", 8200: "nd_reduce", 8300: "nd_separator_factor", 8400: "nd_separator_backsolve", 8500: "nd_interiors_backsolve(wait)"}
 agg = {}
 small = 7 * (nkf - 1) <= 224
 prev = None
@@ -53,7 +55,8 @@ for tag, t in marks:
     if tag == 1: prev = t; continue
     key = names.get(tag) or ({1: "first_factor(kb=0 only)", 2: "trsm", 3: "diagupd+factor_next||update"} if small else {1: "panel", 2: "barrier_after_panel", 3: "update", 4: "barrier_after_update"})[tag // 1000]
     agg.setdefault(key, []).append((t - prev) / 1e3); prev = t
-out = {"nkf": nkf, "n": 7 * (nkf - 1), "marks": k}
+out = {"nkf": nkf, "n": 7 * (nkf - 1), "marks": k, "solver_mode": int(os.environ.get("M3R_SOLVER_MODE", "0")),
+       "segments": int(lib.m3r_debug_solver_segments(C.c_void_p(s.ws_ptr)))}
 for key, v in agg.items():
     out[key] = {"count": len(v), "sum_us": round(sum(v), 2), "max_us": round(max(v), 2), "first_us": round(v[0], 2)}
 if cyc:  # clock64 stamps inside the single-CTA solver, relative to its start (1.965 GHz)

@@ -15,9 +15,11 @@ def timed(fn, reps):
     for _ in range(reps): fn()
     b.record(); torch.cuda.synchronize(); return a.elapsed_time(b) / reps
 T = g["Twc"].clone()
+_lib.load().m3r_debug_set_solver(int(os.environ.get("M3R_SOLVER_MODE", "0")))  # 2: plain envelope solver, 1: dense
 mk = lambda: md.ShardedGaussNewton(P, T, g["Xs"], g["Cs"], g["ii"], g["jj"], g["idx_ii2jj"], g["valid_match"], g["Q"], g["all_ii"], g["all_jj"])
 s = mk(); torch.cuda.synchronize()
-res = {"nkf": nkf, "E": int(g["ii"].numel()), "n": 7 * (nkf - 1)}
+res = {"nkf": nkf, "E": int(g["ii"].numel()), "n": 7 * (nkf - 1), "solver_mode": int(os.environ.get("M3R_SOLVER_MODE", "0")),
+       "segments": int(s.lib.m3r_debug_solver_segments(__import__("ctypes").c_void_p(s.ws_ptr)))}
 tmp = mk(); del tmp; torch.cuda.synchronize()  # leave a cached block of workspace size so begin_ms excludes cudaMalloc
 res["begin_ms"] = timed(lambda: mk(), 3)
 lib = s.lib; import ctypes as C
