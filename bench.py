@@ -438,8 +438,10 @@ def run_ours(args):
         extra["solve_other_ms_per_iter"] = value - hess_ms
         extra["iterations_executed"] = iters
         lanes = (int(info_keep["info"].cpu()[3]) >> 24) & 15
+        segs = (int(info_keep["info"].cpu()[3]) >> 20) & 15
         n_sys = 7 * (nkf - 1)
         extra["linear_solver"] = ("single-CTA shared-memory Cholesky (n = %d)" % n_sys if n_sys <= 224 else
+                                  "segmented envelope Cholesky, %d interiors on %d CTAs, %d lanes (n = %d)" % (segs, segs + 1, lanes, n_sys) if segs > 0 else
                                   "single-CTA envelope Cholesky, %d lanes (n = %d)" % (lanes, n_sys) if lanes > 0 else
                                   "dense multi-CTA Cholesky (n = %d)" % n_sys)
         cpu_base = cpu_gn_sample(1, device=dev)[0] if world == 1 else None

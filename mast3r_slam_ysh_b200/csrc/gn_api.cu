@@ -98,7 +98,7 @@ GnLayout gn_layout(int num_kf, int num_pts, int num_edges, int num_all_edges) {
   L.off_pflag = take(sizeof(int) * (size_t)(L.n / 64 + 4) * (size_t)(L.n / 64 + 5));  // pflag + pmask rows
   // the envelope solver's plan; systems it can take (gn_fused.cu) also get the segmented schedule and its scratch
   const bool nd = L.n > kSmallMaxN && L.nblk <= kSkyMaxBlk;
-  L.off_sky = take(sizeof(int) * (size_t)(SkyPlan::total(L.n_free) + (nd ? NdPlan::total : 0)));
+  L.off_sky = take(sizeof(int) * (size_t)(SkyPlan::total(L.n_free) + (nd ? kNdCandP * kNdCandSw * NdPlan::total + 8 : 0)));
   L.off_nd = nd ? take(sizeof(double) * NdBuf::total) : 0;
   L.off_rec = take(sizeof(GnRecord) * E * (size_t)num_pts);
   L.total = o;

@@ -1420,7 +1420,9 @@ __global__ void __launch_bounds__(kFusedThreads, 1) gn_fused_kernel(const FusedA
   if (nd_p > 0) {  // segmented envelope solver: factorisation, back substitution and retraction on 1 + P CTAs
     if ((int)blockIdx.x > nd_p) return;
     tl_mark(A, 5);
-    nd_solve(A, sm, s_y, nd_p);
+    FusedArgs B = A;  // the planner's winning candidate (gn_solve.cu)
+    B.nd = A.nd + (size_t)__ldcg(A.state + kNdSlot) * NdPlan::total;
+    nd_solve(B, sm, s_y, nd_p);
     return;
   }
   if ((A.phases & M3R_PH_FACTOR) && sky > 0) {

@@ -32,7 +32,8 @@ enum StateSlot {
   kPeerTimeout = 9,            // a peer rank never arrived at the in-kernel all-reduce (multi-GPU path)
   kSkyLanes = 10,              // > 0: the envelope (skyline) factorisation applies and needs this many lanes (gn_solve.cu)
   kNdSegs = 11,                // > 0: the envelope factorisation runs segmented over this many interiors (nd_plan.cuh)
-  kStateInts = 12
+  kNdSlot = 12,                // which of the planner's candidate plans it is
+  kStateInts = 13
 };
 
 // Envelope ("skyline") plan of the assembled system, built once per solve by skyline_plan_kernel (gn_solve.cu) from the

@@ -453,30 +453,32 @@ __global__ void __launch_bounds__(128) skyline_plan_kernel(int* __restrict__ sky
   }
 }
 
-// ---- segmented schedule of the envelope solver (nd_plan.cuh).  One warp, once per solve, after skyline_plan_kernel: lane c
-//      runs the symbolic elimination of candidate c (interiors x separator width), the cheapest valid one is written out by
-//      lane 0 if its chain is under 3/4 of the plain envelope's.  state[kNdSegs] = number of interiors, 0 = not segmented.
-__global__ void __launch_bounds__(32) nd_plan_kernel(int* __restrict__ sky, int n_free, int nblk, int* __restrict__ state) {
-  const int lane = threadIdx.x;
-  const int* adj = sky + SkyPlan::adj(n_free);
-  int* plan = sky + SkyPlan::total(n_free);
-  int cost = 0x7fffffff;
-  if (state[kSkyLanes] > 0 && lane < kNdCandP * kNdCandSw) {
+// ---- segmented schedule of the envelope solver (nd_plan.cuh), once per solve, after skyline_plan_kernel.  The symbolic
+//      elimination is serial integer code (~0.18 ms at 256 keyframes): one candidate (interiors x separator width) per
+//      CTA, one thread each, every valid candidate writes its whole plan into its own slot, the cheapest one is picked with
+//      an atomic minimum and the CTA that finishes last publishes it if its chain is under 3/4 of the plain envelope's:
+//      state[kNdSegs] = number of interiors (0 = not segmented), state[kNdSlot] = the slot.  (As lanes of one warp the 21
+//      candidates diverged and ran one after the other: 1.0 ms.)
+__global__ void __launch_bounds__(32) nd_plan_kernel(int* __restrict__ sky, int n_free, int nblk, int* __restrict__ state,
+                                                     int* __restrict__ ticket /* [0] best cost, [1] CTAs done */) {
+  if (threadIdx.x != 0) return;
+  if (state[kSkyLanes] > 0) {
     int P, sw, c16;
-    nd_candidate(lane, P, sw);
-    if (nd_simulate(adj, nblk, P, sw, nullptr, &c16)) cost = c16 * 32 + lane;  // ties: the lower candidate index
+    nd_candidate(blockIdx.x, P, sw);
+    int* plan = sky + SkyPlan::total(n_free) + (size_t)blockIdx.x * NdPlan::total;
+    if (nd_simulate(sky + SkyPlan::adj(n_free), nblk, P, sw, plan, &c16)) atomicMin(ticket, c16 * 32 + (int)blockIdx.x);
   }
-#pragma unroll
-  for (int o = 16; o > 0; o >>= 1) cost = min(cost, __shfl_xor_sync(0xffffffffu, cost, o));
-  if (lane == 0) {
-    int segs = 0;
-    if (cost != 0x7fffffff && (cost >> 5) < 12 * nblk) {
-      int P, sw, c16;
-      nd_candidate(cost & 31, P, sw);
-      if (nd_simulate(adj, nblk, P, sw, plan, &c16)) segs = P;
+  __threadfence();
+  if (atomicAdd(ticket + 1, 1) == (int)gridDim.x - 1) {  // last CTA: every plan and the minimum are visible
+    __threadfence();
+    const int cost = atomicMin(ticket, 0x7fffffff);
+    int segs = 0, slot = 0;
+    if (cost < 0x7f000000 && (cost >> 5) < 12 * nblk) {  // (the ticket starts at 0x7f7f7f7f: no valid candidate)
+      slot = cost & 31;
+      segs = sky[SkyPlan::total(n_free) + (size_t)slot * NdPlan::total + NdPlan::hdr];
     }
-    if (segs == 0) plan[NdPlan::hdr] = 0;
     state[kNdSegs] = segs;
+    state[kNdSlot] = slot;
   }
 }
 
@@ -503,7 +505,10 @@ int launch_index_prep(const GnWs& ws, const int64_t* local_ii, const int64_t* lo
         skyline_plan_kernel<<<1, 128, 0, st>>>(ws.sky(), ws.L.n_free, ws.L.nblk, ws.state());
         M3R_LAUNCH_CHECK();
         if (g_solver_mode != 2 && ws.L.off_nd != 0 && ws.L.nblk >= 8) {
-          nd_plan_kernel<<<1, 32, 0, st>>>(ws.sky(), ws.L.n_free, ws.L.nblk, ws.state());
+          int* ticket = ws.sky() + SkyPlan::total(ws.L.n_free) + kNdCandP * kNdCandSw * NdPlan::total;
+          M3R_CUDA(cudaMemsetAsync(ticket, 0x7f, sizeof(int), st));
+          M3R_CUDA(cudaMemsetAsync(ticket + 1, 0, sizeof(int), st));
+          nd_plan_kernel<<<kNdCandP * kNdCandSw, 32, 0, st>>>(ws.sky(), ws.L.n_free, ws.L.nblk, ws.state(), ticket);
           M3R_LAUNCH_CHECK();
         }
       }

@@ -26,7 +26,7 @@ constexpr int kNdBorderTiles = kNdMaxBorder * (kNdMaxBorder + 1) / 2;
 
 // int offsets inside the plan region (workspace: sky + SkyPlan::total(n_free))
 struct NdPlan {
-  static constexpr int hdr = 0;                                        // [8] P (0: off), separator blocks, lanes, sw, cost x 16
+  static constexpr int hdr = 0;                                        // [8] P (0: off), separator blocks, lanes, sw, cost x 16, [5] = planner scratch (best candidate)
   static constexpr int stage_begin = 8;                                // [kNdMaxSeg + 2] into order
   static constexpr int order = stage_begin + kNdMaxSeg + 2;            // [kSkyMaxBlk] pivot blocks in elimination order
   static constexpr int pos = order + kSkyMaxBlk;                       // [kSkyMaxBlk] inverse of order

@@ -62,8 +62,9 @@ def run_single(kind, g):
 
 
 # (kind, keyframes, h, w, graph): n = 77 (small single-CTA solver, packed system), n = 273 and n = 553 (envelope solver,
-# row-major system; the plan is built from ALL ranks' edges), n = 413 with loop closures everywhere (dense multi-CTA solver)
-CASES = [("rays", 12, 96, 128, 3), ("rays", 40, 48, 64, 3), ("rays", 80, 24, 32, 8), ("rays", 60, 24, 32, 0),
+# row-major system; the plan is built from ALL ranks' edges), n = 889 (envelope solver, segmented over four interiors),
+# n = 413 with loop closures everywhere (dense multi-CTA solver)
+CASES = [("rays", 12, 96, 128, 3), ("rays", 40, 48, 64, 3), ("rays", 80, 24, 32, 8), ("rays", 128, 16, 24, 8), ("rays", 60, 24, 32, 0),
          ("calib", 12, 96, 128, 3), ("points", 12, 96, 128, 3)]
 for kind, nkf, h, w, span in CASES:
     edges = syn.ring_edges(nkf, span) if span > 0 else syn.loop_closure_edges(nkf, n_loop=3, seed=2)
@@ -81,8 +82,9 @@ for kind, nkf, h, w, span in CASES:
         dist.all_gather(gath, T2)
         same = all(torch.equal(gath[0], x) for x in gath)
         res[mode] = {"pose_rel_vs_single_gpu": rel, "replicas_bit_identical": same, "info": info.tolist(),
+                     "solver_lanes": (info.tolist()[3] >> 24) & 15, "solver_segments": (info.tolist()[3] >> 20) & 15,
                      "gt_err": float((T2 - g["Twc_gt"]).abs().max())}
-        ok = ok and rel < (1e-5 if span == 3 else 1e-4) and same and (info.tolist()[3] & ~(15 << 24)) == 0
+        ok = ok and rel < (1e-5 if span == 3 else 1e-4) and same and (info.tolist()[3] & ~((15 << 24) | (15 << 20))) == 0
         keep[mode] = T2
     res["peer_equals_nccl_bits"] = bool(torch.equal(keep["peer"], keep["nccl"]))
     ok = ok and res["peer_equals_nccl_bits"]

@@ -7,7 +7,7 @@ timeout 900 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --mas
 tail -5 $O/bench_n$N.err | cut -c1-300
 python - <<PY
 import json
-d=json.load(open("$O/bench_n$N.json"))
+d=[json.loads(l) for l in open("$O/bench_n$N.json") if l.startswith("{")][-1]
 print({k:d[k] for k in ("value","n_gpus","ms_per_step")}, d["e2e"]["value"], d["extra"].get("hessian_kernel_ms"), d["extra"].get("linear_solver"))
 print(json.dumps(d["extra"]["configs4_strong_scaling"]))
 PY
