@@ -38,12 +38,29 @@ __host__ __device__ __forceinline__ size_t small_smem_bytes(int n) {
   return sizeof(double) * (size_t)prow(n + 1) + sizeof(SmallAux);
 }
 
-__device__ __forceinline__ double small_rsqrt(double x) {  // see fast_rsqrt in gn_fused.cu
+// 1/sqrt(x) on the serial pivot chain: a MUFU seed and two Newton steps in fp64 (error 1.5 e^2 per step: below 1 ulp after
+// the second).  x <= 0 or NaN is reported by the caller; a pivot outside the seed's range yields inf/NaN, which the back
+// substitution treats as a failed factorisation.
+#ifndef M3R_DIAG_V2
+#define M3R_DIAG_V2 1
+#endif
+__device__ __forceinline__ double small_rsqrt(double x) {
+#if M3R_DIAG_V2
+  // fp64 seed straight from the special-function unit (MUFU.RSQ64H, ~2^-22) instead of F2F -> MUFU.RSQ -> F2F, and the
+  // Newton step as y + y (1/2 - (x/2) y^2): three dependent fp64 operations instead of four
+  double y;
+  asm("rsqrt.approx.ftz.f64 %0, %1;" : "=d"(y) : "d"(x));
+  const double hx = 0.5 * x;
+  y = fma(y, fma(-hx, y * y, 0.5), y);
+  y = fma(y, fma(-hx, y * y, 0.5), y);
+  return y;
+#else
   double y = (double)rsqrtf((float)x);
   const double hx = 0.5 * x;
   y = y * (1.5 - hx * y * y);
   y = y * (1.5 - hx * y * y);
   return y;
+#endif
 }
 
 __device__ __forceinline__ double small_shfl(double v, int src) {
@@ -69,13 +86,27 @@ __device__ __noinline__ bool factor_diag32(double* myrow, DiagAux& d, double* di
     a[c] = v;
   }
   bool bad = false;
+#if M3R_DIAG_V2
+  double djj_next = small_shfl(a[0], 0);
+#endif
 #pragma unroll
   for (int j = 0; j < kBlk; j++) {
+#if M3R_DIAG_V2
+    const double djj = djj_next;
+#else
     const double djj = small_shfl(a[j], j);
+#endif
     if (!(djj > 0.0)) bad = true;  // also catches NaN
     const double inv = small_rsqrt(djj);
     const double l = (lane == j) ? djj * inv : a[j] * inv;
     a[j] = l;
+#if M3R_DIAG_V2
+    // The next pivot only needs row j + 1's OWN entry of this column: lane j + 1 updates its diagonal from its register
+    // and the value goes round by shuffle, so the serial chain is rsqrt -> multiply -> fma -> shuffle and no longer waits
+    // for the column's trip through shared memory (which the off-diagonal updates below still take, off the chain).
+    // Bitwise the same value as the update below computes for that entry.
+    if (j + 1 < kBlk) djj_next = small_shfl(fma(-l, l, a[j + 1]), j + 1);
+#endif
     d.col[lane] = l;
     // every lane stores the same value: a lane-0-only store is a divergent region per pivot (BSSY / BRA / BSYNC in the
     // middle of the serial chain), which cost ~100 cycles per pivot (r1)
