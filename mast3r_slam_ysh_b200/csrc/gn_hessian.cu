@@ -473,6 +473,9 @@ __device__ __forceinline__ void pair_accumulate(V2 (&acc)[kAcc], const EdgeConst
 // segment and refills a stage itself, so no warp waits for the slowest one before copies are issued: 79.6 / 955 us with 3
 // stages (4: 82.1 / 966, 6: 80.0 / 959, 8: 81.1 / 968; profiles/r2_hessian_v8_variants.txt).  Also tried on v7 and dropped:
 // 4 CTAs per SM under a 128-register cap (88 B of spills: 91 / 1141 us), 96-thread CTAs x 5 (118 / 1514 us).
+#ifndef M3R_HESS_EVICT_FIRST
+#define M3R_HESS_EVICT_FIRST 1  // record loads carry an L2 evict-first policy (tma.cuh)
+#endif
 #ifndef M3R_HESS_WARPRING
 #define M3R_HESS_WARPRING 1
 #endif
@@ -597,6 +600,9 @@ __global__ void __launch_bounds__(kHessThreads, kHessCtasPerSm) hessian_kernel(c
     // form one sequence, so the copies run ahead ACROSS segment boundaries.
     int pseg = 0, pkb = 0, pend = 0;
     warp_slice(0, pkb, pend);
+#if M3R_HESS_EVICT_FIRST
+    const unsigned long long l2pol = l2_policy_evict_first();
+#endif
     auto issue_next = [&]() {
       while (pseg < nseg && pkb >= pend) {  // skip segments in which this warp has no records (left)
         pseg++;
@@ -607,7 +613,11 @@ __global__ void __launch_bounds__(kHessThreads, kHessCtasPerSm) hessian_kernel(c
       if (lane == 0) {
         const unsigned bytes = (unsigned)min(kWarpTile, pend - pkb) * (unsigned)sizeof(GnRecord);
         mbar_arrive_expect_tx(&ring.full[warp][st], bytes);
+#if M3R_HESS_EVICT_FIRST
+        bulk_g2s_hint(&ring.r[warp][st][0], rec + (size_t)plan.e[pseg] * num_pts + pkb, bytes, &ring.full[warp][st], l2pol);
+#else
         bulk_g2s(&ring.r[warp][st][0], rec + (size_t)plan.e[pseg] * num_pts + pkb, bytes, &ring.full[warp][st]);
+#endif
       }
       issued++;
       pkb += kWarpTile;

@@ -36,6 +36,21 @@ __device__ __forceinline__ void bulk_g2s(void* dst, const void* src, unsigned by
                "l"(src), "r"(bytes), "r"(smem_u32(b))
                : "memory");
 }
+// same, with an L2 eviction policy (l2_policy_evict_first(): lines of a stream that is read once leave L2 first, so a pass
+// over hundreds of MB does not push everything else -- the next kernel's instructions included -- out of the 126 MB L2)
+__device__ __forceinline__ unsigned long long l2_policy_evict_first() {
+  unsigned long long pol;
+  asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol));
+  return pol;
+}
+__device__ __forceinline__ void bulk_g2s_hint(void* dst, const void* src, unsigned bytes, unsigned long long* b,
+                                              unsigned long long policy) {
+  asm volatile(
+      "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1], %2, [%3], %4;" ::"r"(
+          smem_u32(dst)),
+      "l"(src), "r"(bytes), "r"(smem_u32(b)), "l"(policy)
+      : "memory");
+}
 // hint: bring [src, src + bytes) into L2 (16-byte aligned, size a multiple of 16); no completion to wait for
 __device__ __forceinline__ void bulk_prefetch_l2(const void* src, unsigned bytes) {
   asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(src), "r"(bytes) : "memory");
