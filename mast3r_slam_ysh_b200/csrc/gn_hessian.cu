@@ -105,7 +105,11 @@ __global__ void __launch_bounds__(256) pack_edges_kernel(const float* __restrict
   const float* __restrict__ Xi = Xs + 3 * (size_t)(edge_ok ? ix : 0) * num_pts;
   const float* __restrict__ Xj = Xs + 3 * (size_t)(edge_ok ? jx : 0) * num_pts;
   const long long* __restrict__ idx_e = reinterpret_cast<const long long*>(idx) + eb;
-#pragma unroll 2
+#ifndef M3R_PACK_UNROLL
+#define M3R_PACK_UNROLL 2
+#endif
+  constexpr int kPackUnroll = M3R_PACK_UNROLL;
+#pragma unroll kPackUnroll
   for (int p = 0; p < kPasses; p++) {
     const int lk = p * 1024 + warp * 128 + lane * 4;  // pixel offset inside the tile
     const int k = tile * kTilePix + lk;
