@@ -1202,7 +1202,10 @@ __device__ __forceinline__ void nd_reduce(const FusedArgs& A, double* s_y, int n
       }
       if (pa >= 0 && pb >= 0) src[nsrc++] = (s * kNdBorderTiles + pa * (pa + 1) / 2 + pb);
     }
-    if (nsrc == 0) continue;
+    // no source and assembled: sys already holds the tile.  No source and NOT assembled: the tile only receives fill
+    // inside the separator stage, but that stage loads every tile of its plan from sys -- which, outside the envelope that
+    // the assembly zeroes, still holds the factor of the previous iteration: write the zeros.
+    if (nsrc == 0 && assembled) continue;
     const int col = kBlk * b + lane;
     for (int r0 = 0; r0 < kBlk; r0 += 8) {
       double v[8];

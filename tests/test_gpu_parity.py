@@ -422,6 +422,41 @@ def test_gn_envelope_solver_vs_dense_solver_and_oracle(be, orc, kind, nkf, expec
     assert np.linalg.norm(out[1][0] - dx_o) / nrm <= oracle_tol
 
 
+def test_gn_segmented_solver_full_solve_and_failure(be):
+    """Ten iterations on a 128-keyframe ring (four interiors): the segmented envelope solver must land on the poses of the
+    plain envelope solver and of the dense solver and converge towards the ground truth; with no valid match anywhere
+    (singular interiors AND separators) it must report failures and leave the poses alone (gn_kernels.cu:147-150)."""
+    from mast3r_slam_ysh_b200 import synthetic as syn
+    nkf = 128
+    g = syn.make_gn_problem(nkf, 24, 32, syn.ring_edges(nkf, 8), seed=8, yaw_step_deg=5.0)
+    args = [g[k].to(DEV) for k in ("Xs", "Cs", "ii", "jj", "idx_ii2jj", "valid_match", "Q")]
+    P = (LO["sigma_ray"], LO["sigma_dist"], LO["C_conf"], LO["Q_conf"])
+    res = {}
+    try:
+        for mode in (1, 2, 0):
+            _solver_mode(mode)
+            T = g["Twc"].to(DEV)
+            _, info = be.gauss_newton_rays(T, *args, *P, 10, 1e-8, return_info=True)
+            info = info.cpu().numpy()
+            assert info[2] == 0
+            res[mode] = (T.cpu().numpy(), (int(info[3]) >> 20) & 15, int(info[0]))
+        _solver_mode(0)
+        T = g["Twc"].to(DEV)
+        bad = list(args)
+        bad[5] = torch.zeros_like(bad[5])
+        (dx,), info = be.gauss_newton_rays(T, *bad, *P, 3, 1e-8, return_info=True)
+        info = info.cpu().numpy()
+        assert (int(info[3]) >> 20) & 15 >= 2 and info[2] >= 1
+        assert not dx.any() and torch.equal(T.cpu(), g["Twc"])
+    finally:
+        _solver_mode(0)
+    assert res[0][1] >= 2 and res[1][1] == 0 and res[2][1] == 0
+    assert res[0][2] == res[1][2] == res[2][2]                      # same number of iterations executed
+    assert np.abs(res[0][0] - res[1][0]).max() <= 2e-5 and np.abs(res[0][0] - res[2][0]).max() <= 2e-5
+    gt = g["Twc_gt"].numpy()
+    assert np.abs(res[0][0] - gt).max() < 0.5 * np.abs(g["Twc"].numpy() - gt).max()
+
+
 def test_gn_envelope_solver_failure_is_not_an_error(be):
     """A singular system on the envelope path (no valid match anywhere): dx = 0, poses untouched, failure counted
     (gn_kernels.cu:147-150), exactly like the other two solvers."""
