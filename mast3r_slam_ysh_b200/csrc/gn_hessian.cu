@@ -43,6 +43,12 @@ __global__ void __launch_bounds__(256) conf_scan_kernel(const float* __restrict_
 //            point of frame i (already normalised for the ray residual), the point of frame j and sqrt(q).  The
 //            data-dependent gathers Xs[ix][idx], Cs[ix][idx] (gn_kernels.cu:916-918, 951) are paid once per solve here
 //            instead of once per iteration, and the Hessian kernel becomes a pure stream (TMA bulk copies, no gather).
+// Where the 0.46 ms at configs[2] go (r2, kernel cut short after each phase): phase 1 0.18, scan + compaction 0.15,
+// records 0.13 ms; DRAM traffic 1.06 GB = 2.3 TB/s; ncu: long scoreboard 12 and barrier 8 stall cycles per issue.  Tried and
+// dropped: unrolling phase 1 1/4/8 x (0.538-0.555 ms, no change); a warp-independent version (a warp owns 1024 pixels
+// from the gates to the records, one chained-scan slot per warp, no CTA barrier after the ticket): correct, bit-identical
+// records, but SLOWER, 0.63 against 0.54 ms for the whole pre-pass -- eight times as many chained-scan slots to poll and
+// 32 instead of 256 gathers in flight per round of the record phase cost more than the barriers did.
 __device__ __forceinline__ int ld_acquire(const int* p) {
   int v;
   asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
