@@ -5,9 +5,12 @@
 // 16-byte loads per query through L1 (l1tex 97 % busy, profiles/r1_refine_v1_ncu_full.txt), although neighbouring queries
 // look at nearly the same window of D11.  Here a CTA owns a 16 x 16 tile of query pixels.  Per dilation level it
 //   1. takes the mean of its queries' current centres (one block reduction),
-//   2. has ONE thread fetch the box of D11 around that mean with a 4-D TMA tensor copy (cp.async.bulk.tensor, SASS
-//      UTMALDG; 48 x 48 pixels for the wide levels, 32 x 32 for the narrow ones; out-of-image pixels are zero-filled by
-//      the copy engine), completion on an mbarrier,
+//   2. has ONE thread fetch the box of D11 around that mean with TMA tensor copies (cp.async.bulk.tensor, SASS UTMALDG;
+//      48 x 48 pixels for the wide levels, 32 x 32 for the narrow ones; out-of-image pixels are zero-filled by the copy
+//      engine), completion on an mbarrier.  The maps have the IMAGE ROW as innermost dimension and a box is fetched as
+//      column groups of 16 pixels (16 x 48 B = 192 fp32 elements, the copy engine takes at most 256 per request): 144
+//      requests per 48 x 48 box.  The first version described a box over {fdim, w, h, b}: one request per PIXEL, 2304 per
+//      box and 11.5 k per CTA, and the copy engine's request rate (~10 cycles each), not the scoring, set the pace,
 //   3. scores out of shared memory: every query whose whole (2 r d + 1)^2 window lies inside the box reads its candidates
 //      with LDS.128 (48-byte pixel pitch: conflict-free for neighbouring pixels), the others -- stragglers whose centre
 //      left the neighbourhood -- fall back to global loads,
@@ -25,10 +28,11 @@ constexpr int kRtQ = 16;        // query tile edge
 constexpr int kRtThreads = kRtQ * kRtQ;
 constexpr int kRtBoxBig = 48;   // box edge for levels with 16 + 2 r d <= 48
 constexpr int kRtBoxSmall = 32;
+constexpr int kRtGroup = 16;    // pixels per column group = one copy request per box row
 
 template <int FDIM>
 struct RefineTileSmem {
-  uint4 tile[kRtBoxBig * kRtBoxBig * (FDIM / 8)];  // dense box, row pitch box * FDIM * 2 bytes
+  uint4 tile[kRtBoxBig * kRtBoxBig * (FDIM / 8)];  // box as column groups of 16 pixels: [group][row][16 px][FDIM halves]
   unsigned long long bar;
   int red[3][kRtThreads / 32];
   int origin[3];  // ox, oy, box edge (0: no box this level)
@@ -103,7 +107,9 @@ __global__ void __launch_bounds__(kRtThreads, 2)
         oy = (int)(sv / sc) - box / 2;
         edge = box;
         mbar_arrive_expect_tx(&sm.bar, (unsigned)(box * box * FDIM * 2));
-        tma_load_4d(sm.tile, box == kRtBoxSmall ? &map_small : &map_big, 0, ox, oy, b, &sm.bar);
+        for (int g = 0; g < box / kRtGroup; g++)  // coordinates along the row in fp32 elements (FDIM / 2 per pixel)
+          tma_load_4d(sm.tile + (size_t)g * box * kRtGroup * NV, box == kRtBoxSmall ? &map_small : &map_big,
+                      (ox + kRtGroup * g) * (FDIM / 2), oy, b, 0, &sm.bar);
       }
       sm.origin[0] = ox;
       sm.origin[1] = oy;
@@ -126,7 +132,8 @@ __global__ void __launch_bounds__(kRtThreads, 2)
           for (int jj = 0; jj < NJ; jj++) {
             const int v = v0 - rd + jj * d;
             in[jj] = v >= 0 && v < h;
-            const uint4* c = sm.tile + (size_t)((v - oy) * box + (u - ox)) * NV;
+            const int lx = u - ox;
+            const uint4* c = sm.tile + (size_t)(((lx >> 4) * box + (v - oy)) * kRtGroup + (lx & (kRtGroup - 1))) * NV;
 #pragma unroll
             for (int k = 0; k < NV; k++) t[jj][k] = c[k];
           }
@@ -181,8 +188,9 @@ int launch_refine_tile_f16(const uint16_t* D11, const uint16_t* D21, const int64
   if (kRtQ + 2 * radius * dilation_max > kRtBoxBig) return 1;  // widest window must fit the big box
   if (b > 65535 || ((uintptr_t)D11 & 15) != 0) return 1;
   CUtensorMap big, small;
-  if (!encode_image_tiles(&big, D11, b, h, w, fdim, 2, kRtBoxBig, kRtBoxBig)) return 1;
-  if (!encode_image_tiles(&small, D11, b, h, w, fdim, 2, kRtBoxSmall, kRtBoxSmall)) return 1;
+  // descriptor rows as fp32 elements (two halves each; the copy engine only moves bytes)
+  if (!encode_row_tiles_f32(&big, D11, b, h, w * (fdim / 2), kRtGroup * (fdim / 2), kRtBoxBig)) return 1;
+  if (!encode_row_tiles_f32(&small, D11, b, h, w * (fdim / 2), kRtGroup * (fdim / 2), kRtBoxSmall)) return 1;
   if (fdim == 24) return launch_tile_fdim<24>(big, small, D11, D21, p1, p1_new, b, h, w, dilation_max, st);
   return launch_tile_fdim<16>(big, small, D11, D21, p1, p1_new, b, h, w, dilation_max, st);
 }
