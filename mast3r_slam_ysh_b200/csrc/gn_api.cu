@@ -161,7 +161,8 @@ static int gn_begin_impl(GnWs& ws, const m3r_gn_params* p, const float* Xs, cons
                          const int64_t* local_jj, const int64_t* idx, const uint8_t* valid, const float* Q,
                          const int64_t* all_ii, const int64_t* all_jj, int num_all_edges, cudaStream_t st) {
   int rc;
-  if ((rc = launch_index_prep(ws, local_ii, local_jj, all_ii, all_jj, num_all_edges, st)) != M3R_OK) return rc;
+  cudaEvent_t plan_join = nullptr;  // the solver plans run next to the packing pre-pass (gn_solve.cu)
+  if ((rc = launch_index_prep(ws, local_ii, local_jj, all_ii, all_jj, num_all_edges, st, &plan_join)) != M3R_OK) return rc;
   if (p->kind == M3R_GN_CALIB)
     M3R_CUDA(cudaMemcpyAsync(ws.Kdev(), p->K, sizeof(float) * 9, cudaMemcpyDeviceToDevice, st));
   // the full system buffer is cleared once so the (never read) upper triangle stays finite for the all-reduce
@@ -170,9 +171,10 @@ static int gn_begin_impl(GnWs& ws, const m3r_gn_params* p, const float* Xs, cons
     zero_f32_kernel<<<ceil_div(ws.L.n, 256), 256, 0, st>>>(ws.dx(), ws.L.n);
     M3R_LAUNCH_CHECK();
   }
-  if ((rc = launch_pack_points(ws, Xs, Cs, p->C_thresh, st)) != M3R_OK) return rc;
-  if ((rc = launch_pack_edges(ws, *p, Xs, Cs, idx, valid, Q, st)) != M3R_OK) return rc;
-  return M3R_OK;
+  if ((rc = launch_pack_points(ws, Xs, Cs, p->C_thresh, st)) == M3R_OK)
+    rc = launch_pack_edges(ws, *p, Xs, Cs, idx, valid, Q, st);
+  const int rcj = join_solver_plans(plan_join, st);  // also on the error path: the event must not leak
+  return rc != M3R_OK ? rc : rcj;
 }
 
 // one GN iteration = the Hessian kernel + ONE fused solver launch; the sharded path splits the latter at the all-reduce

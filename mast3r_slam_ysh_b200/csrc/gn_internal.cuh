@@ -121,7 +121,8 @@ int launch_export_blocks(const GnWs& ws, float* Hs, float* gs, cudaStream_t st);
 
 // gn_solve.cu
 int launch_index_prep(const GnWs& ws, const int64_t* local_ii, const int64_t* local_jj, const int64_t* all_ii,
-                      const int64_t* all_jj, int num_all_edges, cudaStream_t st);
+                      const int64_t* all_jj, int num_all_edges, cudaStream_t st, cudaEvent_t* plan_join);
+int join_solver_plans(cudaEvent_t plan_join, cudaStream_t st);
 int launch_direct_edge_index(const GnWs& ws, const int64_t* ii_edge, const int64_t* jj_edge, cudaStream_t st);
 
 // gn_fused.cu

@@ -482,8 +482,32 @@ __global__ void __launch_bounds__(32) nd_plan_kernel(int* __restrict__ sky, int 
   }
 }
 
+// one non-blocking side stream per device for the solver plans (created on first use, kept for the process)
+static cudaStream_t plan_side_stream() {
+  static cudaStream_t side[kMaxDevices] = {};
+  static bool tried[kMaxDevices] = {};
+  const int d = current_device_slot();
+  if (!tried[d]) {
+    tried[d] = true;
+    if (cudaStreamCreateWithFlags(&side[d], cudaStreamNonBlocking) != cudaSuccess) {
+      side[d] = nullptr;
+      (void)cudaGetLastError();
+    }
+  }
+  return side[d];
+}
+
+// the caller's stream waits for the plans that launch_index_prep put on the side stream (no-op if there are none)
+int join_solver_plans(cudaEvent_t plan_join, cudaStream_t st) {
+  if (plan_join == nullptr) return M3R_OK;
+  M3R_CUDA(cudaStreamWaitEvent(st, plan_join, 0));
+  M3R_CUDA(cudaEventDestroy(plan_join));
+  return M3R_OK;
+}
+
 int launch_index_prep(const GnWs& ws, const int64_t* local_ii, const int64_t* local_jj, const int64_t* all_ii,
-                      const int64_t* all_jj, int num_all_edges, cudaStream_t st) {
+                      const int64_t* all_jj, int num_all_edges, cudaStream_t st, cudaEvent_t* plan_join) {
+  *plan_join = nullptr;
   const int E = ws.L.num_edges;
   const int count = 2 * num_all_edges;
   if (count <= kPrepMaxCount) {
@@ -502,15 +526,35 @@ int launch_index_prep(const GnWs& ws, const int64_t* local_ii, const int64_t* lo
                                                          ws.inc_list(), ws.inc_other(), ws.state(), ws.sky());
       M3R_LAUNCH_CHECK();
       if (g_solver_mode != 1 && ws.L.n > kSmallMaxN && ws.L.nblk <= kSkyMaxBlk) {
-        skyline_plan_kernel<<<1, 128, 0, st>>>(ws.sky(), ws.L.n_free, ws.L.nblk, ws.state());
+        // The solver plans (0.07 + 0.21 ms at 256 keyframes, serial integer code on a handful of threads) are first
+        // needed by the first solver launch: they run on a side stream next to the packing pre-pass (0.46 ms and more),
+        // forked here and joined by join_solver_plans() at the end of gn_begin.
+        cudaStream_t ps = st;
+        *plan_join = nullptr;
+        cudaStream_t side = plan_side_stream();
+        cudaEvent_t fork = nullptr;
+        if (side != nullptr && cudaEventCreateWithFlags(&fork, cudaEventDisableTiming) == cudaSuccess &&
+            cudaEventCreateWithFlags(plan_join, cudaEventDisableTiming) == cudaSuccess) {
+          M3R_CUDA(cudaEventRecord(fork, st));
+          M3R_CUDA(cudaStreamWaitEvent(side, fork, 0));
+          ps = side;
+        } else {  // no side stream or no events: the plans simply run in line
+          (void)cudaGetLastError();
+          if (fork != nullptr) (void)cudaEventDestroy(fork);
+          fork = nullptr;
+          *plan_join = nullptr;
+        }
+        skyline_plan_kernel<<<1, 128, 0, ps>>>(ws.sky(), ws.L.n_free, ws.L.nblk, ws.state());
         M3R_LAUNCH_CHECK();
         if (g_solver_mode != 2 && ws.L.off_nd != 0 && ws.L.nblk >= 8) {
           int* ticket = ws.sky() + SkyPlan::total(ws.L.n_free) + kNdCandP * kNdCandSw * NdPlan::total;
-          M3R_CUDA(cudaMemsetAsync(ticket, 0x7f, sizeof(int), st));
-          M3R_CUDA(cudaMemsetAsync(ticket + 1, 0, sizeof(int), st));
-          nd_plan_kernel<<<kNdCandP * kNdCandSw, 32, 0, st>>>(ws.sky(), ws.L.n_free, ws.L.nblk, ws.state(), ticket);
+          M3R_CUDA(cudaMemsetAsync(ticket, 0x7f, sizeof(int), ps));
+          M3R_CUDA(cudaMemsetAsync(ticket + 1, 0, sizeof(int), ps));
+          nd_plan_kernel<<<kNdCandP * kNdCandSw, 32, 0, ps>>>(ws.sky(), ws.L.n_free, ws.L.nblk, ws.state(), ticket);
           M3R_LAUNCH_CHECK();
         }
+        if (ps != st) M3R_CUDA(cudaEventRecord(*plan_join, side));
+        if (fork != nullptr) M3R_CUDA(cudaEventDestroy(fork));  // released once the work that waits on it has passed
       }
       return M3R_OK;
     }
