@@ -141,36 +141,60 @@ __device__ __forceinline__ void st_release_sys_u64(unsigned long long* p, unsign
   asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
 }
 
-// grid barrier over all CTAs of this launch whose last local arriver also meets the other ranks at value `v`
+__device__ __forceinline__ unsigned long long ld_relaxed_sys_u64(const unsigned long long* p) {
+  unsigned long long v;
+  asm volatile("ld.relaxed.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_relaxed_sys_u64(unsigned long long* p, unsigned long long v) {
+  asm volatile("st.relaxed.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+
+// Grid barrier over all CTAs of this launch; the CTA that arrives last also meets the other ranks at value `v`.
+// Warp 0 of every CTA takes part: lane 0 does the local arrival, and in the last CTA LANE p talks to PEER p -- the
+// signals go out together and the flags are polled together (one fence before the relaxed signal stores, one after the
+// relaxed polls).  The first version signalled and polled the peers one after the other from a single thread with
+// release stores / acquire loads: ~27 us per barrier at 8 ranks, 120 us for the whole all-reduce phase against 45 us
+// at 2 ranks (tools/multi_timeline.py).
 __device__ __forceinline__ void grid_peer_barrier(const FusedArgs& A, unsigned long long v) {
   __syncthreads();
-  if (threadIdx.x == 0) {
+  if (threadIdx.x < 32) {
+    const int lane = threadIdx.x;
     int* count = A.state + kBarCount;
     int* gen = A.state + kBarGen;
-    const int g = ld_relaxed_i(gen);
-    __threadfence_system();
-    if (atomicAdd(count, 1) == (int)gridDim.x - 1) {
-      atomicExch(count, 0);
+    int g = 0, last = 0;
+    if (lane == 0) {
+      g = ld_relaxed_i(gen);
+      __threadfence_system();  // this CTA's writes, peer stores included, are visible system-wide before it arrives
+      last = atomicAdd(count, 1) == (int)gridDim.x - 1;
+      if (last) atomicExch(count, 0);
+    }
+    last = __shfl_sync(0xffffffffu, last, 0);
+    if (last) {
       const PeerInfo& P = A.peer;
-      for (int p = 0; p < P.world; p++)
-        if (p != P.rank) st_release_sys_u64(P.flags[p] + P.rank, v);
-      for (int p = 0; p < P.world; p++) {
-        if (p == P.rank) continue;
+      __syncwarp();
+      if (lane < P.world && lane != P.rank) {
+        __threadfence_system();  // cumulative: everything the arrivals ordered before lane 0's atomic comes before the signal
+        st_relaxed_sys_u64(P.flags[lane] + P.rank, v);
         long long spins = 0;
-        while (ld_acquire_sys_u64(P.flags[P.rank] + p) < v) {
+        while (ld_relaxed_sys_u64(P.flags[P.rank] + lane) < v) {
           __nanosleep(64);
           if (++spins > (1LL << 25)) {  // ~4 s: give up instead of hanging the GPU
             A.state[kPeerTimeout] = 1;
             break;
           }
         }
+        __threadfence_system();  // the peer's writes before its signal are visible from here on
       }
-      __threadfence_system();
-      st_release_i(gen, g + 1);
-    } else {
+      __syncwarp();
+      if (lane == 0) {
+        __threadfence_system();
+        st_release_i(gen, g + 1);
+      }
+    } else if (lane == 0) {
       while (ld_relaxed_i(gen) == g) __nanosleep(40);
     }
-    __threadfence_system();
+    if (lane == 0) __threadfence_system();
   }
   __syncthreads();
 }
@@ -211,11 +235,18 @@ __device__ __forceinline__ void peer_allreduce_phase(const FusedArgs& A, int sky
       const size_t i = c * THREADS + threadIdx.x;
       if (i < n2) peer_sum_store(A, i);
     }
-  } else {  // row-major with leading dimension ld (even): row r holds columns 0..min(r, n-1)
-    for (int r = P.rank + P.world * blockIdx.x; r <= A.n; r += P.world * gridDim.x) {
+  } else {  // row-major with leading dimension ld (even): row r holds columns row_first_col(r)..min(r, n-1)
+    // Work items = (row of this rank, chunk of THREADS double2), chunk-major: a thread makes ONE remote round trip per
+    // item and a CTA gets at most two or three non-empty items.  (One CTA per row, looping over the row, gave the threads
+    // of the long rows at the bottom of a ring's envelope four or five round trips in a row while most of the grid idled.)
+    const int rows = (A.n - P.rank) / P.world + 1;              // rows P.rank, P.rank + world, ... <= n
+    const int chunks = ((A.n + 1) / 2 + THREADS - 1) / THREADS;  // of the longest row
+    for (int item = blockIdx.x; item < rows * chunks; item += gridDim.x) {
+      const int chunk = item / rows;
+      const int r = P.rank + P.world * (item - chunk * rows);
       const int len2 = (min(r + 1, A.n) + 1) / 2;
-      const size_t base2 = (size_t)r * A.ld / 2;
-      for (int i = row_first_col(A, sky, r) / 2 + threadIdx.x; i < len2; i += THREADS) peer_sum_store(A, base2 + i);
+      const int i = row_first_col(A, sky, r) / 2 + chunk * THREADS + threadIdx.x;
+      if (i < len2) peer_sum_store(A, (size_t)r * A.ld / 2 + i);
     }
   }
   grid_peer_barrier(A, 2 * P.epoch + 2);
