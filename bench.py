@@ -66,6 +66,9 @@ class ClockSampler(threading.Thread):
             phys = int(vis.split(",")[index]) if vis and all(t.strip().isdigit() for t in vis.split(",")) else index
             self.nv, self.h = pynvml, pynvml.nvmlDeviceGetHandleByIndex(phys)
             self.max_mhz = int(pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM))
+            # the first query of each kind can take longer than the whole timed region: pay for it here
+            pynvml.nvmlDeviceGetClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+            pynvml.nvmlDeviceGetCurrentClocksEventReasons(self.h)
         except Exception as ex:  # noqa
             self.nv, self.err = None, repr(ex)
 
@@ -82,6 +85,17 @@ class ClockSampler(threading.Thread):
 
     def summary(self):
         self.stop_flag = True
+        if self.is_alive():
+            self.join(timeout=1.0)  # a query that was in flight when the timed region ended still counts: it began inside it
+        if self.nv is not None and not self.sm:
+            # the timed region (a dozen milliseconds) was shorter than NVML's first answer: one query right after it, while
+            # the clocks have not had time to drop (flagged below)
+            try:
+                self.sm.append(int(self.nv.nvmlDeviceGetClockInfo(self.h, self.nv.NVML_CLOCK_SM)))
+                self.mask |= int(self.nv.nvmlDeviceGetCurrentClocksEventReasons(self.h))
+                self.err = (self.err or "") + "no sample completed inside the timed region; one taken right after it"
+            except Exception as ex:  # noqa
+                self.err = repr(ex)
         sm = sorted(self.sm)
         out = {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": self.max_mhz,
                "reasons": [n for n, bit in self.REASONS.items() if self.mask & bit], "samples": len(sm),
