@@ -456,7 +456,7 @@ __global__ void __launch_bounds__(128) skyline_plan_kernel(int* __restrict__ sky
 // ---- segmented schedule of the envelope solver (nd_plan.cuh), once per solve, after skyline_plan_kernel.  The symbolic
 //      elimination is serial integer code (~0.18 ms at 256 keyframes): one candidate (interiors x separator width) per
 //      CTA, one thread each, every valid candidate writes its whole plan into its own slot, the cheapest one is picked with
-//      an atomic minimum and the CTA that finishes last publishes it if its chain is under 3/4 of the plain envelope's:
+//      an atomic minimum and the CTA that finishes last publishes it if it beats the plain envelope solver (nd_accept):
 //      state[kNdSegs] = number of interiors (0 = not segmented), state[kNdSlot] = the slot.  (As lanes of one warp the 21
 //      candidates diverged and ran one after the other: 1.0 ms.)
 __global__ void __launch_bounds__(32) nd_plan_kernel(int* __restrict__ sky, int n_free, int nblk, int* __restrict__ state,
@@ -473,7 +473,7 @@ __global__ void __launch_bounds__(32) nd_plan_kernel(int* __restrict__ sky, int 
     __threadfence();
     const int cost = atomicMin(ticket, 0x7fffffff);
     int segs = 0, slot = 0;
-    if (cost < 0x7f000000 && (cost >> 5) < 12 * nblk) {  // (the ticket starts at 0x7f7f7f7f: no valid candidate)
+    if (cost < 0x7f000000 && nd_accept(cost >> 5, nblk)) {  // (the ticket starts at 0x7f7f7f7f: no valid candidate)
       slot = cost & 31;
       segs = sky[SkyPlan::total(n_free) + (size_t)slot * NdPlan::total + NdPlan::hdr];
     }
@@ -623,7 +623,7 @@ extern "C" int m3r_debug_nd_plan(const int* adj, int nblk, int P, int sw, int* p
     nd_candidate(c, p, w);
     if (nd_simulate(adj, nblk, p, w, nullptr, &c16) && c16 * 32 + c < best) best = c16 * 32 + c;
   }
-  if (best == 0x7fffffff || (best >> 5) >= 12 * nblk) return 0;
+  if (best == 0x7fffffff || !nd_accept(best >> 5, nblk)) return 0;
   int p, w;
   nd_candidate(best & 31, p, w);
   return nd_simulate(adj, nblk, p, w, plan_out, &c16) ? p : 0;

@@ -234,13 +234,17 @@ __host__ __device__ inline bool nd_simulate(const int* adj, int nblk, int P, int
     out[NdPlan::hdr + 2] = lanes;
     out[NdPlan::hdr + 3] = sw;
   }
-  // the separator stage's steps carry more tiles than an interior's: weigh them 5/4
-  *cost16 = 16 * longest + 20 * nS;
+  // Measured (tools/time_phases.py, rings and chains of 40-256 keyframes): a separator step costs about what an interior
+  // step costs (fewer rows to solve, more tiles to update), and the three barriers, the reduce and the per-stage set-up
+  // cost about three steps.  The plan is used if that beats the plain chain of nblk steps (nd_accept).
+  *cost16 = 16 * longest + 16 * nS + 48;
   if (out) out[NdPlan::hdr + 4] = *cost16;
   return true;
 }
 
-// candidates tried by the planner, best valid one wins if it shortens the chain to under 3/4 of the plain envelope's
+__host__ __device__ inline bool nd_accept(int cost16, int nblk) { return cost16 < 16 * nblk; }
+
+// candidates tried by the planner, the cheapest valid one wins if nd_accept says it beats the plain envelope solver
 constexpr int kNdCandP = 7;   // P = 2 .. 8
 constexpr int kNdCandSw = 3;  // sw = 1 .. 3
 __host__ __device__ inline void nd_candidate(int c, int& P, int& sw) {
