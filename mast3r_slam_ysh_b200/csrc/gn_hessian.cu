@@ -560,6 +560,9 @@ __global__ void __launch_bounds__(kHessThreads, kHessCtasPerSm) hessian_kernel(c
   while (p < p_end) {
     // ---- plan the next (up to kHessMaxSeg) edge segments of the CTA's record range: thread 0 finds the edge that owns
     //      record p (binary search once, then a forward walk over empty edges) and the segment bounds ...
+    //      (Tried, r2: a 32-way search by warp 0 with the next 32 offsets fetched in one go, and the first copies issued
+    //      before the edge constants are built: 78.8 against 78.1 us at configs[2] -- the offsets sit in L1/L2 and the
+    //      plan is not where the ~13 us of fixed cost per launch go.)
     if (threadIdx.x == 0) {
       int en;
       if (e_cur < 0) {
