@@ -422,6 +422,49 @@ def test_gn_envelope_solver_vs_dense_solver_and_oracle(be, orc, kind, nkf, expec
     assert np.linalg.norm(out[1][0] - dx_o) / nrm <= oracle_tol
 
 
+@pytest.mark.parametrize("seed", [1, 2, 3, 4])
+def test_gn_solvers_agree_on_random_window_graphs(be, seed):
+    """Random chains / rings (window 1-9, 60-200 keyframes, a few loop closures): whichever solver the planner picks
+    (segmented, plain envelope or dense) must reproduce the dense solver's dx; the segmented one is used at least once."""
+    from mast3r_slam_ysh_b200 import synthetic as syn
+    rng = np.random.default_rng(100 + seed)
+    nkf = int(rng.integers(60, 200))
+    win = int(rng.integers(1, 10))
+    ring = bool(rng.integers(0, 2))
+    ii, jj = [], []
+    for i in range(nkf):
+        for k in range(1, win + 1):
+            if ring or i + k < nkf:
+                ii.append(i); jj.append((i + k) % nkf)
+    for _ in range(int(rng.integers(0, 3))):
+        a, b = (int(x) for x in rng.integers(0, nkf, 2))
+        if abs(a - b) > 1:
+            ii.append(min(a, b)); jj.append(max(a, b))
+    g = syn.make_gn_problem(nkf, 12, 16, (ii, jj), seed=seed, yaw_step_deg=360.0 / nkf if ring else 2.0)
+    args = [g[k].to(DEV) for k in ("Xs", "Cs", "ii", "jj", "idx_ii2jj", "valid_match", "Q")]
+    P = (LO["sigma_ray"], LO["sigma_dist"], LO["C_conf"], LO["Q_conf"])
+    out = {}
+    try:
+        for mode in (1, 0):
+            _solver_mode(mode)
+            T = g["Twc"].to(DEV)
+            (dx,), info = be.gauss_newton_rays(T, *args, *P, 1, 1e-8, return_info=True)
+            info = info.cpu().numpy()
+            out[mode] = (dx.cpu().numpy().astype(np.float64), int(info[2]), (int(info[3]) >> 20) & 15)
+    finally:
+        _solver_mode(0)
+    assert out[0][1] == out[1][1]  # both factorisations succeed, or both fail (a keyframe without valid matches)
+    if out[1][1] == 0:
+        nrm = max(np.linalg.norm(out[1][0]), 1e-30)
+        assert np.linalg.norm(out[0][0] - out[1][0]) / nrm <= 1e-6, (nkf, win, ring, out[0][2])
+    _SEGMENTED_SEEN.append(out[0][2])
+    if seed == 4:
+        assert any(v >= 2 for v in _SEGMENTED_SEEN), _SEGMENTED_SEEN
+
+
+_SEGMENTED_SEEN = []
+
+
 def test_gn_segmented_solver_full_solve_and_failure(be):
     """Ten iterations on a 128-keyframe ring (four interiors): the segmented envelope solver must land on the poses of the
     plain envelope solver and of the dense solver (that GN converges on such graphs is the oracle tests' business: at

@@ -161,3 +161,26 @@ def test_open_chain_splits_and_dense_or_random_graphs_do_not():
     dense = [(i, j) for i in range(40) for j in range(i + 1, 40)]
     adj, nblk = block_adj(40, dense)
     assert run_plan(adj, nblk)[0] == 0
+
+
+def test_random_chains_with_extra_edges_never_yield_an_invalid_plan():
+    """40 random graphs: a chain or ring with a random window plus a few random long-range edges.  Whatever the planner
+    decides, a plan it returns must be a valid elimination (and most plain chains must split)."""
+    rng = np.random.default_rng(7)
+    split = 0
+    for trial in range(40):
+        nkf = int(rng.integers(45, 300))
+        win = int(rng.integers(1, 10))
+        ring = bool(rng.integers(0, 2))
+        edges = [(i, (i + k) % nkf) for i in range(nkf) for k in range(1, win + 1) if ring or i + k < nkf]
+        for _ in range(int(rng.integers(0, 4))):  # loop closures
+            a, b = (int(x) for x in rng.integers(0, nkf, 2))
+            if a != b:
+                edges.append((a, b))
+        adj, nblk = block_adj(nkf, edges)
+        segs, plan = run_plan(adj, nblk)
+        if segs:
+            check_plan(adj, nblk, segs, plan)
+            split += 1
+    assert split >= 10
+
