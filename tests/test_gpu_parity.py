@@ -465,6 +465,33 @@ def test_gn_solvers_agree_on_random_window_graphs(be, seed):
 _SEGMENTED_SEEN = []
 
 
+def test_gn_solves_on_two_streams_share_the_plan_side_stream(be):
+    """gn_begin forks the solver plans onto a per-device side stream and joins them after the packing pre-pass; two
+    solves enqueued back to back on different streams (different graphs, both segmented) must give what they give alone."""
+    from mast3r_slam_ysh_b200 import synthetic as syn
+    P = (LO["sigma_ray"], LO["sigma_dist"], LO["C_conf"], LO["Q_conf"])
+    probs = []
+    for nkf, seed in ((128, 11), (96, 12), (64, 13)):
+        g = syn.make_gn_problem(nkf, 12, 16, syn.ring_edges(nkf, 8), seed=seed, yaw_step_deg=360.0 / nkf)
+        probs.append((g, [g[k].to(DEV) for k in ("Xs", "Cs", "ii", "jj", "idx_ii2jj", "valid_match", "Q")]))
+    alone = []
+    for g, args in probs:
+        T = g["Twc"].to(DEV)
+        be.gauss_newton_rays(T, *args, *P, 3, 1e-8)
+        alone.append(T.clone())
+    torch.cuda.synchronize()
+    streams = [torch.cuda.Stream(device=DEV) for _ in probs]
+    for rep in range(3):
+        Ts = [g["Twc"].to(DEV) for g, _ in probs]
+        torch.cuda.synchronize()
+        for (g, args), T, st in zip(probs, Ts, streams):
+            with torch.cuda.stream(st):
+                be.gauss_newton_rays(T, *args, *P, 3, 1e-8)
+        torch.cuda.synchronize()
+        for T, want in zip(Ts, alone):
+            assert torch.equal(T, want), rep
+
+
 def test_gn_segmented_solver_full_solve_and_failure(be):
     """Ten iterations on a 128-keyframe ring (four interiors): the segmented envelope solver must land on the poses of the
     plain envelope solver and of the dense solver (that GN converges on such graphs is the oracle tests' business: at
