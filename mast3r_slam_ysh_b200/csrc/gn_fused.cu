@@ -1285,12 +1285,37 @@ template <bool SOLVE>
 __device__ __forceinline__ void nd_back_rows(const FusedArgs& A, NdBackSmem& sm, double* s_y, const int* rowlist, int cnt) {
   const int n = A.n, ld = A.ld;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  constexpr int kWarps = kFusedThreads / 32;
   if (cnt <= 0) return;
   if (SOLVE) nd_back_stage(A, sm.b, rowlist[0], 0);
   for (int i = 0; i < cnt; i++) {
     const int kb = rowlist[i];
     const int c0 = kb * kBlk;
     const int rows = min(kBlk, n - c0);
+    // column blocks of this block row, dealt round-robin over the warps; the warp's FIRST one does not depend on x_kb:
+    // it is fetched now, so that its L2 round trip overlaps the triangular solve below
+    unsigned m[4];
+#pragma unroll
+    for (int w = 0; w < 4; w++) m[w] = sm.lrow[kb][w] & sm.cols[w];
+    int first_cb = -1;
+    {
+      int slot = 0;
+#pragma unroll
+      for (int w = 0; w < 4; w++) {
+        unsigned mm = m[w];
+        while (mm && first_cb < 0) {
+          const int cb = 32 * w + __ffs((int)mm) - 1;
+          mm &= mm - 1;
+          if (slot++ == warp) first_cb = cb;
+        }
+      }
+    }
+    double vp[kBlk];
+    if (first_cb >= 0) {
+      const int c = kBlk * first_cb + lane;
+#pragma unroll
+      for (int r = 0; r < kBlk; r++) vp[r] = (r < rows && c < n) ? __ldcg(A.sys + (size_t)(c0 + r) * ld + c) : 0.0;
+    }
     if (SOLVE) {
       asm volatile("cp.async.wait_group 0;" ::: "memory");
       __syncthreads();  // L_kk landed for everyone; the previous row's y update is complete
@@ -1309,14 +1334,24 @@ __device__ __forceinline__ void nd_back_rows(const FusedArgs& A, NdBackSmem& sm,
       }
     }
     __syncthreads();
-    // one warp per column block, one column per lane (coalesced along the row of L)
+    if (first_cb >= 0) {
+      double a0 = 0.0, a1 = 0.0;
+#pragma unroll
+      for (int r = 0; r < kBlk; r += 2) {
+        a0 = fma(vp[r], s_y[c0 + r], a0);
+        a1 = fma(vp[r + 1], s_y[c0 + r + 1], a1);
+      }
+      s_y[kBlk * first_cb + lane] -= a0 + a1;
+    }
+    // the warp's other column blocks (rows of L with more than kWarps of them: the long rows of a separator)
     int slot = 0;
     for (int w = 0; w < 4; w++) {
-      unsigned m = sm.lrow[kb][w] & sm.cols[w];
-      while (m) {
-        const int cb = 32 * w + __ffs((int)m) - 1;
-        m &= m - 1;
-        if ((slot++ & (kFusedThreads / 32 - 1)) != warp) continue;
+      unsigned mm = m[w];
+      while (mm) {
+        const int cb = 32 * w + __ffs((int)mm) - 1;
+        mm &= mm - 1;
+        const int sl = slot++;
+        if (sl < kWarps || (sl & (kWarps - 1)) != warp) continue;
         const int c = kBlk * cb + lane;
         double v[kBlk];
 #pragma unroll
