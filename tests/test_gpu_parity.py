@@ -422,7 +422,7 @@ def test_gn_envelope_solver_vs_dense_solver_and_oracle(be, orc, kind, nkf, expec
     assert np.linalg.norm(out[1][0] - dx_o) / nrm <= oracle_tol
 
 
-@pytest.mark.parametrize("seed", [1, 2, 3, 4])
+@pytest.mark.parametrize("seed", [1, 2, 3, 4, 5, 6, 7, 8])
 def test_gn_solvers_agree_on_random_window_graphs(be, seed):
     """Random chains / rings (window 1-9, 60-200 keyframes, a few loop closures): whichever solver the planner picks
     (segmented, plain envelope or dense) must reproduce the dense solver's dx; the segmented one is used at least once."""
@@ -458,8 +458,8 @@ def test_gn_solvers_agree_on_random_window_graphs(be, seed):
         nrm = max(np.linalg.norm(out[1][0]), 1e-30)
         assert np.linalg.norm(out[0][0] - out[1][0]) / nrm <= 1e-6, (nkf, win, ring, out[0][2])
     _SEGMENTED_SEEN.append(out[0][2])
-    if seed == 4:
-        assert any(v >= 2 for v in _SEGMENTED_SEEN), _SEGMENTED_SEEN
+    if seed == 8:
+        assert sum(v >= 2 for v in _SEGMENTED_SEEN) >= 3, _SEGMENTED_SEEN
 
 
 _SEGMENTED_SEEN = []
