@@ -378,6 +378,7 @@ def _long_graph(kind, nkf):
 @pytest.mark.parametrize("kind,nkf,expect_envelope,oracle_tol", [
     ("ring8", 70, True, 1e-4), ("chain3", 40, True, 1e-4),   # north_star tolerance
     ("ring8", 128, True, 1e-4), ("chain3", 150, True, 2e-3),  # long enough for several interiors of the segmented solver
+    ("ring8", 512, True, 2e-3),                               # the reference's keyframe cap: 112 column blocks, 7 interiors
     # long open chains with two neighbours are weakly constrained: the fp32 rounding of the Hessian blocks (ours and the
     # oracle's accumulate in different orders) is amplified by the conditioning for EITHER solver (the dense one alone
     # runs the last case), so the oracle bar is looser there; solver-vs-solver below stays at 1e-6
@@ -410,7 +411,7 @@ def test_gn_envelope_solver_vs_dense_solver_and_oracle(be, orc, kind, nkf, expec
         _solver_mode(0)
     assert out[1][1] == 0 and out[1][2] == 0 and out[2][2] == 0
     assert (out[0][1] > 0) == expect_envelope and (out[2][1] > 0) == expect_envelope
-    if (kind, nkf) in (("ring8", 128), ("chain3", 150), ("chain2+loops", 90), ("chain3", 40), ("chain2", 65)):
+    if (kind, nkf) in (("ring8", 128), ("ring8", 512), ("chain3", 150), ("chain2+loops", 90), ("chain3", 40), ("chain2", 65)):
         assert out[0][2] >= 2, "this graph splits: the segmented schedule must have been used"
     if not expect_envelope:
         assert out[0][2] == 0
